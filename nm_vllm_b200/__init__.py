@@ -1,0 +1,48 @@
+"""nm_vllm_b200 -- B200-native (sm_100a) decode hot path behind nm-vllm's operator API.
+
+Only what the path needs lives here:
+  csrc/            hand-written CUDA kernels + the C ABI (include/b200_ops.h) + the torch operator shim
+  _custom_ops.py   mirror of vllm/_custom_ops.py for the hot-path operators (same names / argument order / returns)
+  quantization/    QuantizationConfig / LinearMethodBase mirrors (gptq_marlin, gptq_marlin_24, marlin, fp8,
+                   compressed-tensors schemes) + layout helpers (scale permutation, 2:4 compression)
+  attention/       PagedAttention wrapper + metadata (vllm/attention/ops/paged_attn.py)
+  parallel.py      tensor-parallel linear layers: N / head sharding + NCCL all-reduce after row-parallel GEMMs
+  decoder.py       synthetic Llama decode step built from the operators above (bench / smoke harness)
+
+There is no CPU fallback: calling an operator without the built extension raises.
+"""
+import os
+
+__all__ = ["load_extension", "extension_paths", "is_built"]
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_OPS = os.path.join(_HERE, "libb200ops.so")
+_LIB_TORCH = os.path.join(_HERE, "_b200_C.so")
+_loaded = False
+
+
+def extension_paths():
+    return _LIB_OPS, _LIB_TORCH
+
+
+def is_built() -> bool:
+    return os.path.exists(_LIB_OPS) and os.path.exists(_LIB_TORCH)
+
+
+def load_extension():
+    """Load libb200ops.so + _b200_C.so (registers torch.ops._b200_C*).  Raises if the extension is not built."""
+    global _loaded
+    if _loaded:
+        return
+    if not is_built():
+        raise RuntimeError(
+            "nm_vllm_b200: the sm_100a extension is not built (expected %s and %s). "
+            "Run `python -m nm_vllm_b200.build` (or __graft_entry__.build()). There is no CPU fallback." %
+            (_LIB_OPS, _LIB_TORCH))
+    import ctypes
+
+    import torch
+
+    ctypes.CDLL(_LIB_OPS, mode=ctypes.RTLD_GLOBAL)
+    torch.ops.load_library(_LIB_TORCH)
+    _loaded = True

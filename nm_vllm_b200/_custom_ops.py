@@ -1,0 +1,169 @@
+"""Mirror of vllm/_custom_ops.py (reference lines cited per function) for the hot-path operators.
+
+Same names, positional order, defaults and return conventions; each function forwards to torch.ops._b200_C* which the
+in-tree extension registers with the reference's schema strings.  `install()` rebinds these onto an importable
+`vllm._custom_ops` so the reference's LinearMethod / PagedAttention classes call the sm_100a kernels unchanged.
+"""
+from typing import Optional, Tuple, Type
+
+import torch
+
+from . import load_extension
+
+
+def _ops():
+    load_extension()
+    return torch.ops._b200_C
+
+
+def _cache_ops():
+    load_extension()
+    return torch.ops._b200_C_cache_ops
+
+
+# ---- paged attention: vllm/_custom_ops.py:74-129 -----------------------------------------------------------------
+def paged_attention_v1(out: torch.Tensor, query: torch.Tensor, key_cache: torch.Tensor, value_cache: torch.Tensor,
+                       num_kv_heads: int, scale: float, block_tables: torch.Tensor, seq_lens: torch.Tensor,
+                       block_size: int, max_seq_len: int, alibi_slopes: Optional[torch.Tensor], kv_cache_dtype: str,
+                       kv_scale: float, tp_rank: int = 0, blocksparse_local_blocks: int = 0,
+                       blocksparse_vert_stride: int = 0, blocksparse_block_size: int = 64,
+                       blocksparse_head_sliding_step: int = 0) -> None:
+    _ops().paged_attention_v1(out, query, key_cache, value_cache, num_kv_heads, scale, block_tables, seq_lens,
+                              block_size, max_seq_len, alibi_slopes, kv_cache_dtype, kv_scale, tp_rank,
+                              blocksparse_local_blocks, blocksparse_vert_stride, blocksparse_block_size,
+                              blocksparse_head_sliding_step)
+
+
+def paged_attention_v2(out: torch.Tensor, exp_sum: torch.Tensor, max_logits: torch.Tensor, tmp_out: torch.Tensor,
+                       query: torch.Tensor, key_cache: torch.Tensor, value_cache: torch.Tensor, num_kv_heads: int,
+                       scale: float, block_tables: torch.Tensor, seq_lens: torch.Tensor, block_size: int,
+                       max_seq_len: int, alibi_slopes: Optional[torch.Tensor], kv_cache_dtype: str, kv_scale: float,
+                       tp_rank: int = 0, blocksparse_local_blocks: int = 0, blocksparse_vert_stride: int = 0,
+                       blocksparse_block_size: int = 64, blocksparse_head_sliding_step: int = 0) -> None:
+    _ops().paged_attention_v2(out, exp_sum, max_logits, tmp_out, query, key_cache, value_cache, num_kv_heads, scale,
+                              block_tables, seq_lens, block_size, max_seq_len, alibi_slopes, kv_cache_dtype, kv_scale,
+                              tp_rank, blocksparse_local_blocks, blocksparse_vert_stride, blocksparse_block_size,
+                              blocksparse_head_sliding_step)
+
+
+# ---- glue: vllm/_custom_ops.py:48-50 (silu_and_mul), :132-160 (rotary_embedding, rms_norm, fused_add_rms_norm) ----
+def silu_and_mul(out: torch.Tensor, x: torch.Tensor) -> None:
+    _ops().silu_and_mul(out, x)
+
+
+def rotary_embedding(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor, head_size: int,
+                     cos_sin_cache: torch.Tensor, is_neox: bool) -> None:
+    _ops().rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox)
+
+
+def rms_norm(out: torch.Tensor, input: torch.Tensor, weight: torch.Tensor, epsilon: float) -> None:
+    _ops().rms_norm(out, input, weight, epsilon)
+
+
+def fused_add_rms_norm(input: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor, epsilon: float) -> None:
+    _ops().fused_add_rms_norm(input, residual, weight, epsilon)
+
+
+# ---- marlin: vllm/_custom_ops.py:201-220 --------------------------------------------------------------------------
+def marlin_gemm(a: torch.Tensor, b_q_weight: torch.Tensor, b_scales: torch.Tensor, workspace: torch.Tensor,
+                size_m: int, size_n: int, size_k: int) -> torch.Tensor:
+    return _ops().marlin_gemm(a, b_q_weight, b_scales, workspace, size_m, size_n, size_k)
+
+
+def gptq_marlin_24_gemm(a: torch.Tensor, b_q_weight: torch.Tensor, b_meta: torch.Tensor, b_scales: torch.Tensor,
+                        workspace: torch.Tensor, num_bits: int, size_m: int, size_n: int,
+                        size_k: int) -> torch.Tensor:
+    return _ops().gptq_marlin_24_gemm(a, b_q_weight, b_meta, b_scales, workspace, num_bits, size_m, size_n, size_k)
+
+
+# ---- cutlass_scaled_mm: vllm/_custom_ops.py:223-238 -----------------------------------------------------------------
+def cutlass_scaled_mm_supports_fp8(cuda_device_capability: int) -> bool:
+    return _ops().cutlass_scaled_mm_supports_fp8(cuda_device_capability)
+
+
+def cutlass_scaled_mm(a: torch.Tensor, b: torch.Tensor, scale_a: torch.Tensor, scale_b: torch.Tensor,
+                      out_dtype: Type[torch.dtype], bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    assert (b.shape[0] % 16 == 0 and b.shape[1] % 16 == 0)
+    assert (out_dtype is torch.bfloat16 or out_dtype is torch.float16)
+    m = a.shape[0]
+    n = b.shape[1]
+    out = torch.empty((m, n), dtype=out_dtype, device=a.device)
+    _ops().cutlass_scaled_mm(out, a, b, scale_a, scale_b, bias)
+    return out
+
+
+# ---- gptq_marlin: vllm/_custom_ops.py:257-280 ----------------------------------------------------------------------
+def gptq_marlin_repack(b_q_weight: torch.Tensor, perm: torch.Tensor, size_k: int, size_n: int,
+                       num_bits: int) -> torch.Tensor:
+    return _ops().gptq_marlin_repack(b_q_weight, perm, size_k, size_n, num_bits)
+
+
+def gptq_marlin_gemm(a: torch.Tensor, b_q_weight: torch.Tensor, b_scales: torch.Tensor, g_idx: torch.Tensor,
+                     perm: torch.Tensor, workspace: torch.Tensor, num_bits: int, size_m: int, size_n: int,
+                     size_k: int, is_k_full: bool) -> torch.Tensor:
+    return _ops().gptq_marlin_gemm(a, b_q_weight, b_scales, g_idx, perm, workspace, num_bits, size_m, size_n, size_k,
+                                   is_k_full)
+
+
+# ---- fp8 / int8 activation quantizers: vllm/_custom_ops.py:284-350 --------------------------------------------------
+def scaled_fp8_quant(input: torch.Tensor, scale: Optional[torch.Tensor] = None,
+                     batch_dim_padding: Optional[int] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    if batch_dim_padding:
+        shape = (max(batch_dim_padding, input.shape[0]), *input.shape[1:])
+        output = torch.empty(shape, device=input.device, dtype=torch.float8_e4m3fn)
+    else:
+        output = torch.empty_like(input, dtype=torch.float8_e4m3fn)
+    if scale is None:
+        scale = torch.zeros(1, device=input.device, dtype=torch.float32)
+        _ops().dynamic_scaled_fp8_quant(output, input, scale)
+    else:
+        _ops().static_scaled_fp8_quant(output, input, scale)
+    return output, scale
+
+
+def scaled_int8_quant(input: torch.Tensor, scale: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    output = torch.empty_like(input, dtype=torch.int8)
+    if scale is not None:
+        _ops().static_scaled_int8_quant(output, input, scale)
+        return output, scale
+    input_scales = torch.empty((input.numel() // input.shape[-1], 1), device=input.device, dtype=torch.float32)
+    _ops().dynamic_scaled_int8_quant(output, input, input_scales)
+    return output, input_scales
+
+
+# ---- cache ops: vllm/_custom_ops.py:370-412 ---------------------------------------------------------------------------
+def reshape_and_cache(key: torch.Tensor, value: torch.Tensor, key_cache: torch.Tensor, value_cache: torch.Tensor,
+                      slot_mapping: torch.Tensor, kv_cache_dtype: str, kv_scale: float) -> None:
+    _cache_ops().reshape_and_cache(key, value, key_cache, value_cache, slot_mapping, kv_cache_dtype, kv_scale)
+
+
+def convert_fp8(output: torch.Tensor, input: torch.Tensor, scale: float = 1.0, kv_dtype: str = "fp8") -> None:
+    _cache_ops().convert_fp8(output, input, scale, kv_dtype)
+
+
+def get_device_attribute(attribute: int, device: int) -> int:
+    load_extension()
+    return torch.ops._b200_C_cuda_utils.get_device_attribute(attribute, device)
+
+
+def get_max_shared_memory_per_block_device_attribute(device: int) -> int:
+    load_extension()
+    return torch.ops._b200_C_cuda_utils.get_max_shared_memory_per_block_device_attribute(device)
+
+
+_HOT_PATH_OPS = [
+    "paged_attention_v1", "paged_attention_v2", "silu_and_mul", "rotary_embedding", "rms_norm", "fused_add_rms_norm",
+    "marlin_gemm", "gptq_marlin_24_gemm", "cutlass_scaled_mm_supports_fp8", "cutlass_scaled_mm", "gptq_marlin_repack",
+    "gptq_marlin_gemm", "scaled_fp8_quant", "scaled_int8_quant", "reshape_and_cache", "convert_fp8",
+    "get_device_attribute", "get_max_shared_memory_per_block_device_attribute",
+]
+
+
+def install(target=None) -> list:
+    """Rebind the hot-path functions of `vllm._custom_ops` (or `target`) to this module's.  Returns the names bound."""
+    if target is None:
+        import vllm._custom_ops as target  # type: ignore
+    g = globals()
+    for name in _HOT_PATH_OPS:
+        setattr(target, name, g[name])
+    return list(_HOT_PATH_OPS)

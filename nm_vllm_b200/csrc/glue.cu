@@ -1,0 +1,145 @@
+// Decode-step glue kernels: RMSNorm (+fused residual add), SiLU*mul, rotary embedding.
+// Reference: csrc/layernorm_kernels.cu:22-47, :201-243; csrc/activation_kernels.cu:14-40;
+// csrc/pos_encoding_kernels.cu:10-93.  The rounding points of the reference are kept (each scalar_t operator there
+// rounds to the element type): norm = T(x * rsqrt(var+eps)) * w ; residual' = T(in + res) ; silu = T(x/(1+e^-x)) * y ;
+// rope = T(T(x*cos) - T(y*sin)).
+// These move <= 64 x 8192 x 2 B per call in decode: one CTA per token, 8-byte vector accesses, fp32 statistics.
+#include "common.cuh"
+
+namespace b200 {
+
+template <typename T> __device__ __forceinline__ T mul_t(T a, T b) { return from_f32<T>(to_f32<T>(a) * to_f32<T>(b)); }
+template <typename T> __device__ __forceinline__ T add_t(T a, T b) { return from_f32<T>(to_f32<T>(a) + to_f32<T>(b)); }
+template <typename T> __device__ __forceinline__ T sub_t(T a, T b) { return from_f32<T>(to_f32<T>(a) - to_f32<T>(b)); }
+
+__device__ __forceinline__ float block_sum_1024(float v, float* red) {
+  v = warp_sum(v);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float r = threadIdx.x < ((blockDim.x + 31) >> 5) ? red[threadIdx.x] : 0.f;
+    r = warp_sum(r);
+    if (threadIdx.x == 0) red[32] = r;
+  }
+  __syncthreads();
+  return red[32];
+}
+
+template <typename T, bool FUSED_ADD>
+__global__ void rms_norm_kernel(T* __restrict__ out, T* __restrict__ input, T* __restrict__ residual,
+                                const T* __restrict__ weight, float eps, int hidden) {
+  __shared__ float red[33];
+  const int64_t base = (int64_t)blockIdx.x * hidden;
+  float var = 0.f;
+  for (int i = threadIdx.x; i < hidden; i += blockDim.x) {
+    T z = input[base + i];
+    if (FUSED_ADD) {
+      z = add_t<T>(z, residual[base + i]);
+      residual[base + i] = z;
+    }
+    const float x = to_f32<T>(z);
+    var += x * x;
+  }
+  var = block_sum_1024(var, red);
+  const float inv = rsqrtf(var / hidden + eps);
+  for (int i = threadIdx.x; i < hidden; i += blockDim.x) {
+    const float x = to_f32<T>(FUSED_ADD ? residual[base + i] : input[base + i]);
+    out[base + i] = mul_t<T>(from_f32<T>(x * inv), weight[i]);
+  }
+}
+
+template <typename T>
+__global__ void silu_and_mul_kernel(T* __restrict__ out, const T* __restrict__ input, int d) {
+  const int64_t tok = blockIdx.x;
+  for (int i = threadIdx.x; i < d; i += blockDim.x) {
+    const float x = to_f32<T>(input[tok * 2 * d + i]);
+    const T y = input[tok * 2 * d + d + i];
+    out[tok * d + i] = mul_t<T>(from_f32<T>(x / (1.0f + expf(-x))), y);
+  }
+}
+
+template <typename T, bool NEOX>
+__device__ __forceinline__ void rope_one(T* arr, const T* cos_ptr, const T* sin_ptr, int rot_offset, int embed_dim) {
+  int xi, yi;
+  T c, s;
+  if (NEOX) { xi = rot_offset; yi = embed_dim + rot_offset; c = cos_ptr[xi]; s = sin_ptr[xi]; }
+  else { xi = 2 * rot_offset; yi = xi + 1; c = cos_ptr[rot_offset]; s = sin_ptr[rot_offset]; }
+  const T x = arr[xi], y = arr[yi];
+  arr[xi] = sub_t<T>(mul_t<T>(x, c), mul_t<T>(y, s));
+  arr[yi] = add_t<T>(mul_t<T>(y, c), mul_t<T>(x, s));
+}
+
+template <typename T, bool NEOX>
+__global__ void rotary_kernel(const int64_t* __restrict__ positions, T* __restrict__ query, T* __restrict__ key,
+                              const T* __restrict__ cos_sin_cache, int rot_dim, int64_t q_stride, int64_t k_stride,
+                              int num_heads, int num_kv_heads, int head_size) {
+  const int64_t tok = blockIdx.x;
+  const T* cache = cos_sin_cache + positions[tok] * rot_dim;
+  const int embed = rot_dim / 2;
+  for (int i = threadIdx.x; i < num_heads * embed; i += blockDim.x)
+    rope_one<T, NEOX>(query + tok * q_stride + (int64_t)(i / embed) * head_size, cache, cache + embed, i % embed, embed);
+  for (int i = threadIdx.x; i < num_kv_heads * embed; i += blockDim.x)
+    rope_one<T, NEOX>(key + tok * k_stride + (int64_t)(i / embed) * head_size, cache, cache + embed, i % embed, embed);
+}
+
+static inline int tok_threads(int n, int cap) {
+  int t = ((n + 31) / 32) * 32;
+  return t < cap ? (t < 32 ? 32 : t) : cap;
+}
+}  // namespace b200
+
+extern "C" int b200_rms_norm(void* out, const void* input, const void* weight, int64_t num_tokens, int hidden_size,
+                             float epsilon, int dtype, void* stream) {
+  using namespace b200;
+  if (num_tokens == 0) return B200_OK;
+  B200_DISPATCH_FLOAT(dtype, "rms_norm", {
+    rms_norm_kernel<scalar_t, false><<<(unsigned)num_tokens, tok_threads(hidden_size, 1024), 0, (cudaStream_t)stream>>>(
+        (scalar_t*)out, (scalar_t*)input, nullptr, (const scalar_t*)weight, epsilon, hidden_size);
+  });
+  B200_LAUNCH_CHECK("rms_norm");
+  return B200_OK;
+}
+
+extern "C" int b200_fused_add_rms_norm(void* input, void* residual, const void* weight, int64_t num_tokens,
+                                       int hidden_size, float epsilon, int dtype, void* stream) {
+  using namespace b200;
+  if (num_tokens == 0) return B200_OK;
+  B200_DISPATCH_FLOAT(dtype, "fused_add_rms_norm", {
+    rms_norm_kernel<scalar_t, true><<<(unsigned)num_tokens, tok_threads(hidden_size, 1024), 0, (cudaStream_t)stream>>>(
+        (scalar_t*)input, (scalar_t*)input, (scalar_t*)residual, (const scalar_t*)weight, epsilon, hidden_size);
+  });
+  B200_LAUNCH_CHECK("fused_add_rms_norm");
+  return B200_OK;
+}
+
+extern "C" int b200_silu_and_mul(void* out, const void* input, int64_t num_tokens, int d, int dtype, void* stream) {
+  using namespace b200;
+  if (num_tokens == 0) return B200_OK;
+  B200_DISPATCH_FLOAT(dtype, "silu_and_mul", {
+    silu_and_mul_kernel<scalar_t><<<(unsigned)num_tokens, tok_threads(d, 1024), 0, (cudaStream_t)stream>>>(
+        (scalar_t*)out, (const scalar_t*)input, d);
+  });
+  B200_LAUNCH_CHECK("silu_and_mul");
+  return B200_OK;
+}
+
+extern "C" int b200_rotary_embedding(const int64_t* positions, void* query, void* key, int head_size,
+                                     const void* cos_sin_cache, int rot_dim, int is_neox, int64_t num_tokens,
+                                     int num_heads, int num_kv_heads, int64_t query_stride, int64_t key_stride,
+                                     int dtype, void* stream) {
+  using namespace b200;
+  if (num_tokens == 0) return B200_OK;
+  const int threads = tok_threads(num_heads * rot_dim / 2, 512);
+  B200_DISPATCH_FLOAT(dtype, "rotary_embedding", {
+    if (is_neox)
+      rotary_kernel<scalar_t, true><<<(unsigned)num_tokens, threads, 0, (cudaStream_t)stream>>>(
+          positions, (scalar_t*)query, (scalar_t*)key, (const scalar_t*)cos_sin_cache, rot_dim, query_stride,
+          key_stride, num_heads, num_kv_heads, head_size);
+    else
+      rotary_kernel<scalar_t, false><<<(unsigned)num_tokens, threads, 0, (cudaStream_t)stream>>>(
+          positions, (scalar_t*)query, (scalar_t*)key, (const scalar_t*)cos_sin_cache, rot_dim, query_stride,
+          key_stride, num_heads, num_kv_heads, head_size);
+  });
+  B200_LAUNCH_CHECK("rotary_embedding");
+  return B200_OK;
+}

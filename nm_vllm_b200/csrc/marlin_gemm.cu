@@ -1,0 +1,598 @@
+// Marlin-layout W4A16 / W8A16 GEMM for sm_100a:  C[M,N] = A[M,K] . (s (.) (Q - 2^(bits-1)))
+//
+// Replaces gptq_marlin_gemm / marlin_gemm of the reference (csrc/quantization/gptq_marlin/gptq_marlin.cu:410-1363
+// kernel, :1577-1731 launcher, :1735-1868 op; csrc/quantization/marlin/dense/marlin_cuda_kernel.cu).  The STORED
+// layouts are the reference's (qweight [K/16, N*16/pf] int32 in 16x64 mma-fragment order, scales permuted by
+// scale_perm / scale_perm_single); everything else is a different machine:
+//
+//   * swap-AB: the 128 weight rows (output channels) are the M=128 side of a tcgen05.mma, the skinny activation
+//     batch (padded to MPAD in {16,32,64,128,256}) is the N side.  Decode M=1..64 therefore fills the tensor core.
+//   * the dequantised weight operand never touches shared memory: packed int4 tiles arrive by 1-D bulk TMA
+//     (cp.async.bulk, 1 KB contiguous per 16(k) x 128(n) slab), 8 dequant warps expand them in registers
+//     (lop3 magic-number trick, exact zero-point subtraction, group scale in the activation dtype like the
+//     reference :270-278) and write them with tcgen05.st.16x128b.x2 straight into TMEM.  The Marlin fragment order
+//     (thread l holds k = {2q,2q+1,2q+8,2q+9}, n = c, c+8 with c = l/4, q = l%4) IS the register layout of that
+//     store shape, so no shuffle is needed and K stays in natural order in TMEM.
+//   * activations come by tensor-map TMA (128-byte swizzle, zero-filled rows beyond M) and are the B operand from
+//     shared memory; accumulators live in TMEM (double buffered), read back by 4 epilogue warps with tcgen05.ld.
+//   * work is split stream-K style: the (tile, 64-wide k-unit) space is cut into one contiguous range per CTA
+//     (grid = #SMs).  Tiles whose K range is shared by several CTAs are reduced deterministically: every
+//     contributor writes an fp32 partial to its own scratch slot, bumps the tile counter, and the last arriver adds
+//     the slots in CTA order (no float atomics, no spin locks; counters reset themselves -> CUDA-graph safe).
+//
+// Warp roles (512 threads): w0 TMA producer | w1 MMA issuer | w2 TMEM allocator | w3 idle | w4-11 dequant
+// (TMEM lane quarter = warp%4) | w12-15 epilogue (quarter = warp%4).
+#include "common.cuh"
+#include "ptx.cuh"
+#include "tma_host.cuh"
+
+namespace b200 {
+using namespace ptx;
+
+constexpr int kTileN = 128;
+constexpr int kUnitK = 64;
+constexpr int kGemmThreads = 512;
+constexpr int kNumDequantWarps = 8;
+constexpr int kNA = 4;        // TMEM ring of dequantised-weight stages
+constexpr int kAColsPerStage = kUnitK / 2;  // 32 columns of packed 16-bit pairs
+constexpr int kAccCol0 = kNA * kAColsPerStage;
+
+template <int MPAD, int BITS>
+struct GemmCfg {
+  static constexpr int W_STAGE_BYTES = kTileN * kUnitK * BITS / 8;  // 4096 (4-bit) / 8192 (8-bit)
+  static constexpr int W_ROW_BYTES = W_STAGE_BYTES / 4;             // one 16(k) x 128(n) slab
+  static constexpr int A_STAGE_BYTES = MPAD * 128;
+  static constexpr int STAGE_BYTES = W_STAGE_BYTES + A_STAGE_BYTES;
+  static constexpr int NSTAGES_RAW = (196 * 1024) / STAGE_BYTES;
+  static constexpr int NSTAGES = NSTAGES_RAW > 32 ? 32 : NSTAGES_RAW;
+  static constexpr int NACC = MPAD <= 128 ? 2 : 1;
+  static constexpr int TMEM_COLS = (kAccCol0 + NACC * MPAD <= 256) ? 256 : 512;
+  static constexpr int BAR_BYTES = (2 * NSTAGES + 2 * kNA + 4) * 8 + 16;
+  static constexpr int SMEM_BYTES = 1024 /*align slack*/ + NSTAGES * STAGE_BYTES + BAR_BYTES;
+};
+
+struct GemmArgs {
+  const uint8_t* B;      // packed weights
+  const void* scales;    // [num_groups, N]
+  void* C;               // [M, N]
+  float* scratch;        // [2 * grid][128 * MPAD] fp32 partial slots
+  int* counters;         // [tiles], zero between launches
+  int M, N, K;
+  int num_groups, group_size;  // group_size == K when channelwise
+  int n_tiles, m_chunks, KS;   // KS = K / 64
+  int total_units;
+};
+
+struct Partition {
+  int q, r;
+  __device__ __forceinline__ Partition(int total, int g) : q(total / g), r(total % g) {}
+  __device__ __forceinline__ int start(int b) const { return b * q + min(b, r); }
+  __device__ __forceinline__ int owner(int u) const {
+    const int big = r * (q + 1);
+    return u < big ? u / (q + 1) : r + (u - big) / q;
+  }
+};
+
+// ---- dequantisation ------------------------------------------------------------------------------------------
+// one packed int32 of the 4-bit Marlin layout -> 4 registers in tcgen05.st.16x128b.x2 order:
+//   o[0] = (n=c  , k=2q,2q+1)  o[1] = (n=c+8, k=2q,2q+1)  o[2] = (n=c  , k=2q+8,2q+9)  o[3] = (n=c+8, k=2q+8,2q+9)
+// nibble positions (marlin_perms.py:29 interleave [0,2,4,6,1,3,5,7]): p0,p4 -> o[0]; p1,p5 -> o[2]; p2,p6 -> o[1]; p3,p7 -> o[3]
+template <typename T>
+__device__ __forceinline__ void dequant4(uint32_t q, uint32_t (&o)[4]);
+
+template <>
+__device__ __forceinline__ void dequant4<__half>(uint32_t q, uint32_t (&o)[4]) {
+  // (q & 0x000f000f) | 0x64006400 = half2(1024 + nib); (q & 0x00f000f0) | 0x6400.. = half2(1024 + 16 nib)
+  constexpr uint32_t LO = 0x000f000f, HI = 0x00f000f0, EX = 0x64006400;
+  constexpr uint32_t SUB = 0x64086408;   // 1032 = 1024 + 8
+  constexpr uint32_t MUL = 0x2c002c00;   // 1/16
+  constexpr uint32_t ADD = 0xd480d480;   // -72 = -(1024/16 + 8)
+  uint32_t lo0, hi0, lo1, hi1;
+  asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(lo0) : "r"(q), "n"(LO), "n"(EX));
+  asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(hi0) : "r"(q), "n"(HI), "n"(EX));
+  q >>= 8;
+  asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(lo1) : "r"(q), "n"(LO), "n"(EX));
+  asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(hi1) : "r"(q), "n"(HI), "n"(EX));
+  __half2 a = __hsub2(*reinterpret_cast<__half2*>(&lo0), *reinterpret_cast<const __half2*>(&SUB));
+  __half2 b = __hsub2(*reinterpret_cast<__half2*>(&lo1), *reinterpret_cast<const __half2*>(&SUB));
+  __half2 c = __hfma2(*reinterpret_cast<__half2*>(&hi0), *reinterpret_cast<const __half2*>(&MUL),
+                      *reinterpret_cast<const __half2*>(&ADD));
+  __half2 d = __hfma2(*reinterpret_cast<__half2*>(&hi1), *reinterpret_cast<const __half2*>(&MUL),
+                      *reinterpret_cast<const __half2*>(&ADD));
+  o[0] = *reinterpret_cast<uint32_t*>(&a);
+  o[1] = *reinterpret_cast<uint32_t*>(&b);
+  o[2] = *reinterpret_cast<uint32_t*>(&c);
+  o[3] = *reinterpret_cast<uint32_t*>(&d);
+}
+
+template <>
+__device__ __forceinline__ void dequant4<__nv_bfloat16>(uint32_t q, uint32_t (&o)[4]) {
+  // bf16 has 7 mantissa bits: (nib | 0x4300) = 128 + nib exactly; each nibble pair needs its own shift
+  constexpr uint32_t MASK = 0x000f000f, EX = 0x43004300;
+  constexpr uint32_t ONE = 0x3f803f80;   // 1.0
+  constexpr uint32_t ADD = 0xc308c308;   // -136 = -(128 + 8)
+  uint32_t v[4];
+  asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(v[0]) : "r"(q), "n"(MASK), "n"(EX));  // p0,p4 -> o[0]
+  q >>= 4;
+  asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(v[2]) : "r"(q), "n"(MASK), "n"(EX));  // p1,p5 -> o[2]
+  q >>= 4;
+  asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(v[1]) : "r"(q), "n"(MASK), "n"(EX));  // p2,p6 -> o[1]
+  q >>= 4;
+  asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(v[3]) : "r"(q), "n"(MASK), "n"(EX));  // p3,p7 -> o[3]
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    __nv_bfloat162 t = __hfma2(*reinterpret_cast<__nv_bfloat162*>(&v[i]), *reinterpret_cast<const __nv_bfloat162*>(&ONE),
+                               *reinterpret_cast<const __nv_bfloat162*>(&ADD));
+    o[i] = *reinterpret_cast<uint32_t*>(&t);
+  }
+}
+
+// 8-bit: two int32 per fragment (half b = 0/1), byte order [k=2q, 2q+8, 2q+1, 2q+9] (marlin_perms.py:31)
+template <typename T>
+__device__ __forceinline__ void dequant8(uint32_t q0, uint32_t q1, uint32_t (&o)[4]);
+
+template <>
+__device__ __forceinline__ void dequant8<__half>(uint32_t q0, uint32_t q1, uint32_t (&o)[4]) {
+  constexpr uint32_t EX = 0x64646464;
+  constexpr uint32_t SUB = 0x64806480;  // 1152 = 1024 + 128
+  uint32_t t[4];
+  t[0] = __byte_perm(q0, EX, 0x4240);  // bytes 0,2 -> (k=2q, 2q+1), n = c
+  t[1] = __byte_perm(q1, EX, 0x4240);  //                             n = c + 8
+  t[2] = __byte_perm(q0, EX, 0x4341);  // bytes 1,3 -> (k=2q+8, 2q+9)
+  t[3] = __byte_perm(q1, EX, 0x4341);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    __half2 v = __hsub2(*reinterpret_cast<__half2*>(&t[i]), *reinterpret_cast<const __half2*>(&SUB));
+    o[i] = *reinterpret_cast<uint32_t*>(&v);
+  }
+}
+
+template <>
+__device__ __forceinline__ void dequant8<__nv_bfloat16>(uint32_t q0, uint32_t q1, uint32_t (&o)[4]) {
+  // through fp32: (0x4B000000 | byte) = 8388608 + byte exactly; subtract 8388736 = 8388608 + 128
+  constexpr uint32_t EX = 0x4B000000;
+  const float bias = 8388736.0f;
+  auto one = [&](uint32_t q, int sel_lo, int sel_hi) -> uint32_t {
+    float f0 = __uint_as_float(__byte_perm(q, EX, sel_lo)) - bias;
+    float f1 = __uint_as_float(__byte_perm(q, EX, sel_hi)) - bias;
+    __nv_bfloat162 v = __floats2bfloat162_rn(f0, f1);
+    return *reinterpret_cast<uint32_t*>(&v);
+  };
+  o[0] = one(q0, 0x7650, 0x7652);
+  o[1] = one(q1, 0x7650, 0x7652);
+  o[2] = one(q0, 0x7651, 0x7653);
+  o[3] = one(q1, 0x7651, 0x7653);
+}
+
+template <typename T> struct Pack2;
+template <> struct Pack2<__half> {
+  using type = __half2;
+  static __device__ __forceinline__ uint32_t mul(uint32_t v, uint32_t s) {
+    __half2 r = __hmul2(*reinterpret_cast<__half2*>(&v), *reinterpret_cast<__half2*>(&s));
+    return *reinterpret_cast<uint32_t*>(&r);
+  }
+  static __device__ __forceinline__ uint32_t bcast(uint16_t s) { return (uint32_t)s | ((uint32_t)s << 16); }
+  static constexpr uint32_t FMT = 0;  // F16
+};
+template <> struct Pack2<__nv_bfloat16> {
+  using type = __nv_bfloat162;
+  static __device__ __forceinline__ uint32_t mul(uint32_t v, uint32_t s) {
+    __nv_bfloat162 r = __hmul2(*reinterpret_cast<__nv_bfloat162*>(&v), *reinterpret_cast<__nv_bfloat162*>(&s));
+    return *reinterpret_cast<uint32_t*>(&r);
+  }
+  static __device__ __forceinline__ uint32_t bcast(uint16_t s) { return (uint32_t)s | ((uint32_t)s << 16); }
+  static constexpr uint32_t FMT = 1;  // BF16
+};
+
+// position of output column n (0..31 within a 32-chunk) in a scale row permuted by scale_perm_single
+// (gptq_marlin.py:34-38: perm[8 i + jj] = 2 i + {0,1,8,9,16,17,24,25}[jj])
+__device__ __forceinline__ int scale_single_pos(int n32) {
+  const int rem = n32 & 7;
+  return 8 * (rem >> 1) + 2 * (n32 >> 3) + (rem & 1);
+}
+
+// ---- the kernel --------------------------------------------------------------------------------------------------
+template <typename T, int MPAD, int BITS>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const GemmArgs args) {
+  using Cfg = GemmCfg<MPAD, BITS>;
+  constexpr int NS = Cfg::NSTAGES;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  // layout: [activation stages (1024-aligned)] [weight stages] [barriers]
+  const uint32_t act_base = smem_base;
+  const uint32_t w_base = act_base + NS * Cfg::A_STAGE_BYTES;
+  const uint32_t bar_base = w_base + NS * Cfg::W_STAGE_BYTES;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (NS + s); };
+  auto afull_bar = [&](int s) { return bar_base + 8u * (2 * NS + s); };
+  auto aempty_bar = [&](int s) { return bar_base + 8u * (2 * NS + kNA + s); };
+  auto accfull_bar = [&](int s) { return bar_base + 8u * (2 * NS + 2 * kNA + s); };
+  auto accempty_bar = [&](int s) { return bar_base + 8u * (2 * NS + 2 * kNA + 2 + s); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * NS + 2 * kNA + 4);
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));  // generic pointer to the aligned base
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmap_a);
+    for (int s = 0; s < NS; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), kNumDequantWarps + 1);
+    }
+    for (int s = 0; s < kNA; ++s) {
+      mbar_init(afull_bar(s), kNumDequantWarps);
+      mbar_init(aempty_bar(s), 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(accfull_bar(s), 1);
+      mbar_init(accempty_bar(s), 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
+
+  const Partition part(args.total_units, gridDim.x);
+  const int u_begin = part.start(blockIdx.x), u_end = part.start(blockIdx.x + 1);
+  const int KS = args.KS;
+
+  if (warp == 0) {
+    // ================= TMA producer =================
+    if (lane == 0) {
+      const uint64_t pol_w = policy_evict_first();
+      int it = 0;
+      for (int u = u_begin; u < u_end;) {
+        const int tile = u / KS, ks0 = u % KS;
+        const int ks1 = min(KS, ks0 + (u_end - u));
+        const int nt = tile % args.n_tiles, mc = tile / args.n_tiles;
+        const int n0 = nt * kTileN;
+        const int n_valid = min(kTileN, args.N - n0);                       // 128 or 64
+        const uint32_t row_bytes = (uint32_t)(n_valid * 16 * BITS / 8);     // one k16 slab of this tile
+        const size_t row_pitch = (size_t)args.N * 16 * BITS / 8;            // bytes per k16 row of qweight
+        const uint8_t* wsrc = args.B + (size_t)n0 * 16 * BITS / 8;
+        for (int ks = ks0; ks < ks1; ++ks, ++it) {
+          const int s = it % NS;
+          const uint32_t ph = (it / NS) & 1;
+          mbar_wait(empty_bar(s), ph ^ 1);
+          mbar_arrive_expect_tx(full_bar(s), 4 * row_bytes + Cfg::A_STAGE_BYTES);
+          const uint32_t wdst = w_base + s * Cfg::W_STAGE_BYTES;
+#pragma unroll
+          for (int r = 0; r < 4; ++r)
+            bulk_g2s_hint(wdst + r * Cfg::W_ROW_BYTES, wsrc + (size_t)(ks * 4 + r) * row_pitch, row_bytes, full_bar(s), pol_w);
+          tma_2d_g2s(act_base + s * Cfg::A_STAGE_BYTES, &tmap_a, ks * kUnitK, mc * MPAD, full_bar(s));
+        }
+        u += ks1 - ks0;
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(1 /*F32*/, Pack2<T>::FMT, Pack2<T>::FMT, 128, MPAD);
+      int it = 0, seg = 0;
+      for (int u = u_begin; u < u_end; ++seg) {
+        const int ks0 = u % KS;
+        const int ks1 = min(KS, ks0 + (u_end - u));
+        const int ab = seg % Cfg::NACC;
+        const uint32_t accph = (seg / Cfg::NACC) & 1;
+        mbar_wait(accempty_bar(ab), accph ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + kAccCol0 + ab * MPAD;
+        for (int ks = ks0; ks < ks1; ++ks, ++it) {
+          const int s = it % NS, sa = it % kNA;
+          mbar_wait(full_bar(s), (it / NS) & 1);
+          mbar_wait(afull_bar(sa), (it / kNA) & 1);
+          tc_fence_after();
+          const uint32_t a_tmem = tmem_base + sa * kAColsPerStage;
+          const uint32_t b_smem = act_base + s * Cfg::A_STAGE_BYTES;
+#pragma unroll
+          for (int r = 0; r < 4; ++r)
+            mma_f16_ts(d_tmem, a_tmem + r * 8, make_kmajor_sw128_desc(b_smem + r * 32), idesc, (ks > ks0 || r > 0) ? 1u : 0u);
+          tc_commit(aempty_bar(sa));
+          tc_commit(empty_bar(s));
+        }
+        tc_commit(accfull_bar(ab));
+        u += ks1 - ks0;
+      }
+    }
+  } else if (warp >= 4 && warp < 4 + kNumDequantWarps) {
+    // ================= dequant warps: smem (packed) -> registers -> TMEM =================
+    const int qd = warp & 3;          // TMEM lane quarter: rows 32 qd .. 32 qd + 31 of the tile
+    const int half_k = (warp - 4) >> 2;  // which pair of k16 slabs of the unit
+    const int t64 = qd >> 1, jpair = qd & 1;
+    const int c = lane >> 2;
+    const bool grouped = args.num_groups > 1;
+    const uint16_t* sc = reinterpret_cast<const uint16_t*>(args.scales);
+    int it = 0;
+    int cur_g = -1, cur_tile = -1;
+    uint32_t s2[4] = {0, 0, 0, 0};  // broadcast scales for (jj, b): index 2 jj + b
+    for (int u = u_begin; u < u_end;) {
+      const int tile = u / KS, ks0 = u % KS;
+      const int ks1 = min(KS, ks0 + (u_end - u));
+      const int nt = tile % args.n_tiles;
+      const int n0 = nt * kTileN;
+      if (tile != cur_tile) { cur_tile = tile; cur_g = -1; }
+      for (int ks = ks0; ks < ks1; ++ks, ++it) {
+        const int s = it % NS, sa = it % kNA;
+        if (grouped) {
+          const int g = (ks * kUnitK + half_k * 32) / args.group_size;  // both slabs of this warp share a group (gs >= 32)
+          if (g != cur_g) {
+            cur_g = g;
+            // scale_perm (gptq_marlin.py:30-33): position 8 c + b' holds column c + 8 b' of the 64-chunk
+            const int ncol = n0 + 64 * t64;
+            if (ncol < args.N) {
+              const uint2 raw = *reinterpret_cast<const uint2*>(sc + (size_t)g * args.N + ncol + 8 * c + 4 * jpair);
+              s2[0] = Pack2<T>::bcast((uint16_t)(raw.x & 0xffff));
+              s2[1] = Pack2<T>::bcast((uint16_t)(raw.x >> 16));
+              s2[2] = Pack2<T>::bcast((uint16_t)(raw.y & 0xffff));
+              s2[3] = Pack2<T>::bcast((uint16_t)(raw.y >> 16));
+            }
+          }
+        }
+        mbar_wait(full_bar(s), (it / NS) & 1);
+        // packed words of this thread: slab r, 64-chunk t64, fragment lane, n16-tiles (2 jpair, 2 jpair + 1)
+        uint32_t w[2][BITS == 4 ? 2 : 4];
+#pragma unroll
+        for (int rr = 0; rr < 2; ++rr) {
+          const int r = half_k * 2 + rr;
+          if (BITS == 4) {
+            const uint2 v = *reinterpret_cast<const uint2*>(smem_gen + (w_base - smem_base) + s * Cfg::W_STAGE_BYTES +
+                                                            r * Cfg::W_ROW_BYTES + t64 * 512 + lane * 16 + jpair * 8);
+            w[rr][0] = v.x; w[rr][1] = v.y;
+          } else {
+            const uint4 v = *reinterpret_cast<const uint4*>(smem_gen + (w_base - smem_base) + s * Cfg::W_STAGE_BYTES +
+                                                            r * Cfg::W_ROW_BYTES + t64 * 1024 + lane * 32 + jpair * 16);
+            w[rr][0] = v.x; w[rr][1] = v.y; w[rr][2] = v.z; w[rr][3] = v.w;
+          }
+        }
+        mbar_wait(aempty_bar(sa), ((it / kNA) & 1) ^ 1);
+        tc_fence_after();
+#pragma unroll
+        for (int rr = 0; rr < 2; ++rr) {
+          const int r = half_k * 2 + rr;
+#pragma unroll
+          for (int jj = 0; jj < 2; ++jj) {
+            uint32_t o[4];
+            if (BITS == 4) dequant4<T>(w[rr][jj], o);
+            else dequant8<T>(w[rr][2 * jj], w[rr][2 * jj + 1], o);
+            if (grouped) {
+              o[0] = Pack2<T>::mul(o[0], s2[2 * jj]);
+              o[1] = Pack2<T>::mul(o[1], s2[2 * jj + 1]);
+              o[2] = Pack2<T>::mul(o[2], s2[2 * jj]);
+              o[3] = Pack2<T>::mul(o[3], s2[2 * jj + 1]);
+            }
+            const uint32_t taddr = tmem_base + ((uint32_t)(32 * qd + 16 * jj) << 16) + sa * kAColsPerStage + r * 8;
+            tmem_st_16x128b_x2(taddr, o[0], o[1], o[2], o[3]);
+          }
+        }
+        // smem slot consumed (values are in registers and have been used)
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty_bar(s));
+        tc_wait_st();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(afull_bar(sa));
+      }
+      u += ks1 - ks0;
+    }
+  } else if (warp >= 12) {
+    // ================= epilogue: TMEM -> registers -> global (direct, or split-K partial + last-arriver reduce) ==
+    const int qd = warp & 3;
+    const int row = 32 * qd + lane;  // output channel within the tile == TMEM lane
+    const int et = threadIdx.x - 12 * 32;  // 0..127
+    __shared__ int s_last;
+    const bool grouped = args.num_groups > 1;
+    int seg = 0;
+    for (int u = u_begin; u < u_end; ++seg) {
+      const int tile = u / KS, ks0 = u % KS;
+      const int ks1 = min(KS, ks0 + (u_end - u));
+      const int nt = tile % args.n_tiles, mc = tile / args.n_tiles;
+      const int n = nt * kTileN + row;
+      const int m0 = mc * MPAD;
+      const int m_valid = min(MPAD, args.M - m0);
+      const bool n_ok = n < args.N;
+      const int ab = seg % Cfg::NACC;
+      const uint32_t accph = (seg / Cfg::NACC) & 1;
+      const bool full_k = (ks0 == 0 && ks1 == KS);
+      float ch_scale = 1.f;
+      if (!grouped && n_ok) {
+        const int n32 = n & 31;
+        ch_scale = to_f32<T>(reinterpret_cast<const T*>(args.scales)[(n & ~31) + scale_single_pos(n32)]);
+      }
+      // slot of this segment: 0 when it is the CTA's first segment, else 1
+      const int my_slot = 2 * blockIdx.x + ((u == u_begin) ? 0 : 1);
+      float* part_dst = args.scratch + (size_t)my_slot * (kTileN * MPAD);
+      T* cdst = reinterpret_cast<T*>(args.C) + (size_t)m0 * args.N + n;
+
+      mbar_wait(accfull_bar(ab), accph);
+      tc_fence_after();
+      const uint32_t acc_addr = tmem_base + ((uint32_t)(32 * qd) << 16) + kAccCol0 + ab * MPAD;
+#pragma unroll 1
+      for (int j0 = 0; j0 < MPAD; j0 += 16) {
+        uint32_t v[16];
+        tmem_ld_32x32b_x16(acc_addr + j0, v);
+        tc_wait_ld();
+        if (full_k) {
+          if (n_ok) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (j0 + j < m_valid) cdst[(size_t)(j0 + j) * args.N] = from_f32<T>(__uint_as_float(v[j]) * ch_scale);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            if (j0 + j < m_valid) part_dst[(j0 + j) * kTileN + row] = __uint_as_float(v[j]);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(accempty_bar(ab));
+
+      if (!full_k) {
+        // contributors of this tile are the CTAs whose unit ranges intersect [tile*KS, (tile+1)*KS)
+        const int b_first = part.owner(tile * KS), b_last = part.owner(tile * KS + KS - 1);
+        const int nseg = b_last - b_first + 1;
+        __threadfence();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (et == 0) {
+          const int old = atomicAdd(&args.counters[tile], 1);
+          s_last = (old == nseg - 1);
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (s_last) {
+          __threadfence();
+          if (n_ok) {
+#pragma unroll 1
+            for (int j0 = 0; j0 < m_valid; j0 += 8) {
+              float acc[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+              for (int b = b_first; b <= b_last; ++b) {
+                const int slot = 2 * b + ((part.start(b) / KS == tile) ? 0 : 1);
+                const float* src = args.scratch + (size_t)slot * (kTileN * MPAD) + row;
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                  if (j0 + j < m_valid) acc[j] += __ldcg(src + (j0 + j) * kTileN);
+              }
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                if (j0 + j < m_valid) cdst[(size_t)(j0 + j) * args.N] = from_f32<T>(acc[j] * ch_scale);
+            }
+          }
+          if (et == 0) args.counters[tile] = 0;  // self-reset: the next launch starts from zero
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");  // s_last is reused by the next segment
+      }
+      u += ks1 - ks0;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+}
+
+// ---- host side -------------------------------------------------------------------------------------------------------
+struct DeviceScratch {
+  float* partials = nullptr;
+  int* counters = nullptr;
+  size_t partial_floats = 0;
+  int counter_ints = 0;
+};
+static DeviceScratch g_scratch[64];
+
+static int ensure_scratch(int dev, size_t partial_floats, int counter_ints, cudaStream_t st) {
+  DeviceScratch& s = g_scratch[dev];
+  if (s.partials && s.partial_floats >= partial_floats && s.counter_ints >= counter_ints) return B200_OK;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(st, &cap);
+  if (cap != cudaStreamCaptureStatusNone)
+    return set_error(B200_EINVAL,
+                     "marlin gemm: split-K scratch must be reserved before CUDA-graph capture "
+                     "(run one eager call or b200_gemm_scratch_reserve first)");
+  // grow generously once: worst case MPAD = 256
+  if (partial_floats < (size_t)2 * 256 * kTileN * 256) partial_floats = (size_t)2 * 256 * kTileN * 256;
+  if (counter_ints < 1 << 16) counter_ints = 1 << 16;
+  cudaDeviceSynchronize();
+  if (s.partials) cudaFree(s.partials);
+  if (s.counters) cudaFree(s.counters);
+  if (cudaMalloc(&s.partials, partial_floats * sizeof(float)) != cudaSuccess ||
+      cudaMalloc(&s.counters, counter_ints * sizeof(int)) != cudaSuccess)
+    return set_error(B200_ECUDA, "marlin gemm: scratch allocation failed");
+  cudaMemset(s.counters, 0, counter_ints * sizeof(int));
+  cudaDeviceSynchronize();
+  s.partial_floats = partial_floats;
+  s.counter_ints = counter_ints;
+  return B200_OK;
+}
+
+template <typename T, int MPAD, int BITS>
+static int launch_gemm(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t st) {
+  using Cfg = GemmCfg<MPAD, BITS>;
+  GemmArgs a = a_in;
+  a.m_chunks = (a.M + MPAD - 1) / MPAD;
+  const int tiles = a.n_tiles * a.m_chunks;
+  a.total_units = tiles * a.KS;
+  int grid = num_sms();
+  if (grid > a.total_units) grid = a.total_units;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (int e = ensure_scratch(dev, (size_t)2 * grid * kTileN * MPAD, tiles, st)) return e;
+  a.scratch = g_scratch[dev].partials;
+  a.counters = g_scratch[dev].counters;
+  CUtensorMap tmap;
+  const CUtensorMapDataType dt = std::is_same<T, __half>::value ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  if (!make_tmap_2d(&tmap, A, dt, 2, (uint64_t)a.M, (uint64_t)a.K, (uint64_t)lda * 2, MPAD, kUnitK))
+    return set_error(B200_ECUDA, "marlin gemm: cuTensorMapEncodeTiled failed (A=%p M=%d K=%d lda=%lld)", A, a.M, a.K, (long long)lda);
+  auto kern = marlin_gemm_kernel<T, MPAD, BITS>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    attr_set = true;
+  }
+  kern<<<grid, kGemmThreads, Cfg::SMEM_BYTES, st>>>(tmap, a);
+  return B200_OK;
+}
+
+template <typename T, int BITS>
+static int dispatch_mpad(const GemmArgs& a, const void* A, int64_t lda, cudaStream_t st) {
+  if (a.M <= 16) return launch_gemm<T, 16, BITS>(a, A, lda, st);
+  if (a.M <= 32) return launch_gemm<T, 32, BITS>(a, A, lda, st);
+  if (a.M <= 64) return launch_gemm<T, 64, BITS>(a, A, lda, st);
+  if (a.M <= 128) return launch_gemm<T, 128, BITS>(a, A, lda, st);
+  return launch_gemm<T, 256, BITS>(a, A, lda, st);
+}
+
+}  // namespace b200
+
+extern "C" int b200_gemm_scratch_reserve(int64_t max_m, int64_t max_n) {
+  (void)max_m; (void)max_n;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return b200::ensure_scratch(dev, 1, 1, 0);
+}
+
+extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_weight, const void* b_scales,
+                                     const int32_t* g_idx, const int32_t* perm, int32_t* workspace,
+                                     int64_t workspace_numel, int num_bits, int64_t size_m, int64_t size_n,
+                                     int64_t size_k, int64_t lda, int num_groups, int is_k_full, int dtype,
+                                     void* stream) {
+  using namespace b200;
+  (void)workspace; (void)is_k_full;
+  B200_CHECK(num_bits == 4 || num_bits == 8, "num_bits must be 4 or 8. Got = %d", num_bits);
+  B200_CHECK(dtype == B200_F16 || dtype == B200_BF16, "gpt_marlin_gemm only supports bfloat16 and float16");
+  B200_CHECK(size_n % 64 == 0, "size_n = %lld, is not divisible by min_thread_n = 64", (long long)size_n);
+  B200_CHECK(size_k % 128 == 0, "size_k = %lld is not divisible by 128 (gptq_marlin.py:21 min_thread_k)", (long long)size_k);
+  B200_CHECK(workspace_numel >= (size_n / 64) * 16, "workspace.numel = %lld is below min_workspace_size = %lld",
+             (long long)workspace_numel, (long long)((size_n / 64) * 16));
+  B200_CHECK(num_groups >= 1 && size_k % num_groups == 0, "size_k = %lld, is not divisible by b_scales.size(0) = %d",
+             (long long)size_k, num_groups);
+  B200_CHECK((reinterpret_cast<uintptr_t>(a) & 15) == 0 && (lda * 2) % 16 == 0, "A must be 16-byte aligned with a 16-byte multiple row pitch");
+  if (g_idx != nullptr || perm != nullptr)
+    return set_error(B200_ENOTSUP, "gptq_marlin_gemm: act-order (g_idx/perm) is not covered by the sm_100a kernel yet");
+  if (size_m == 0 || size_n == 0) return B200_OK;
+  const int gs = (int)(size_k / num_groups);
+  if (num_groups > 1) B200_CHECK(gs == 32 || gs == 64 || gs == 128, "Unexpected group_size = %d", gs);
+  GemmArgs ga;
+  ga.B = reinterpret_cast<const uint8_t*>(b_q_weight);
+  ga.scales = b_scales;
+  ga.C = c;
+  ga.scratch = nullptr;
+  ga.counters = nullptr;
+  ga.M = (int)size_m; ga.N = (int)size_n; ga.K = (int)size_k;
+  ga.num_groups = num_groups; ga.group_size = gs;
+  ga.n_tiles = (int)((size_n + kTileN - 1) / kTileN);
+  ga.m_chunks = 1;
+  ga.KS = (int)(size_k / kUnitK);
+  ga.total_units = 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc;
+  if (dtype == B200_F16) rc = (num_bits == 4) ? dispatch_mpad<__half, 4>(ga, a, lda, st) : dispatch_mpad<__half, 8>(ga, a, lda, st);
+  else rc = (num_bits == 4) ? dispatch_mpad<__nv_bfloat16, 4>(ga, a, lda, st) : dispatch_mpad<__nv_bfloat16, 8>(ga, a, lda, st);
+  if (rc) return rc;
+  B200_LAUNCH_CHECK("gptq_marlin_gemm");
+  return B200_OK;
+}
