@@ -25,30 +25,38 @@
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tma_host.cuh"
+#include <stdlib.h>
 
 namespace b200 {
 using namespace ptx;
 
 constexpr int kTileN = 128;
-constexpr int kUnitK = 64;
-constexpr int kGemmThreads = 512;
-constexpr int kNumDequantWarps = 8;
-constexpr int kNA = 4;        // TMEM ring of dequantised-weight stages
-constexpr int kAColsPerStage = kUnitK / 2;  // 32 columns of packed 16-bit pairs
-constexpr int kAccCol0 = kNA * kAColsPerStage;
+constexpr int kUnitK = 128;                 // one pipeline stage / scheduling unit = 128 (k) x 128 (n) weights
+constexpr int kSlabs = kUnitK / 16;         // 16-row k slabs per unit
+constexpr int kGemmThreads = 768;
+constexpr int kDequantWarp0 = 4;
+constexpr int kNumDequantWarps = 16;        // 4 per TMEM lane quarter; warp j of a quarter owns units it % 4 == j
+constexpr int kEpiWarp0 = kDequantWarp0 + kNumDequantWarps;  // 20..23 (warp % 4 == quarter)
+constexpr int kNA = 4;                      // TMEM ring of dequantised-weight stages (one per dequant warp of a quarter)
+constexpr int kAColsPerStage = kUnitK / 2;  // 64 columns of packed 16-bit pairs
+constexpr int kAccCol0 = kNA * kAColsPerStage;  // 256
 
 template <int MPAD, int BITS>
 struct GemmCfg {
-  static constexpr int W_STAGE_BYTES = kTileN * kUnitK * BITS / 8;  // 4096 (4-bit) / 8192 (8-bit)
-  static constexpr int W_ROW_BYTES = W_STAGE_BYTES / 4;             // one 16(k) x 128(n) slab
-  static constexpr int A_STAGE_BYTES = MPAD * 128;
-  static constexpr int STAGE_BYTES = W_STAGE_BYTES + A_STAGE_BYTES;
-  static constexpr int NSTAGES_RAW = (196 * 1024) / STAGE_BYTES;
-  static constexpr int NSTAGES = NSTAGES_RAW > 32 ? 32 : NSTAGES_RAW;
+  static constexpr int W_ROW_BYTES = kTileN * 16 * BITS / 8;         // one 16(k) x 128(n) slab: 1024 (4-bit) / 2048 (8-bit)
+  static constexpr int W_STAGE_BYTES = kSlabs * W_ROW_BYTES;         // 8192 / 16384
+  static constexpr int A_BOX_BYTES = MPAD * 128;                     // one 64(k) x MPAD box, 128-byte swizzle
+  static constexpr int A_STAGE_BYTES = 2 * A_BOX_BYTES;
+  static constexpr int S_STAGE_BYTES = 1024;                         // up to four 128-column scale slabs (group 32)
+  static constexpr int STAGE_BYTES = W_STAGE_BYTES + A_STAGE_BYTES + S_STAGE_BYTES;
+  static constexpr int NSTAGES_RAW = (200 * 1024) / STAGE_BYTES;
+  static constexpr int NSTAGES = NSTAGES_RAW > 16 ? 16 : NSTAGES_RAW;
   static constexpr int NACC = MPAD <= 128 ? 2 : 1;
-  static constexpr int TMEM_COLS = (kAccCol0 + NACC * MPAD <= 256) ? 256 : 512;
+  static constexpr int TMEM_COLS = 512;
   static constexpr int BAR_BYTES = (2 * NSTAGES + 2 * kNA + 4) * 8 + 16;
   static constexpr int SMEM_BYTES = 1024 /*align slack*/ + NSTAGES * STAGE_BYTES + BAR_BYTES;
+  static_assert(NSTAGES >= 2, "pipeline needs at least two stages");
+  static_assert(kAccCol0 + NACC * MPAD <= 512, "TMEM budget");
 };
 
 struct GemmArgs {
@@ -59,8 +67,10 @@ struct GemmArgs {
   int* counters;         // [tiles], zero between launches
   int M, N, K;
   int num_groups, group_size;  // group_size == K when channelwise
-  int n_tiles, m_chunks, KS;   // KS = K / 64
+  int n_tiles, m_chunks, KS;   // KS = K / kUnitK
   int total_units;
+  int groups_per_unit;         // scale rows staged per unit: 0 (channelwise), 1, 2 or 4
+  int dbg;                     // bring-up switches (B200_GEMM_DBG), 0 in production
 };
 
 struct Partition {
@@ -194,15 +204,17 @@ __device__ __forceinline__ int scale_single_pos(int n32) {
 // ---- the kernel --------------------------------------------------------------------------------------------------
 template <typename T, int MPAD, int BITS>
 __global__ void __launch_bounds__(kGemmThreads, 1)
-marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const GemmArgs args) {
+marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
+                   const __grid_constant__ CUtensorMap tmap_s, const GemmArgs args) {
   using Cfg = GemmCfg<MPAD, BITS>;
   constexpr int NS = Cfg::NSTAGES;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  // layout: [activation stages (1024-aligned)] [weight stages] [barriers]
+  // layout: [activation stages (1024-aligned)] [weight stages] [scale stages] [barriers]
   const uint32_t act_base = smem_base;
   const uint32_t w_base = act_base + NS * Cfg::A_STAGE_BYTES;
-  const uint32_t bar_base = w_base + NS * Cfg::W_STAGE_BYTES;
+  const uint32_t sc_base = w_base + NS * Cfg::W_STAGE_BYTES;
+  const uint32_t bar_base = sc_base + NS * Cfg::S_STAGE_BYTES;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (NS + s); };
   auto afull_bar = [&](int s) { return bar_base + 8u * (2 * NS + s); };
@@ -216,12 +228,14 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const GemmArgs ar
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_a);
+    prefetch_tmap(&tmap_w);
+    prefetch_tmap(&tmap_s);
     for (int s = 0; s < NS; ++s) {
       mbar_init(full_bar(s), 1);
-      mbar_init(empty_bar(s), kNumDequantWarps + 1);
+      mbar_init(empty_bar(s), 4 + 1);   // one dequant warp per quarter + the MMA commit
     }
     for (int s = 0; s < kNA; ++s) {
-      mbar_init(afull_bar(s), kNumDequantWarps);
+      mbar_init(afull_bar(s), 4);
       mbar_init(aempty_bar(s), 1);
     }
     for (int s = 0; s < 2; ++s) {
@@ -239,31 +253,31 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const GemmArgs ar
   const Partition part(args.total_units, gridDim.x);
   const int u_begin = part.start(blockIdx.x), u_end = part.start(blockIdx.x + 1);
   const int KS = args.KS;
+  const int gpu_ = args.groups_per_unit;
 
-  if (warp == 0) {
-    // ================= TMA producer =================
+  if (warp == 0 || (warp == 3 && (args.dbg & 2))) {
+    // ================= TMA producer: 4 tensor copies per 128 x 128 unit =================
+    const int pstride = (args.dbg & 2) ? 2 : 1, pfirst = (warp == 3) ? 1 : 0;
     if (lane == 0) {
-      const uint64_t pol_w = policy_evict_first();
+      const uint64_t pol_w = policy_evict_first();   // weights are streamed exactly once
+      const uint64_t pol_a = policy_evict_last();    // activations / scales are re-read by every CTA
+      const uint32_t tx = Cfg::W_STAGE_BYTES + Cfg::A_STAGE_BYTES + (uint32_t)gpu_ * 256u;
       int it = 0;
       for (int u = u_begin; u < u_end;) {
-        const int tile = u / KS, ks0 = u % KS;
+        const int tile = u / KS, ks0 = u - tile * KS;
         const int ks1 = min(KS, ks0 + (u_end - u));
         const int nt = tile % args.n_tiles, mc = tile / args.n_tiles;
-        const int n0 = nt * kTileN;
-        const int n_valid = min(kTileN, args.N - n0);                       // 128 or 64
-        const uint32_t row_bytes = (uint32_t)(n_valid * 16 * BITS / 8);     // one k16 slab of this tile
-        const size_t row_pitch = (size_t)args.N * 16 * BITS / 8;            // bytes per k16 row of qweight
-        const uint8_t* wsrc = args.B + (size_t)n0 * 16 * BITS / 8;
+        const int wcol = nt * (Cfg::W_ROW_BYTES / 8);  // tensor-map column in 8-byte elements
         for (int ks = ks0; ks < ks1; ++ks, ++it) {
           const int s = it % NS;
-          const uint32_t ph = (it / NS) & 1;
-          mbar_wait(empty_bar(s), ph ^ 1);
-          mbar_arrive_expect_tx(full_bar(s), 4 * row_bytes + Cfg::A_STAGE_BYTES);
-          const uint32_t wdst = w_base + s * Cfg::W_STAGE_BYTES;
-#pragma unroll
-          for (int r = 0; r < 4; ++r)
-            bulk_g2s_hint(wdst + r * Cfg::W_ROW_BYTES, wsrc + (size_t)(ks * 4 + r) * row_pitch, row_bytes, full_bar(s), pol_w);
-          tma_2d_g2s(act_base + s * Cfg::A_STAGE_BYTES, &tmap_a, ks * kUnitK, mc * MPAD, full_bar(s));
+          if ((it % pstride) != pfirst) continue;
+          mbar_wait(empty_bar(s), ((it / NS) & 1) ^ 1);
+          mbar_arrive_expect_tx(full_bar(s), tx);
+          tma_2d_g2s_hint(w_base + s * Cfg::W_STAGE_BYTES, &tmap_w, wcol, ks * kSlabs, full_bar(s), pol_w);
+          tma_2d_g2s_hint(act_base + s * Cfg::A_STAGE_BYTES, &tmap_a, ks * kUnitK, mc * MPAD, full_bar(s), pol_a);
+          tma_2d_g2s_hint(act_base + s * Cfg::A_STAGE_BYTES + Cfg::A_BOX_BYTES, &tmap_a, ks * kUnitK + 64, mc * MPAD,
+                          full_bar(s), pol_a);
+          if (gpu_) tma_2d_g2s_hint(sc_base + s * Cfg::S_STAGE_BYTES, &tmap_s, nt * kTileN, ks * gpu_, full_bar(s), pol_a);
         }
         u += ks1 - ks0;
       }
@@ -277,8 +291,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const GemmArgs ar
         const int ks0 = u % KS;
         const int ks1 = min(KS, ks0 + (u_end - u));
         const int ab = seg % Cfg::NACC;
-        const uint32_t accph = (seg / Cfg::NACC) & 1;
-        mbar_wait(accempty_bar(ab), accph ^ 1);
+        mbar_wait(accempty_bar(ab), ((seg / Cfg::NACC) & 1) ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + kAccCol0 + ab * MPAD;
         for (int ks = ks0; ks < ks1; ++ks, ++it) {
@@ -289,8 +302,10 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const GemmArgs ar
           const uint32_t a_tmem = tmem_base + sa * kAColsPerStage;
           const uint32_t b_smem = act_base + s * Cfg::A_STAGE_BYTES;
 #pragma unroll
-          for (int r = 0; r < 4; ++r)
-            mma_f16_ts(d_tmem, a_tmem + r * 8, make_kmajor_sw128_desc(b_smem + r * 32), idesc, (ks > ks0 || r > 0) ? 1u : 0u);
+          for (int r = 0; r < kSlabs; ++r)
+            if (!(args.dbg & 1) || r == 0)
+            mma_f16_ts(d_tmem, a_tmem + r * 8, make_kmajor_sw128_desc(b_smem + (r >> 2) * Cfg::A_BOX_BYTES + (r & 3) * 32),
+                       idesc, (ks > ks0 || r > 0) ? 1u : 0u);
           tc_commit(aempty_bar(sa));
           tc_commit(empty_bar(s));
         }
@@ -298,96 +313,83 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const GemmArgs ar
         u += ks1 - ks0;
       }
     }
-  } else if (warp >= 4 && warp < 4 + kNumDequantWarps) {
+  } else if (warp >= kDequantWarp0 && warp < kEpiWarp0) {
     // ================= dequant warps: smem (packed) -> registers -> TMEM =================
-    const int qd = warp & 3;          // TMEM lane quarter: rows 32 qd .. 32 qd + 31 of the tile
-    const int half_k = (warp - 4) >> 2;  // which pair of k16 slabs of the unit
+    const int qd = warp & 3;                      // TMEM lane quarter: rows 32 qd .. 32 qd + 31 of the tile
+    const int own = (warp - kDequantWarp0) >> 2;  // this warp handles units with it % 4 == own (TMEM stage `own`)
     const int t64 = qd >> 1, jpair = qd & 1;
     const int c = lane >> 2;
-    const bool grouped = args.num_groups > 1;
-    const uint16_t* sc = reinterpret_cast<const uint16_t*>(args.scales);
-    int it = 0;
-    int cur_g = -1, cur_tile = -1;
-    uint32_t s2[4] = {0, 0, 0, 0};  // broadcast scales for (jj, b): index 2 jj + b
-    for (int u = u_begin; u < u_end;) {
-      const int tile = u / KS, ks0 = u % KS;
-      const int ks1 = min(KS, ks0 + (u_end - u));
-      const int nt = tile % args.n_tiles;
-      const int n0 = nt * kTileN;
-      if (tile != cur_tile) { cur_tile = tile; cur_g = -1; }
-      for (int ks = ks0; ks < ks1; ++ks, ++it) {
-        const int s = it % NS, sa = it % kNA;
-        if (grouped) {
-          const int g = (ks * kUnitK + half_k * 32) / args.group_size;  // both slabs of this warp share a group (gs >= 32)
-          if (g != cur_g) {
-            cur_g = g;
-            // scale_perm (gptq_marlin.py:30-33): position 8 c + b' holds column c + 8 b' of the 64-chunk
-            const int ncol = n0 + 64 * t64;
-            if (ncol < args.N) {
-              const uint2 raw = *reinterpret_cast<const uint2*>(sc + (size_t)g * args.N + ncol + 8 * c + 4 * jpair);
-              s2[0] = Pack2<T>::bcast((uint16_t)(raw.x & 0xffff));
-              s2[1] = Pack2<T>::bcast((uint16_t)(raw.x >> 16));
-              s2[2] = Pack2<T>::bcast((uint16_t)(raw.y & 0xffff));
-              s2[3] = Pack2<T>::bcast((uint16_t)(raw.y >> 16));
-            }
-          }
-        }
-        mbar_wait(full_bar(s), (it / NS) & 1);
-        // packed words of this thread: slab r, 64-chunk t64, fragment lane, n16-tiles (2 jpair, 2 jpair + 1)
-        uint32_t w[2][BITS == 4 ? 2 : 4];
+    const bool grouped = gpu_ > 0;
+    const int slabs_per_group = grouped ? (kSlabs / gpu_) : kSlabs;  // k16 slabs sharing one scale row
+    const uint32_t a_col = tmem_base + ((uint32_t)(32 * qd) << 16) + own * kAColsPerStage;
+    const uint8_t* wsm = smem_gen + (w_base - smem_base) + t64 * (Cfg::W_ROW_BYTES / 2) + lane * (4 * BITS) + jpair * (2 * BITS);
+    const uint8_t* ssm = smem_gen + (sc_base - smem_base) + (64 * t64 + 8 * c + 4 * jpair) * 2;
+    const int n_units = u_end - u_begin;
+    for (int it = own; it < n_units; it += kNA) {
+      const int s = it % NS;
+      mbar_wait(full_bar(s), (it / NS) & 1);
+      // packed words of this thread for all 8 slabs: 64-chunk t64, fragment lane, n16-tiles (2 jpair, 2 jpair + 1)
+      uint32_t w[kSlabs][BITS == 4 ? 2 : 4];
 #pragma unroll
-        for (int rr = 0; rr < 2; ++rr) {
-          const int r = half_k * 2 + rr;
-          if (BITS == 4) {
-            const uint2 v = *reinterpret_cast<const uint2*>(smem_gen + (w_base - smem_base) + s * Cfg::W_STAGE_BYTES +
-                                                            r * Cfg::W_ROW_BYTES + t64 * 512 + lane * 16 + jpair * 8);
-            w[rr][0] = v.x; w[rr][1] = v.y;
-          } else {
-            const uint4 v = *reinterpret_cast<const uint4*>(smem_gen + (w_base - smem_base) + s * Cfg::W_STAGE_BYTES +
-                                                            r * Cfg::W_ROW_BYTES + t64 * 1024 + lane * 32 + jpair * 16);
-            w[rr][0] = v.x; w[rr][1] = v.y; w[rr][2] = v.z; w[rr][3] = v.w;
-          }
+      for (int r = 0; r < kSlabs; ++r) {
+        if (BITS == 4) {
+          const uint2 v = *reinterpret_cast<const uint2*>(wsm + s * Cfg::W_STAGE_BYTES + r * Cfg::W_ROW_BYTES);
+          w[r][0] = v.x; w[r][1] = v.y;
+        } else {
+          const uint4 v = *reinterpret_cast<const uint4*>(wsm + s * Cfg::W_STAGE_BYTES + r * Cfg::W_ROW_BYTES);
+          w[r][0] = v.x; w[r][1] = v.y; w[r][2] = v.z; w[r][3] = v.w;
         }
-        mbar_wait(aempty_bar(sa), ((it / kNA) & 1) ^ 1);
-        tc_fence_after();
-#pragma unroll
-        for (int rr = 0; rr < 2; ++rr) {
-          const int r = half_k * 2 + rr;
-#pragma unroll
-          for (int jj = 0; jj < 2; ++jj) {
-            uint32_t o[4];
-            if (BITS == 4) dequant4<T>(w[rr][jj], o);
-            else dequant8<T>(w[rr][2 * jj], w[rr][2 * jj + 1], o);
-            if (grouped) {
-              o[0] = Pack2<T>::mul(o[0], s2[2 * jj]);
-              o[1] = Pack2<T>::mul(o[1], s2[2 * jj + 1]);
-              o[2] = Pack2<T>::mul(o[2], s2[2 * jj]);
-              o[3] = Pack2<T>::mul(o[3], s2[2 * jj + 1]);
-            }
-            const uint32_t taddr = tmem_base + ((uint32_t)(32 * qd + 16 * jj) << 16) + sa * kAColsPerStage + r * 8;
-            tmem_st_16x128b_x2(taddr, o[0], o[1], o[2], o[3]);
-          }
-        }
-        // smem slot consumed (values are in registers and have been used)
-        __syncwarp();
-        if (lane == 0) mbar_arrive(empty_bar(s));
-        tc_wait_st();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(afull_bar(sa));
       }
-      u += ks1 - ks0;
+      mbar_wait(aempty_bar(own), ((it / kNA) & 1) ^ 1);
+      tc_fence_after();
+      if (args.dbg & 4) {
+        __syncwarp();
+        if (lane == 0) { mbar_arrive(empty_bar(s)); mbar_arrive(afull_bar(own)); }
+        continue;
+      }
+      uint32_t s2[4] = {0, 0, 0, 0};  // broadcast scales for (jj, b): index 2 jj + b
+#pragma unroll
+      for (int r = 0; r < kSlabs; ++r) {
+        if (grouped && (r % slabs_per_group) == 0) {
+          // scale_perm (gptq_marlin.py:30-33): position 8 c + b' of a 64-chunk holds column c + 8 b'; this thread needs
+          // b' = 4 jpair .. 4 jpair + 3  ->  one 8-byte read of the scale row the producer staged with the weights
+          const uint2 raw = *reinterpret_cast<const uint2*>(ssm + s * Cfg::S_STAGE_BYTES + (r / slabs_per_group) * 256);
+          s2[0] = Pack2<T>::bcast((uint16_t)(raw.x & 0xffff));
+          s2[1] = Pack2<T>::bcast((uint16_t)(raw.x >> 16));
+          s2[2] = Pack2<T>::bcast((uint16_t)(raw.y & 0xffff));
+          s2[3] = Pack2<T>::bcast((uint16_t)(raw.y >> 16));
+        }
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+          uint32_t o[4];
+          if (BITS == 4) dequant4<T>(w[r][jj], o);
+          else dequant8<T>(w[r][2 * jj], w[r][2 * jj + 1], o);
+          if (grouped) {
+            o[0] = Pack2<T>::mul(o[0], s2[2 * jj]);
+            o[1] = Pack2<T>::mul(o[1], s2[2 * jj + 1]);
+            o[2] = Pack2<T>::mul(o[2], s2[2 * jj]);
+            o[3] = Pack2<T>::mul(o[3], s2[2 * jj + 1]);
+          }
+          tmem_st_16x128b_x2(a_col + ((uint32_t)(16 * jj) << 16) + r * 8, o[0], o[1], o[2], o[3]);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty_bar(s));  // smem slot consumed (values are in registers and have been used)
+      tc_wait_st();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(afull_bar(own));
     }
-  } else if (warp >= 12) {
+  } else if (warp >= kEpiWarp0) {
     // ================= epilogue: TMEM -> registers -> global (direct, or split-K partial + last-arriver reduce) ==
     const int qd = warp & 3;
     const int row = 32 * qd + lane;  // output channel within the tile == TMEM lane
-    const int et = threadIdx.x - 12 * 32;  // 0..127
+    const int et = threadIdx.x - kEpiWarp0 * 32;  // 0..127
     __shared__ int s_last;
-    const bool grouped = args.num_groups > 1;
+    const bool grouped = gpu_ > 0;
     int seg = 0;
     for (int u = u_begin; u < u_end; ++seg) {
-      const int tile = u / KS, ks0 = u % KS;
+      const int tile = u / KS, ks0 = u - tile * KS;
       const int ks1 = min(KS, ks0 + (u_end - u));
       const int nt = tile % args.n_tiles, mc = tile / args.n_tiles;
       const int n = nt * kTileN + row;
@@ -395,23 +397,21 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const GemmArgs ar
       const int m_valid = min(MPAD, args.M - m0);
       const bool n_ok = n < args.N;
       const int ab = seg % Cfg::NACC;
-      const uint32_t accph = (seg / Cfg::NACC) & 1;
       const bool full_k = (ks0 == 0 && ks1 == KS);
       float ch_scale = 1.f;
-      if (!grouped && n_ok) {
-        const int n32 = n & 31;
-        ch_scale = to_f32<T>(reinterpret_cast<const T*>(args.scales)[(n & ~31) + scale_single_pos(n32)]);
-      }
+      if (!grouped && n_ok)
+        ch_scale = to_f32<T>(reinterpret_cast<const T*>(args.scales)[(n & ~31) + scale_single_pos(n & 31)]);
       // slot of this segment: 0 when it is the CTA's first segment, else 1
       const int my_slot = 2 * blockIdx.x + ((u == u_begin) ? 0 : 1);
       float* part_dst = args.scratch + (size_t)my_slot * (kTileN * MPAD);
       T* cdst = reinterpret_cast<T*>(args.C) + (size_t)m0 * args.N + n;
 
-      mbar_wait(accfull_bar(ab), accph);
+      mbar_wait(accfull_bar(ab), (seg / Cfg::NACC) & 1);
       tc_fence_after();
       const uint32_t acc_addr = tmem_base + ((uint32_t)(32 * qd) << 16) + kAccCol0 + ab * MPAD;
 #pragma unroll 1
       for (int j0 = 0; j0 < MPAD; j0 += 16) {
+        if (j0 >= m_valid) break;
         uint32_t v[16];
         tmem_ld_32x32b_x16(acc_addr + j0, v);
         tc_wait_ld();
@@ -523,17 +523,30 @@ static int launch_gemm(const GemmArgs& a_in, const void* A, int64_t lda, cudaStr
   if (int e = ensure_scratch(dev, (size_t)2 * grid * kTileN * MPAD, tiles, st)) return e;
   a.scratch = g_scratch[dev].partials;
   a.counters = g_scratch[dev].counters;
-  CUtensorMap tmap;
+  CUtensorMap tmap_a, tmap_w, tmap_s;
   const CUtensorMapDataType dt = std::is_same<T, __half>::value ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
-  if (!make_tmap_2d(&tmap, A, dt, 2, (uint64_t)a.M, (uint64_t)a.K, (uint64_t)lda * 2, MPAD, kUnitK))
-    return set_error(B200_ECUDA, "marlin gemm: cuTensorMapEncodeTiled failed (A=%p M=%d K=%d lda=%lld)", A, a.M, a.K, (long long)lda);
+  // activations [M, K] (row pitch lda): boxes of 64 (k) x MPAD rows, 128-byte swizzle, rows beyond M read as zero
+  bool ok = make_tmap_2d(&tmap_a, A, dt, 2, (uint64_t)a.M, (uint64_t)a.K, (uint64_t)lda * 2, MPAD, 64);
+  // packed weights [K/16, N*16*BITS/8 bytes] viewed as 8-byte elements: box = 8 slabs x one 128-column tile
+  const uint64_t wrow_bytes = (uint64_t)a.N * 16 * BITS / 8;
+  ok = ok && make_tmap_2d(&tmap_w, a.B, CU_TENSOR_MAP_DATA_TYPE_UINT64, 8, (uint64_t)a.K / 16, wrow_bytes / 8, wrow_bytes,
+                          kSlabs, Cfg::W_ROW_BYTES / 8, CU_TENSOR_MAP_SWIZZLE_NONE);
+  // group scales [num_groups, N]: box = (scale rows of one unit) x 128 columns
+  if (a.groups_per_unit > 0)
+    ok = ok && make_tmap_2d(&tmap_s, a.scales, dt, 2, (uint64_t)a.num_groups, (uint64_t)a.N, (uint64_t)a.N * 2,
+                            (uint32_t)a.groups_per_unit, kTileN, CU_TENSOR_MAP_SWIZZLE_NONE);
+  else
+    tmap_s = tmap_a;
+  if (!ok)
+    return set_error(B200_ECUDA, "marlin gemm: cuTensorMapEncodeTiled failed (A=%p M=%d K=%d N=%d lda=%lld)", A, a.M, a.K,
+                     a.N, (long long)lda);
   auto kern = marlin_gemm_kernel<T, MPAD, BITS>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static bool attr_set[64] = {};
+  if (!attr_set[dev & 63]) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
-    attr_set = true;
+    attr_set[dev & 63] = true;
   }
-  kern<<<grid, kGemmThreads, Cfg::SMEM_BYTES, st>>>(tmap, a);
+  kern<<<grid, kGemmThreads, Cfg::SMEM_BYTES, st>>>(tmap_a, tmap_w, tmap_s, a);
   return B200_OK;
 }
 
@@ -588,6 +601,8 @@ extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_
   ga.m_chunks = 1;
   ga.KS = (int)(size_k / kUnitK);
   ga.total_units = 0;
+  ga.groups_per_unit = num_groups > 1 ? kUnitK / gs : 0;
+  { const char* d = getenv("B200_GEMM_DBG"); ga.dbg = d ? atoi(d) : 0; }
   cudaStream_t st = (cudaStream_t)stream;
   int rc;
   if (dtype == B200_F16) rc = (num_bits == 4) ? dispatch_mpad<__half, 4>(ga, a, lda, st) : dispatch_mpad<__half, 8>(ga, a, lda, st);

@@ -83,12 +83,28 @@ __device__ __forceinline__ void tma_2d_g2s(uint32_t dst_smem, const CUtensorMap*
       "l"(map), "r"(c0), "r"(c1), "r"(bar)
       : "memory");
 }
+__device__ __forceinline__ void tma_2d_g2s_hint(uint32_t dst_smem, const CUtensorMap* map, int c0, int c1, uint32_t bar,
+                                                uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%2, %3}], [%4], %5;" ::
+          "r"(dst_smem),
+      "l"(map), "r"(c0), "r"(c1), "r"(bar), "l"(policy)
+      : "memory");
+}
 __device__ __forceinline__ void tma_3d_g2s(uint32_t dst_smem, const CUtensorMap* map, int c0, int c1, int c2,
                                            uint32_t bar) {
   asm volatile(
       "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::
           "r"(dst_smem),
       "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ void tma_3d_g2s_hint(uint32_t dst_smem, const CUtensorMap* map, int c0, int c1, int c2,
+                                                uint32_t bar, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%2, %3, %4}], [%5], %6;" ::
+          "r"(dst_smem),
+      "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(bar), "l"(policy)
       : "memory");
 }
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {

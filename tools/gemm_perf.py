@@ -1,0 +1,61 @@
+"""Kernel micro-benchmark (bring-up / tuning helper): Marlin W4A16 GEMM time and achieved HBM GB/s on the Llama-3-8B
+layer shapes, cold-L2 by rotating distinct weight buffers (> 126 MB of weights in rotation)."""
+import json
+import sys
+
+import torch
+
+sys.path.insert(0, ".")
+from nm_vllm_b200 import _custom_ops as ops  # noqa: E402
+
+DEV = "cuda:0"
+SHAPES = {"qkv": (4096, 6144), "o": (4096, 4096), "gate_up": (4096, 28672), "down": (14336, 4096)}
+MS = [1, 16, 32, 64] if len(sys.argv) < 2 else [int(x) for x in sys.argv[1].split(",")]
+dt = torch.float16 if (len(sys.argv) < 3 or sys.argv[2] == "fp16") else torch.bfloat16
+peak = 6524.6
+try:
+    peak = json.load(open("MEASURED_PEAKS.json"))["hbm_gbs"]
+except Exception:
+    pass
+res = {}
+if len(sys.argv) > 3:
+    SHAPES = {k: v for k, v in SHAPES.items() if k in sys.argv[3].split(",")}
+for name, (K, N) in SHAPES.items():
+    wbytes = K * N // 2
+    ncopy = max(3, int(400e6 // wbytes) + 1)
+    g = torch.Generator(device=DEV).manual_seed(0)
+    ws_ = [torch.randint(-2**31, 2**31 - 1, (K // 16, N * 2), generator=g, dtype=torch.int32, device=DEV) for _ in range(ncopy)]
+    ss_ = [(torch.rand((K // 128, N), generator=g, device=DEV) * 0.01 + 0.005).to(dt) for _ in range(ncopy)]
+    e = torch.empty(0, dtype=torch.int32, device=DEV)
+    wk = torch.zeros((N // 64) * 16, dtype=torch.int32, device=DEV)
+    for M in MS:
+        a = torch.randn((M, K), device=DEV, dtype=dt)
+        for i in range(3):
+            ops.gptq_marlin_gemm(a, ws_[i % ncopy], ss_[i % ncopy], e, e, wk, 4, M, N, K, True)
+        torch.cuda.synchronize()
+        # one CUDA graph = `reps` GEMMs over rotating weight buffers (removes host launch overhead from the timing)
+        reps = ncopy * 2
+        st = torch.cuda.Stream()
+        with torch.cuda.stream(st):
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, stream=st):
+                for i in range(reps):
+                    ops.gptq_marlin_gemm(a, ws_[i % ncopy], ss_[i % ncopy], e, e, wk, 4, M, N, K, True)
+            for _ in range(max(3, int(0.2 / (reps * 30e-6)))):   # ~0.2 s warm-up so clocks ramp
+                gr.replay()
+            torch.cuda.synchronize()
+            iters = 10
+            evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(iters)]
+            for i in range(iters):
+                evs[i][0].record()
+                gr.replay()
+                evs[i][1].record()
+            torch.cuda.synchronize()
+        ts = sorted(s.elapsed_time(t) / reps for s, t in evs)
+        med = ts[len(ts) // 2]
+        alg = K * N / 2 + (K / 128) * N * 2 + 2 * M * (K + N)
+        gbs = alg / (med * 1e-3) / 1e9
+        res[f"{name}_M{M}"] = dict(us=med * 1e3, gbs=gbs, frac=gbs / peak)
+        print(f"{name:8s} M={M:3d} K={K} N={N}: {med*1e3:8.2f} us  {gbs:7.1f} GB/s  {gbs/peak*100:5.1f}% of measured {peak:.0f}", flush=True)
+    del ws_, ss_
+json.dump(res, open("gpurun_out/gemm_perf.json", "w"), indent=1)
