@@ -63,6 +63,8 @@ paged_attn_generic_kernel(float* __restrict__ exp_sums, float* __restrict__ max_
                           int partition_size /* 0: whole sequence (v1) */, float kv_scale) {
   constexpr int X = 16 / sizeof(cache_t);
   extern __shared__ float smem[];
+  pdl_wait();
+  pdl_launch_dependents();
   const int head = blockIdx.x, seq = blockIdx.y, part = blockIdx.z;
   const int num_heads = gridDim.x, num_parts = gridDim.z;
   const int seq_len = seq_lens[seq];
@@ -188,6 +190,8 @@ paged_attn_v2_reduce_kernel(scalar_t* __restrict__ out, const float* __restrict_
                             const float* __restrict__ max_logits, const scalar_t* __restrict__ tmp_out,
                             const int* __restrict__ seq_lens, int head_size, int max_parts) {
   extern __shared__ float smem[];
+  pdl_wait();
+  pdl_launch_dependents();
   const int head = blockIdx.x, seq = blockIdx.y, num_heads = gridDim.x;
   const int seq_len = seq_lens[seq];
   const int nparts = (seq_len + kPartition - 1) / kPartition;
@@ -239,7 +243,7 @@ static int launch_generic_t(float* exp_sums, float* max_logits, void* out, const
                      max_seq_len, smem);
   if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   dim3 grid(num_heads, num_seqs, num_parts);
-  kern<<<grid, kAttnThreads, smem, st>>>(exp_sums, max_logits, (scalar_t*)out, (const scalar_t*)q,
+  launch_pdl(kern, grid, dim3(kAttnThreads), smem, st, exp_sums, max_logits, (scalar_t*)out, (const scalar_t*)q,
                                          (const cache_t*)kc, (const cache_t*)vc, num_kv_heads, scale, block_tables,
                                          seq_lens, max_blocks_per_seq, alibi, q_stride, kvbs, kvhs, head_size,
                                          block_size, partition_size, kv_scale);
@@ -272,7 +276,7 @@ int launch_v2_reduce(void* out, const float* exp_sums, const float* max_logits, 
   dim3 grid(num_heads, num_seqs);
   const size_t smem = sizeof(float) * (max_parts + 8);
   B200_DISPATCH_FLOAT(dtype, "paged_attention_v2", {
-    paged_attn_v2_reduce_kernel<scalar_t><<<grid, kAttnThreads, smem, st>>>(
+    launch_pdl(paged_attn_v2_reduce_kernel<scalar_t>, grid, dim3(kAttnThreads), smem, st,
         (scalar_t*)out, exp_sums, max_logits, (const scalar_t*)tmp_out, seq_lens, head_size, max_parts);
   });
   return B200_OK;

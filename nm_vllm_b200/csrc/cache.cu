@@ -26,6 +26,8 @@ __global__ void reshape_and_cache_kernel(const scalar_t* __restrict__ key, const
                                          const int64_t* __restrict__ slot_mapping, int64_t key_stride,
                                          int64_t value_stride, int num_heads, int head_size, int block_size,
                                          int x, float kv_scale) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int64_t token = blockIdx.x;
   const int64_t slot = slot_mapping[token];
   if (slot < 0) return;  // padding token (model_runner.py:60 _PAD_SLOT_ID)
@@ -91,7 +93,7 @@ extern "C" int b200_reshape_and_cache(const void* key, const void* value, void* 
   dim3 grid((unsigned)num_tokens), block(n < 512 ? ((n + 31) / 32) * 32 : 512);
   cudaStream_t st = (cudaStream_t)stream;
 #define LAUNCH(CT, KV)                                                                                    \
-  reshape_and_cache_kernel<scalar_t, CT, KV><<<grid, block, 0, st>>>(                                     \
+  launch_pdl(reshape_and_cache_kernel<scalar_t, CT, KV>, grid, block, 0, st,                              \
       (const scalar_t*)key, (const scalar_t*)value, (CT*)key_cache, (CT*)value_cache, slot_mapping,       \
       key_stride, value_stride, num_kv_heads, head_size, block_size, x, kv_scale)
   B200_DISPATCH_FLOAT(dtype, "reshape_and_cache", {

@@ -1,6 +1,7 @@
 // C-ABI plumbing shared by all kernels: thread-local error string, device queries, build info.
 #include "common.cuh"
 #include <mutex>
+#include <stdlib.h>
 
 namespace b200 {
 static thread_local char g_err[512] = "";
@@ -11,6 +12,15 @@ int set_error(int code, const char* fmt, ...) {
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
   return code;
+}
+
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200_NO_PDL");
+    v = (e && atoi(e) != 0) ? 0 : 1;
+  }
+  return v == 1;
 }
 
 int num_sms() {

@@ -28,6 +28,33 @@ int set_error(int code, const char* fmt, ...);  // defined in capi.cu; returns `
 
 int num_sms();  // cached SM count of the current device
 
+// ---- programmatic dependent launch (PDL) ------------------------------------------------------------------------------
+// Every kernel of the decode step is launched with the programmatic-stream-serialization attribute: it may start
+// while its predecessor is still running, calls pdl_wait() before touching anything the predecessor could still
+// read or write, and calls pdl_launch_dependents() as early as possible so that ITS successor can do the same.  Rule:
+// a kernel launched through launch_pdl() MUST execute pdl_wait() on every path that reaches global memory shared
+// with other kernels (the wait also orders it after the predecessor's predecessor).  B200_NO_PDL=1 disables it.
+bool pdl_enabled();  // defined in capi.cu
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+#endif
+
 // ---- scalar conversions -----------------------------------------------------------------------------
 template <typename T> __device__ __forceinline__ float to_f32(T v);
 template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }

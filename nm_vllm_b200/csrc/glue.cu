@@ -28,6 +28,8 @@ __device__ __forceinline__ float block_sum_1024(float v, float* red) {
 template <typename T, bool FUSED_ADD>
 __global__ void rms_norm_kernel(T* __restrict__ out, T* __restrict__ input, T* __restrict__ residual,
                                 const T* __restrict__ weight, float eps, int hidden) {
+  pdl_wait();
+  pdl_launch_dependents();
   __shared__ float red[33];
   const int64_t base = (int64_t)blockIdx.x * hidden;
   float var = 0.f;
@@ -50,6 +52,8 @@ __global__ void rms_norm_kernel(T* __restrict__ out, T* __restrict__ input, T* _
 
 template <typename T>
 __global__ void silu_and_mul_kernel(T* __restrict__ out, const T* __restrict__ input, int d) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int64_t tok = blockIdx.x;
   for (int i = threadIdx.x; i < d; i += blockDim.x) {
     const float x = to_f32<T>(input[tok * 2 * d + i]);
@@ -73,6 +77,8 @@ template <typename T, bool NEOX>
 __global__ void rotary_kernel(const int64_t* __restrict__ positions, T* __restrict__ query, T* __restrict__ key,
                               const T* __restrict__ cos_sin_cache, int rot_dim, int64_t q_stride, int64_t k_stride,
                               int num_heads, int num_kv_heads, int head_size) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int64_t tok = blockIdx.x;
   const T* cache = cos_sin_cache + positions[tok] * rot_dim;
   const int embed = rot_dim / 2;
@@ -93,7 +99,7 @@ extern "C" int b200_rms_norm(void* out, const void* input, const void* weight, i
   using namespace b200;
   if (num_tokens == 0) return B200_OK;
   B200_DISPATCH_FLOAT(dtype, "rms_norm", {
-    rms_norm_kernel<scalar_t, false><<<(unsigned)num_tokens, tok_threads(hidden_size, 1024), 0, (cudaStream_t)stream>>>(
+    launch_pdl(rms_norm_kernel<scalar_t, false>, dim3((unsigned)num_tokens), dim3(tok_threads(hidden_size, 1024)), 0, (cudaStream_t)stream, 
         (scalar_t*)out, (scalar_t*)input, nullptr, (const scalar_t*)weight, epsilon, hidden_size);
   });
   B200_LAUNCH_CHECK("rms_norm");
@@ -105,7 +111,7 @@ extern "C" int b200_fused_add_rms_norm(void* input, void* residual, const void* 
   using namespace b200;
   if (num_tokens == 0) return B200_OK;
   B200_DISPATCH_FLOAT(dtype, "fused_add_rms_norm", {
-    rms_norm_kernel<scalar_t, true><<<(unsigned)num_tokens, tok_threads(hidden_size, 1024), 0, (cudaStream_t)stream>>>(
+    launch_pdl(rms_norm_kernel<scalar_t, true>, dim3((unsigned)num_tokens), dim3(tok_threads(hidden_size, 1024)), 0, (cudaStream_t)stream, 
         (scalar_t*)input, (scalar_t*)input, (scalar_t*)residual, (const scalar_t*)weight, epsilon, hidden_size);
   });
   B200_LAUNCH_CHECK("fused_add_rms_norm");
@@ -116,7 +122,7 @@ extern "C" int b200_silu_and_mul(void* out, const void* input, int64_t num_token
   using namespace b200;
   if (num_tokens == 0) return B200_OK;
   B200_DISPATCH_FLOAT(dtype, "silu_and_mul", {
-    silu_and_mul_kernel<scalar_t><<<(unsigned)num_tokens, tok_threads(d, 1024), 0, (cudaStream_t)stream>>>(
+    launch_pdl(silu_and_mul_kernel<scalar_t>, dim3((unsigned)num_tokens), dim3(tok_threads(d, 1024)), 0, (cudaStream_t)stream, 
         (scalar_t*)out, (const scalar_t*)input, d);
   });
   B200_LAUNCH_CHECK("silu_and_mul");
@@ -132,11 +138,11 @@ extern "C" int b200_rotary_embedding(const int64_t* positions, void* query, void
   const int threads = tok_threads(num_heads * rot_dim / 2, 512);
   B200_DISPATCH_FLOAT(dtype, "rotary_embedding", {
     if (is_neox)
-      rotary_kernel<scalar_t, true><<<(unsigned)num_tokens, threads, 0, (cudaStream_t)stream>>>(
+      launch_pdl(rotary_kernel<scalar_t, true>, dim3((unsigned)num_tokens), dim3(threads), 0, (cudaStream_t)stream, 
           positions, (scalar_t*)query, (scalar_t*)key, (const scalar_t*)cos_sin_cache, rot_dim, query_stride,
           key_stride, num_heads, num_kv_heads, head_size);
     else
-      rotary_kernel<scalar_t, false><<<(unsigned)num_tokens, threads, 0, (cudaStream_t)stream>>>(
+      launch_pdl(rotary_kernel<scalar_t, false>, dim3((unsigned)num_tokens), dim3(threads), 0, (cudaStream_t)stream, 
           positions, (scalar_t*)query, (scalar_t*)key, (const scalar_t*)cos_sin_cache, rot_dim, query_stride,
           key_stride, num_heads, num_kv_heads, head_size);
   });

@@ -6,22 +6,27 @@
 // scale_perm / scale_perm_single); everything else is a different machine:
 //
 //   * swap-AB: the 128 weight rows (output channels) are the M=128 side of a tcgen05.mma, the skinny activation
-//     batch (padded to MPAD in {16,32,64,128,256}) is the N side.  Decode M=1..64 therefore fills the tensor core.
-//   * the dequantised weight operand never touches shared memory: packed int4 tiles arrive by 1-D bulk TMA
-//     (cp.async.bulk, 1 KB contiguous per 16(k) x 128(n) slab), 8 dequant warps expand them in registers
+//     batch (padded to MPAD in {16,32,64,128}) is the N side.  Decode M=1..64 therefore fills the tensor core.
+//   * the dequantised weight operand never touches shared memory: packed int4 tiles arrive by tensor-map TMA
+//     (one 16 KB request = 16 k16-slabs x 1 KB of a 128-column tile), 16 dequant warps expand them in registers
 //     (lop3 magic-number trick, exact zero-point subtraction, group scale in the activation dtype like the
 //     reference :270-278) and write them with tcgen05.st.16x128b.x2 straight into TMEM.  The Marlin fragment order
 //     (thread l holds k = {2q,2q+1,2q+8,2q+9}, n = c, c+8 with c = l/4, q = l%4) IS the register layout of that
 //     store shape, so no shuffle is needed and K stays in natural order in TMEM.
-//   * activations come by tensor-map TMA (128-byte swizzle, zero-filled rows beyond M) and are the B operand from
-//     shared memory; accumulators live in TMEM (double buffered), read back by 4 epilogue warps with tcgen05.ld.
-//   * work is split stream-K style: the (tile, 64-wide k-unit) space is cut into one contiguous range per CTA
+//   * activations come by one 3-D tensor-map request per stage (128-byte swizzle, zero-filled rows beyond M) and are
+//     the B operand from shared memory; accumulators live in TMEM (double buffered), read back by 4 epilogue warps.
+//   * one thread can only issue a TMA request every ~200-500 cycles (measured, tools/tma_bw2.cu), so THREE producer
+//     warps take the pipeline stages round-robin and a stage is 256 k deep (16 KB of weights).
+//   * work is split stream-K style: the (tile, 256-deep k-stage) space is cut into one contiguous range per CTA
 //     (grid = #SMs).  Tiles whose K range is shared by several CTAs are reduced deterministically: every
 //     contributor writes an fp32 partial to its own scratch slot, bumps the tile counter, and the last arriver adds
-//     the slots in CTA order (no float atomics, no spin locks; counters reset themselves -> CUDA-graph safe).
+//     the slots in CTA order with 16-byte loads (no float atomics, no spin locks; counters reset themselves).
+//   * programmatic dependent launch: the kernel is launched with the stream-serialization attribute and only waits
+//     for its predecessor (griddepcontrol.wait) before touching activations / outputs / scratch, so barrier setup,
+//     TMEM allocation and the first ring of weight + scale requests overlap the previous kernel of the decode step.
 //
-// Warp roles (512 threads): w0 TMA producer | w1 MMA issuer | w2 TMEM allocator | w3 idle | w4-11 dequant
-// (TMEM lane quarter = warp%4) | w12-15 epilogue (quarter = warp%4).
+// Warp roles (768 threads): w0-2 TMA producers | w3 TMEM allocator + MMA issuer | w4-19 dequant (TMEM lane quarter =
+// warp%4, warp j of a quarter owns half-stages h % 4 == j) | w20-23 epilogue (quarter = warp%4).
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tma_host.cuh"
@@ -31,27 +36,31 @@ namespace b200 {
 using namespace ptx;
 
 constexpr int kTileN = 128;
-constexpr int kUnitK = 128;                 // one pipeline stage / scheduling unit = 128 (k) x 128 (n) weights
-constexpr int kSlabs = kUnitK / 16;         // 16-row k slabs per unit
+constexpr int kStageK = 256;                // one pipeline stage / scheduling unit = 256 (k) x 128 (n) weights
+constexpr int kHalfK = 128;                 // dequant / TMEM granularity: half a stage
+constexpr int kSlabs = kHalfK / 16;         // 16-row k slabs per half stage
 constexpr int kGemmThreads = 768;
+constexpr int kNumProducers = 3;
+constexpr int kMmaWarp = 3;
 constexpr int kDequantWarp0 = 4;
-constexpr int kNumDequantWarps = 16;        // 4 per TMEM lane quarter; warp j of a quarter owns units it % 4 == j
+constexpr int kNumDequantWarps = 16;        // 4 per TMEM lane quarter
 constexpr int kEpiWarp0 = kDequantWarp0 + kNumDequantWarps;  // 20..23 (warp % 4 == quarter)
-constexpr int kNA = 4;                      // TMEM ring of dequantised-weight stages (one per dequant warp of a quarter)
-constexpr int kAColsPerStage = kUnitK / 2;  // 64 columns of packed 16-bit pairs
-constexpr int kAccCol0 = kNA * kAColsPerStage;  // 256
+constexpr int kNA = 4;                      // TMEM ring of dequantised half stages (one per dequant warp of a quarter)
+constexpr int kAColsPerHalf = kHalfK / 2;   // 64 columns of packed 16-bit pairs
+constexpr int kAccCol0 = kNA * kAColsPerHalf;  // 256
 
 template <int MPAD, int BITS>
 struct GemmCfg {
   static constexpr int W_ROW_BYTES = kTileN * 16 * BITS / 8;         // one 16(k) x 128(n) slab: 1024 (4-bit) / 2048 (8-bit)
-  static constexpr int W_STAGE_BYTES = kSlabs * W_ROW_BYTES;         // 8192 / 16384
-  static constexpr int A_BOX_BYTES = MPAD * 128;                     // one 64(k) x MPAD box, 128-byte swizzle
-  static constexpr int A_STAGE_BYTES = 2 * A_BOX_BYTES;
-  static constexpr int S_STAGE_BYTES = 1024;                         // up to four 128-column scale slabs (group 32)
+  static constexpr int W_HALF_BYTES = kSlabs * W_ROW_BYTES;          // 8192 / 16384
+  static constexpr int W_STAGE_BYTES = 2 * W_HALF_BYTES;             // 16384 / 32768
+  static constexpr int A_BOX_BYTES = MPAD * 128;                     // one 64(k) x MPAD chunk, 128-byte swizzle
+  static constexpr int A_STAGE_BYTES = 4 * A_BOX_BYTES;
+  static constexpr int S_STAGE_BYTES = 2048;                         // up to eight 128-column scale rows (group 32)
   static constexpr int STAGE_BYTES = W_STAGE_BYTES + A_STAGE_BYTES + S_STAGE_BYTES;
-  static constexpr int NSTAGES_RAW = (200 * 1024) / STAGE_BYTES;
-  static constexpr int NSTAGES = NSTAGES_RAW > 16 ? 16 : NSTAGES_RAW;
-  static constexpr int NACC = MPAD <= 128 ? 2 : 1;
+  static constexpr int NSTAGES_RAW = (198 * 1024) / STAGE_BYTES;
+  static constexpr int NSTAGES = NSTAGES_RAW > 8 ? 8 : NSTAGES_RAW;
+  static constexpr int NACC = 2;
   static constexpr int TMEM_COLS = 512;
   static constexpr int BAR_BYTES = (2 * NSTAGES + 2 * kNA + 4) * 8 + 16;
   static constexpr int SMEM_BYTES = 1024 /*align slack*/ + NSTAGES * STAGE_BYTES + BAR_BYTES;
@@ -63,14 +72,15 @@ struct GemmArgs {
   const uint8_t* B;      // packed weights
   const void* scales;    // [num_groups, N]
   void* C;               // [M, N]
-  float* scratch;        // [2 * grid][128 * MPAD] fp32 partial slots
+  float* scratch;        // [2 * grid][MPAD * 128] fp32 partial slots
   int* counters;         // [tiles], zero between launches
   int M, N, K;
   int num_groups, group_size;  // group_size == K when channelwise
-  int n_tiles, m_chunks, KS;   // KS = K / kUnitK
+  int n_tiles, m_chunks, KS;   // KS = ceil(K / kStageK)
   int total_units;
-  int groups_per_unit;         // scale rows staged per unit: 0 (channelwise), 1, 2 or 4
+  int groups_per_stage;        // scale rows staged per stage: 0 (channelwise), 2, 4 or 8
   int dbg;                     // bring-up switches (B200_GEMM_DBG), 0 in production
+  long long* prof;             // bring-up cycle counters [grid][16] (B200_GEMM_PROF), nullptr in production
 };
 
 struct Partition {
@@ -82,6 +92,7 @@ struct Partition {
     return u < big ? u / (q + 1) : r + (u - big) / q;
   }
 };
+
 
 // ---- dequantisation ------------------------------------------------------------------------------------------
 // one packed int32 of the 4-bit Marlin layout -> 4 registers in tcgen05.st.16x128b.x2 order:
@@ -201,6 +212,8 @@ __device__ __forceinline__ int scale_single_pos(int n32) {
   return 8 * (rem >> 1) + 2 * (n32 >> 3) + (rem & 1);
 }
 
+#define PROF_T0() const long long p_t0 = args.prof ? clock64() : 0
+#define PROF_ACC(var) if (args.prof) { const long long p_t1 = clock64(); var += p_t1 - p_mark; p_mark = p_t1; }
 // ---- the kernel --------------------------------------------------------------------------------------------------
 template <typename T, int MPAD, int BITS>
 __global__ void __launch_bounds__(kGemmThreads, 1)
@@ -225,6 +238,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));  // generic pointer to the aligned base
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long k_t0 = args.prof ? clock64() : 0;
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_a);
@@ -232,7 +246,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     prefetch_tmap(&tmap_s);
     for (int s = 0; s < NS; ++s) {
       mbar_init(full_bar(s), 1);
-      mbar_init(empty_bar(s), 4 + 1);   // one dequant warp per quarter + the MMA commit
+      mbar_init(empty_bar(s), 8 + 1);   // 2 halves x 4 quarter warps + the MMA commit
     }
     for (int s = 0; s < kNA; ++s) {
       mbar_init(afull_bar(s), 4);
@@ -244,90 +258,135 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     }
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
+  if (warp == kMmaWarp) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_launch_dependents();   // the next kernel of the stream may start its own prologue now
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
 
   const Partition part(args.total_units, gridDim.x);
   const int u_begin = part.start(blockIdx.x), u_end = part.start(blockIdx.x + 1);
+  const int n_units = u_end - u_begin;
   const int KS = args.KS;
-  const int gpu_ = args.groups_per_unit;
+  const int gps = args.groups_per_stage;
 
-  if (warp == 0 || (warp == 3 && (args.dbg & 2))) {
-    // ================= TMA producer: 4 tensor copies per 128 x 128 unit =================
-    const int pstride = (args.dbg & 2) ? 2 : 1, pfirst = (warp == 3) ? 1 : 0;
-    if (lane == 0) {
+  if (warp < kNumProducers) {
+    // ================= TMA producers: stage `it` belongs to warp it % 3; 3 tensor copies per 256 x 128 stage ==========
+    // (the whole warp runs the loops so that coordinates / descriptors stay warp-uniform; one elected lane issues)
+    {
       const uint64_t pol_w = policy_evict_first();   // weights are streamed exactly once
       const uint64_t pol_a = policy_evict_last();    // activations / scales are re-read by every CTA
-      const uint32_t tx = Cfg::W_STAGE_BYTES + Cfg::A_STAGE_BYTES + (uint32_t)gpu_ * 256u;
-      int it = 0;
-      for (int u = u_begin; u < u_end;) {
-        const int tile = u / KS, ks0 = u - tile * KS;
-        const int ks1 = min(KS, ks0 + (u_end - u));
-        const int nt = tile % args.n_tiles, mc = tile / args.n_tiles;
-        const int wcol = nt * (Cfg::W_ROW_BYTES / 8);  // tensor-map column in 8-byte elements
-        for (int ks = ks0; ks < ks1; ++ks, ++it) {
-          const int s = it % NS;
-          if ((it % pstride) != pfirst) continue;
-          mbar_wait(empty_bar(s), ((it / NS) & 1) ^ 1);
+      const uint32_t tx = Cfg::W_STAGE_BYTES + Cfg::A_STAGE_BYTES + (uint32_t)gps * 256u;
+      auto coords = [&](int it, int& nt, int& mc, int& ks) {
+        const int u = u_begin + it;
+        const int tile = u / KS;
+        ks = u - tile * KS;
+        nt = tile % args.n_tiles;
+        mc = tile / args.n_tiles;
+      };
+      auto issue_ws = [&](int it) {
+        int nt, mc, ks;
+        coords(it, nt, mc, ks);
+        const int s = it % NS;
+        if (elect_one()) {
           mbar_arrive_expect_tx(full_bar(s), tx);
-          tma_2d_g2s_hint(w_base + s * Cfg::W_STAGE_BYTES, &tmap_w, wcol, ks * kSlabs, full_bar(s), pol_w);
-          tma_2d_g2s_hint(act_base + s * Cfg::A_STAGE_BYTES, &tmap_a, ks * kUnitK, mc * MPAD, full_bar(s), pol_a);
-          tma_2d_g2s_hint(act_base + s * Cfg::A_STAGE_BYTES + Cfg::A_BOX_BYTES, &tmap_a, ks * kUnitK + 64, mc * MPAD,
-                          full_bar(s), pol_a);
-          if (gpu_) tma_2d_g2s_hint(sc_base + s * Cfg::S_STAGE_BYTES, &tmap_s, nt * kTileN, ks * gpu_, full_bar(s), pol_a);
+          tma_2d_g2s_hint(w_base + s * Cfg::W_STAGE_BYTES, &tmap_w, nt * (Cfg::W_ROW_BYTES / 8), ks * (kStageK / 16),
+                          full_bar(s), pol_w);
+          if (gps) tma_2d_g2s_hint(sc_base + s * Cfg::S_STAGE_BYTES, &tmap_s, nt * kTileN, ks * gps, full_bar(s), pol_a);
         }
-        u += ks1 - ks0;
+        __syncwarp();
+      };
+      auto issue_a = [&](int it) {
+        int nt, mc, ks;
+        coords(it, nt, mc, ks);
+        const int s = it % NS;
+        if (elect_one())
+          tma_3d_g2s_hint(act_base + s * Cfg::A_STAGE_BYTES, &tmap_a, 0, mc * MPAD, ks * (kStageK / 64), full_bar(s), pol_a);
+        __syncwarp();
+      };
+      // first ring pass: weights + scales do not depend on the previous kernel -> issue them before the PDL wait
+      for (int it = warp; it < n_units && it < NS; it += kNumProducers) issue_ws(it);
+      pdl_wait();
+      for (int it = warp; it < n_units && it < NS; it += kNumProducers) issue_a(it);
+      int it = warp;
+      while (it < NS) it += kNumProducers;
+      long long p_mark = args.prof ? clock64() : 0, p_wait = 0, p_issue = 0;
+      for (; it < n_units; it += kNumProducers) {
+        mbar_wait(empty_bar(it % NS), ((it / NS) & 1) ^ 1);
+        PROF_ACC(p_wait);
+        issue_ws(it);
+        issue_a(it);
+        PROF_ACC(p_issue);
       }
+      if (args.prof && warp == 0 && lane == 0) { args.prof[blockIdx.x * 16 + 0] = p_wait; args.prof[blockIdx.x * 16 + 1] = p_issue; }
     }
-  } else if (warp == 1) {
-    // ================= MMA issuer =================
-    if (lane == 0) {
+  } else if (warp == kMmaWarp) {
+    // ================= MMA issuer (warp-converged loops, one elected lane issues MMAs and commits) =================
+    {
       constexpr uint32_t idesc = make_idesc(1 /*F32*/, Pack2<T>::FMT, Pack2<T>::FMT, 128, MPAD);
       int it = 0, seg = 0;
+      long long p_mark = args.prof ? clock64() : 0, p_wacc = 0, p_wfull = 0, p_wafull = 0, p_issue = 0;
       for (int u = u_begin; u < u_end; ++seg) {
         const int ks0 = u % KS;
         const int ks1 = min(KS, ks0 + (u_end - u));
         const int ab = seg % Cfg::NACC;
         mbar_wait(accempty_bar(ab), ((seg / Cfg::NACC) & 1) ^ 1);
+        PROF_ACC(p_wacc);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + kAccCol0 + ab * MPAD;
         for (int ks = ks0; ks < ks1; ++ks, ++it) {
-          const int s = it % NS, sa = it % kNA;
+          const int s = it % NS;
           mbar_wait(full_bar(s), (it / NS) & 1);
-          mbar_wait(afull_bar(sa), (it / kNA) & 1);
-          tc_fence_after();
-          const uint32_t a_tmem = tmem_base + sa * kAColsPerStage;
+          PROF_ACC(p_wfull);
           const uint32_t b_smem = act_base + s * Cfg::A_STAGE_BYTES;
 #pragma unroll
-          for (int r = 0; r < kSlabs; ++r)
-            if (!(args.dbg & 1) || r == 0)
-            mma_f16_ts(d_tmem, a_tmem + r * 8, make_kmajor_sw128_desc(b_smem + (r >> 2) * Cfg::A_BOX_BYTES + (r & 3) * 32),
-                       idesc, (ks > ks0 || r > 0) ? 1u : 0u);
-          tc_commit(aempty_bar(sa));
-          tc_commit(empty_bar(s));
+          for (int h = 0; h < 2; ++h) {
+            const int hu = 2 * it + h, sa = hu % kNA;
+            mbar_wait(afull_bar(sa), (hu / kNA) & 1);
+            PROF_ACC(p_wafull);
+            tc_fence_after();
+            const uint32_t a_tmem = tmem_base + sa * kAColsPerHalf;
+            if (elect_one()) {
+#pragma unroll
+              for (int r = 0; r < kSlabs; ++r) {
+                const int R = h * kSlabs + r;   // k16 slab within the stage
+                mma_f16_ts(d_tmem, a_tmem + r * 8,
+                           make_kmajor_sw128_desc(b_smem + (R >> 2) * Cfg::A_BOX_BYTES + (R & 3) * 32), idesc,
+                           (ks > ks0 || h > 0 || r > 0) ? 1u : 0u);
+              }
+              tc_commit(aempty_bar(sa));
+              if (h == 1) tc_commit(empty_bar(s));
+              if (h == 1 && ks == ks1 - 1) tc_commit(accfull_bar(ab));
+            }
+            __syncwarp();
+            PROF_ACC(p_issue);
+          }
         }
-        tc_commit(accfull_bar(ab));
         u += ks1 - ks0;
       }
+      if (args.prof && lane == 0) { long long* q = args.prof + blockIdx.x * 16; q[2] = p_wacc; q[3] = p_wfull; q[4] = p_wafull; q[5] = p_issue; }
     }
   } else if (warp >= kDequantWarp0 && warp < kEpiWarp0) {
     // ================= dequant warps: smem (packed) -> registers -> TMEM =================
     const int qd = warp & 3;                      // TMEM lane quarter: rows 32 qd .. 32 qd + 31 of the tile
-    const int own = (warp - kDequantWarp0) >> 2;  // this warp handles units with it % 4 == own (TMEM stage `own`)
+    const int own = (warp - kDequantWarp0) >> 2;  // this warp handles half stages hu % 4 == own (TMEM slot `own`)
+    const int h = own & 1;                        // ... which are always the same half of their stage
     const int t64 = qd >> 1, jpair = qd & 1;
     const int c = lane >> 2;
-    const bool grouped = gpu_ > 0;
-    const int slabs_per_group = grouped ? (kSlabs / gpu_) : kSlabs;  // k16 slabs sharing one scale row
-    const uint32_t a_col = tmem_base + ((uint32_t)(32 * qd) << 16) + own * kAColsPerStage;
-    const uint8_t* wsm = smem_gen + (w_base - smem_base) + t64 * (Cfg::W_ROW_BYTES / 2) + lane * (4 * BITS) + jpair * (2 * BITS);
-    const uint8_t* ssm = smem_gen + (sc_base - smem_base) + (64 * t64 + 8 * c + 4 * jpair) * 2;
-    const int n_units = u_end - u_begin;
-    for (int it = own; it < n_units; it += kNA) {
+    const bool grouped = gps > 0;
+    const int gph = gps >> 1;                                        // scale rows per half stage
+    const int slabs_per_group = grouped ? (kSlabs / gph) : kSlabs;   // k16 slabs sharing one scale row
+    const uint32_t a_col = tmem_base + ((uint32_t)(32 * qd) << 16) + own * kAColsPerHalf;
+    const uint8_t* wsm = smem_gen + (w_base - smem_base) + h * Cfg::W_HALF_BYTES + t64 * (Cfg::W_ROW_BYTES / 2) +
+                         lane * (4 * BITS) + jpair * (2 * BITS);
+    const uint8_t* ssm = smem_gen + (sc_base - smem_base) + h * gph * 256 + (64 * t64 + 8 * c + 4 * jpair) * 2;
+    long long p_mark = args.prof ? clock64() : 0, p_wfull = 0, p_lds = 0, p_waempty = 0, p_deq = 0, p_st = 0;
+    for (int hu = own; hu < 2 * n_units; hu += kNA) {
+      const int it = hu >> 1;
       const int s = it % NS;
       mbar_wait(full_bar(s), (it / NS) & 1);
+      PROF_ACC(p_wfull);
       // packed words of this thread for all 8 slabs: 64-chunk t64, fragment lane, n16-tiles (2 jpair, 2 jpair + 1)
       uint32_t w[kSlabs][BITS == 4 ? 2 : 4];
 #pragma unroll
@@ -340,13 +399,10 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
           w[r][0] = v.x; w[r][1] = v.y; w[r][2] = v.z; w[r][3] = v.w;
         }
       }
-      mbar_wait(aempty_bar(own), ((it / kNA) & 1) ^ 1);
+      PROF_ACC(p_lds);
+      mbar_wait(aempty_bar(own), ((hu / kNA) & 1) ^ 1);
+      PROF_ACC(p_waempty);
       tc_fence_after();
-      if (args.dbg & 4) {
-        __syncwarp();
-        if (lane == 0) { mbar_arrive(empty_bar(s)); mbar_arrive(afull_bar(own)); }
-        continue;
-      }
       uint32_t s2[4] = {0, 0, 0, 0};  // broadcast scales for (jj, b): index 2 jj + b
 #pragma unroll
       for (int r = 0; r < kSlabs; ++r) {
@@ -374,19 +430,27 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         }
       }
       __syncwarp();
+      PROF_ACC(p_deq);
       if (lane == 0) mbar_arrive(empty_bar(s));  // smem slot consumed (values are in registers and have been used)
       tc_wait_st();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(afull_bar(own));
+      PROF_ACC(p_st);
     }
-  } else if (warp >= kEpiWarp0) {
+    if (args.prof && warp == kDequantWarp0 && lane == 0) {
+      long long* q = args.prof + blockIdx.x * 16; q[6] = p_wfull; q[7] = p_lds; q[8] = p_waempty; q[9] = p_deq; q[10] = p_st;
+    }
+  }
+  else if (warp >= kEpiWarp0) {
     // ================= epilogue: TMEM -> registers -> global (direct, or split-K partial + last-arriver reduce) ==
     const int qd = warp & 3;
     const int row = 32 * qd + lane;  // output channel within the tile == TMEM lane
     const int et = threadIdx.x - kEpiWarp0 * 32;  // 0..127
     __shared__ int s_last;
-    const bool grouped = gpu_ > 0;
+    const bool grouped = gps > 0;
+    pdl_wait();   // C, the partial slots and the tile counters may still be in use by the previous kernel
+    long long p_mark = args.prof ? clock64() : 0, p_wacc = 0, p_epi = 0;
     int seg = 0;
     for (int u = u_begin; u < u_end; ++seg) {
       const int tile = u / KS, ks0 = u - tile * KS;
@@ -398,30 +462,38 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       const bool n_ok = n < args.N;
       const int ab = seg % Cfg::NACC;
       const bool full_k = (ks0 == 0 && ks1 == KS);
-      float ch_scale = 1.f;
-      if (!grouped && n_ok)
-        ch_scale = to_f32<T>(reinterpret_cast<const T*>(args.scales)[(n & ~31) + scale_single_pos(n & 31)]);
       // slot of this segment: 0 when it is the CTA's first segment, else 1
       const int my_slot = 2 * blockIdx.x + ((u == u_begin) ? 0 : 1);
       float* part_dst = args.scratch + (size_t)my_slot * (kTileN * MPAD);
       T* cdst = reinterpret_cast<T*>(args.C) + (size_t)m0 * args.N + n;
 
       mbar_wait(accfull_bar(ab), (seg / Cfg::NACC) & 1);
+      PROF_ACC(p_wacc);
       tc_fence_after();
       const uint32_t acc_addr = tmem_base + ((uint32_t)(32 * qd) << 16) + kAccCol0 + ab * MPAD;
+      if (full_k) {
+        float ch_scale = 1.f;
+        if (!grouped && n_ok)
+          ch_scale = to_f32<T>(reinterpret_cast<const T*>(args.scales)[(n & ~31) + scale_single_pos(n & 31)]);
 #pragma unroll 1
-      for (int j0 = 0; j0 < MPAD; j0 += 16) {
-        if (j0 >= m_valid) break;
-        uint32_t v[16];
-        tmem_ld_32x32b_x16(acc_addr + j0, v);
-        tc_wait_ld();
-        if (full_k) {
+        for (int j0 = 0; j0 < MPAD; j0 += 16) {
+          if (j0 >= m_valid) break;
+          uint32_t v[16];
+          tmem_ld_32x32b_x16(acc_addr + j0, v);
+          tc_wait_ld();
           if (n_ok) {
 #pragma unroll
             for (int j = 0; j < 16; ++j)
               if (j0 + j < m_valid) cdst[(size_t)(j0 + j) * args.N] = from_f32<T>(__uint_as_float(v[j]) * ch_scale);
           }
-        } else {
+        }
+      } else {
+#pragma unroll 1
+        for (int j0 = 0; j0 < MPAD; j0 += 16) {
+          if (j0 >= m_valid) break;
+          uint32_t v[16];
+          tmem_ld_32x32b_x16(acc_addr + j0, v);
+          tc_wait_ld();
 #pragma unroll
           for (int j = 0; j < 16; ++j)
             if (j0 + j < m_valid) part_dst[(j0 + j) * kTileN + row] = __uint_as_float(v[j]);
@@ -444,22 +516,51 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         asm volatile("bar.sync 1, 128;" ::: "memory");
         if (s_last) {
           __threadfence();
-          if (n_ok) {
+          // the tile's partials are [m][128] fp32 per slot: thread et sums float4 number et + 128 j (row m = j * 4 +
+          // et / 32, channels 4 (et % 32) .. +3) over the slots in CTA order, 8 independent 16-byte loads in flight
+          const int total4 = m_valid * (kTileN / 4);
+          const int r4 = (et & 31) * 4;
+          const int nn = nt * kTileN + r4;
+          float4 chs = make_float4(1.f, 1.f, 1.f, 1.f);
+          if (!grouped && nn < args.N) {
+            const T* sp = reinterpret_cast<const T*>(args.scales);
+            chs.x = to_f32<T>(sp[(nn & ~31) + scale_single_pos((nn + 0) & 31)]);
+            chs.y = to_f32<T>(sp[(nn & ~31) + scale_single_pos((nn + 1) & 31)]);
+            chs.z = to_f32<T>(sp[(nn & ~31) + scale_single_pos((nn + 2) & 31)]);
+            chs.w = to_f32<T>(sp[(nn & ~31) + scale_single_pos((nn + 3) & 31)]);
+          }
+          constexpr int U = 8;
 #pragma unroll 1
-            for (int j0 = 0; j0 < m_valid; j0 += 8) {
-              float acc[8];
+          for (int i0 = et; i0 < total4; i0 += 128 * U) {
+            float4 acc[U];
 #pragma unroll
-              for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-              for (int b = b_first; b <= b_last; ++b) {
-                const int slot = 2 * b + ((part.start(b) / KS == tile) ? 0 : 1);
-                const float* src = args.scratch + (size_t)slot * (kTileN * MPAD) + row;
+            for (int j = 0; j < U; ++j) acc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int b = b_first; b <= b_last; ++b) {
+              const int slot = 2 * b + ((part.start(b) / KS == tile) ? 0 : 1);
+              const float4* src = reinterpret_cast<const float4*>(args.scratch + (size_t)slot * (kTileN * MPAD));
+              float4 v[U];
 #pragma unroll
-                for (int j = 0; j < 8; ++j)
-                  if (j0 + j < m_valid) acc[j] += __ldcg(src + (j0 + j) * kTileN);
+              for (int j = 0; j < U; ++j) {
+                const int idx = i0 + 128 * j;
+                v[j] = idx < total4 ? __ldcg(src + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
               }
 #pragma unroll
-              for (int j = 0; j < 8; ++j)
-                if (j0 + j < m_valid) cdst[(size_t)(j0 + j) * args.N] = from_f32<T>(acc[j] * ch_scale);
+              for (int j = 0; j < U; ++j) {
+                acc[j].x += v[j].x; acc[j].y += v[j].y; acc[j].z += v[j].z; acc[j].w += v[j].w;
+              }
+            }
+            if (nn < args.N) {   // N % 64 == 0, so a group of 4 channels is either fully inside or fully outside
+#pragma unroll
+              for (int j = 0; j < U; ++j) {
+                const int idx = i0 + 128 * j;
+                if (idx < total4) {
+                  const int m = idx >> 5;
+                  T o[4] = {from_f32<T>(acc[j].x * chs.x), from_f32<T>(acc[j].y * chs.y), from_f32<T>(acc[j].z * chs.z),
+                            from_f32<T>(acc[j].w * chs.w)};
+                  *reinterpret_cast<uint2*>(reinterpret_cast<T*>(args.C) + (size_t)(m0 + m) * args.N + nn) =
+                      *reinterpret_cast<const uint2*>(o);
+                }
+              }
             }
           }
           if (et == 0) args.counters[tile] = 0;  // self-reset: the next launch starts from zero
@@ -467,34 +568,56 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         asm volatile("bar.sync 1, 128;" ::: "memory");  // s_last is reused by the next segment
       }
       u += ks1 - ks0;
+      PROF_ACC(p_epi);
     }
+    if (args.prof && et == 0) { args.prof[blockIdx.x * 16 + 13] = p_wacc; args.prof[blockIdx.x * 16 + 14] = p_epi; }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+  if (args.prof && threadIdx.x == 0) { args.prof[blockIdx.x * 16 + 11] = clock64() - k_t0; args.prof[blockIdx.x * 16 + 12] = n_units; }
+  if (warp == kMmaWarp) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+}
+
+// act-order: the reference permutes the activation columns into a temporary before the GEMM (permute_cols_kernel,
+// gptq_marlin.cu:283-339); the repacked weight rows are sorted by group, so with is_k_full the groups are again
+// uniform blocks of group_size rows and the regular kernel applies.
+template <typename T>
+__global__ void permute_cols_kernel(T* __restrict__ out, const T* __restrict__ a, const int* __restrict__ perm, int K,
+                                    int64_t lda) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int64_t m = blockIdx.y;
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < K; k += gridDim.x * blockDim.x)
+    out[m * K + k] = a[m * lda + perm[k]];
 }
 
 // ---- host side -------------------------------------------------------------------------------------------------------
 struct DeviceScratch {
   float* partials = nullptr;
   int* counters = nullptr;
+  void* a_tmp = nullptr;
   size_t partial_floats = 0;
+  size_t a_tmp_bytes = 0;
   int counter_ints = 0;
 };
 static DeviceScratch g_scratch[64];
 
+static bool capturing(cudaStream_t st) {
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(st, &cap);
+  return cap != cudaStreamCaptureStatusNone;
+}
+
 static int ensure_scratch(int dev, size_t partial_floats, int counter_ints, cudaStream_t st) {
   DeviceScratch& s = g_scratch[dev];
   if (s.partials && s.partial_floats >= partial_floats && s.counter_ints >= counter_ints) return B200_OK;
-  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-  cudaStreamIsCapturing(st, &cap);
-  if (cap != cudaStreamCaptureStatusNone)
+  if (capturing(st))
     return set_error(B200_EINVAL,
                      "marlin gemm: split-K scratch must be reserved before CUDA-graph capture "
                      "(run one eager call or b200_gemm_scratch_reserve first)");
-  // grow generously once: worst case MPAD = 256
-  if (partial_floats < (size_t)2 * 256 * kTileN * 256) partial_floats = (size_t)2 * 256 * kTileN * 256;
+  // grow generously once: worst case MPAD = 128 on 256 CTAs
+  if (partial_floats < (size_t)2 * 256 * kTileN * 128) partial_floats = (size_t)2 * 256 * kTileN * 128;
   if (counter_ints < 1 << 16) counter_ints = 1 << 16;
   cudaDeviceSynchronize();
   if (s.partials) cudaFree(s.partials);
@@ -506,6 +629,19 @@ static int ensure_scratch(int dev, size_t partial_floats, int counter_ints, cuda
   cudaDeviceSynchronize();
   s.partial_floats = partial_floats;
   s.counter_ints = counter_ints;
+  return B200_OK;
+}
+
+static int ensure_a_tmp(int dev, size_t bytes, cudaStream_t st) {
+  DeviceScratch& s = g_scratch[dev];
+  if (s.a_tmp && s.a_tmp_bytes >= bytes) return B200_OK;
+  if (capturing(st))
+    return set_error(B200_EINVAL, "marlin gemm: act-order scratch must be reserved before CUDA-graph capture (run one eager call first)");
+  if (bytes < ((size_t)8 << 20)) bytes = (size_t)8 << 20;
+  cudaDeviceSynchronize();
+  if (s.a_tmp) cudaFree(s.a_tmp);
+  if (cudaMalloc(&s.a_tmp, bytes) != cudaSuccess) return set_error(B200_ECUDA, "marlin gemm: act-order scratch allocation failed");
+  s.a_tmp_bytes = bytes;
   return B200_OK;
 }
 
@@ -525,16 +661,17 @@ static int launch_gemm(const GemmArgs& a_in, const void* A, int64_t lda, cudaStr
   a.counters = g_scratch[dev].counters;
   CUtensorMap tmap_a, tmap_w, tmap_s;
   const CUtensorMapDataType dt = std::is_same<T, __half>::value ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
-  // activations [M, K] (row pitch lda): boxes of 64 (k) x MPAD rows, 128-byte swizzle, rows beyond M read as zero
-  bool ok = make_tmap_2d(&tmap_a, A, dt, 2, (uint64_t)a.M, (uint64_t)a.K, (uint64_t)lda * 2, MPAD, 64);
-  // packed weights [K/16, N*16*BITS/8 bytes] viewed as 8-byte elements: box = 8 slabs x one 128-column tile
+  // activations [M, K] (row pitch lda) as {64, M, K/64}: one box = 4 chunks of 64 (k) x MPAD rows, 128-byte swizzle,
+  // rows beyond M and chunks beyond K read as zero
+  bool ok = make_tmap_act3d(&tmap_a, A, dt, (uint64_t)a.M, (uint64_t)a.K, (uint64_t)lda * 2, MPAD, kStageK / 64);
+  // packed weights [K/16, N*16*BITS/8 bytes] viewed as 8-byte elements: box = 16 slabs x one 128-column tile
   const uint64_t wrow_bytes = (uint64_t)a.N * 16 * BITS / 8;
   ok = ok && make_tmap_2d(&tmap_w, a.B, CU_TENSOR_MAP_DATA_TYPE_UINT64, 8, (uint64_t)a.K / 16, wrow_bytes / 8, wrow_bytes,
-                          kSlabs, Cfg::W_ROW_BYTES / 8, CU_TENSOR_MAP_SWIZZLE_NONE);
-  // group scales [num_groups, N]: box = (scale rows of one unit) x 128 columns
-  if (a.groups_per_unit > 0)
+                          kStageK / 16, Cfg::W_ROW_BYTES / 8, CU_TENSOR_MAP_SWIZZLE_NONE);
+  // group scales [num_groups, N]: box = (scale rows of one stage) x 128 columns
+  if (a.groups_per_stage > 0)
     ok = ok && make_tmap_2d(&tmap_s, a.scales, dt, 2, (uint64_t)a.num_groups, (uint64_t)a.N, (uint64_t)a.N * 2,
-                            (uint32_t)a.groups_per_unit, kTileN, CU_TENSOR_MAP_SWIZZLE_NONE);
+                            (uint32_t)a.groups_per_stage, kTileN, CU_TENSOR_MAP_SWIZZLE_NONE);
   else
     tmap_s = tmap_a;
   if (!ok)
@@ -546,7 +683,35 @@ static int launch_gemm(const GemmArgs& a_in, const void* A, int64_t lda, cudaStr
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
     attr_set[dev & 63] = true;
   }
-  kern<<<grid, kGemmThreads, Cfg::SMEM_BYTES, st>>>(tmap_a, tmap_w, tmap_s, a);
+  static const bool prof_on = getenv("B200_GEMM_PROF") != nullptr;
+  a.prof = nullptr;
+  if (prof_on) { cudaMallocManaged(&a.prof, sizeof(long long) * 16 * grid); cudaMemset(a.prof, 0, sizeof(long long) * 16 * grid); }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmap_a, tmap_w, tmap_s, a);
+  if (e != cudaSuccess) return set_error(B200_ECUDA, "marlin gemm launch: %s", cudaGetErrorString(e));
+  if (prof_on) {
+    cudaDeviceSynchronize();
+    static const char* names[15] = {"prod.wait_empty", "prod.issue", "mma.wait_accempty", "mma.wait_full", "mma.wait_afull", "mma.issue",
+                                    "deq.wait_full", "deq.lds", "deq.wait_aempty", "deq.compute", "deq.wait_st", "cta.total", "cta.units",
+                                    "epi.wait_accfull", "epi.work"};
+    fprintf(stderr, "[gemm prof] M=%d N=%d K=%d MPAD=%d grid=%d stages=%d:", a.M, a.N, a.K, MPAD, grid, Cfg::NSTAGES);
+    for (int i = 0; i < 15; ++i) {
+      double sum = 0, mx = 0;
+      for (int b = 0; b < grid; ++b) { sum += (double)a.prof[b * 16 + i]; if ((double)a.prof[b * 16 + i] > mx) mx = (double)a.prof[b * 16 + i]; }
+      fprintf(stderr, " %s=%.0f(max %.0f)", names[i], sum / grid, mx);
+    }
+    fprintf(stderr, "\n");
+    cudaFree(a.prof);
+  }
   return B200_OK;
 }
 
@@ -555,8 +720,7 @@ static int dispatch_mpad(const GemmArgs& a, const void* A, int64_t lda, cudaStre
   if (a.M <= 16) return launch_gemm<T, 16, BITS>(a, A, lda, st);
   if (a.M <= 32) return launch_gemm<T, 32, BITS>(a, A, lda, st);
   if (a.M <= 64) return launch_gemm<T, 64, BITS>(a, A, lda, st);
-  if (a.M <= 128) return launch_gemm<T, 128, BITS>(a, A, lda, st);
-  return launch_gemm<T, 256, BITS>(a, A, lda, st);
+  return launch_gemm<T, 128, BITS>(a, A, lda, st);
 }
 
 }  // namespace b200
@@ -574,7 +738,7 @@ extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_
                                      int64_t size_k, int64_t lda, int num_groups, int is_k_full, int dtype,
                                      void* stream) {
   using namespace b200;
-  (void)workspace; (void)is_k_full;
+  (void)workspace;
   B200_CHECK(num_bits == 4 || num_bits == 8, "num_bits must be 4 or 8. Got = %d", num_bits);
   B200_CHECK(dtype == B200_F16 || dtype == B200_BF16, "gpt_marlin_gemm only supports bfloat16 and float16");
   B200_CHECK(size_n % 64 == 0, "size_n = %lld, is not divisible by min_thread_n = 64", (long long)size_n);
@@ -584,11 +748,28 @@ extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_
   B200_CHECK(num_groups >= 1 && size_k % num_groups == 0, "size_k = %lld, is not divisible by b_scales.size(0) = %d",
              (long long)size_k, num_groups);
   B200_CHECK((reinterpret_cast<uintptr_t>(a) & 15) == 0 && (lda * 2) % 16 == 0, "A must be 16-byte aligned with a 16-byte multiple row pitch");
-  if (g_idx != nullptr || perm != nullptr)
-    return set_error(B200_ENOTSUP, "gptq_marlin_gemm: act-order (g_idx/perm) is not covered by the sm_100a kernel yet");
+  const bool act_order = (g_idx != nullptr && perm != nullptr);
+  B200_CHECK((g_idx == nullptr) == (perm == nullptr), "g_idx and perm must both be given (act-order) or both be empty");
+  if (act_order && !is_k_full)
+    return set_error(B200_ENOTSUP, "gptq_marlin_gemm: act-order with is_k_full=False (row-parallel shard of an act-order "
+                                   "checkpoint) is not covered by the sm_100a kernel");
   if (size_m == 0 || size_n == 0) return B200_OK;
   const int gs = (int)(size_k / num_groups);
   if (num_groups > 1) B200_CHECK(gs == 32 || gs == 64 || gs == 128, "Unexpected group_size = %d", gs);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (act_order) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (int e = ensure_a_tmp(dev, (size_t)size_m * size_k * 2, st)) return e;
+    void* tmp = g_scratch[dev].a_tmp;
+    dim3 grid((unsigned)((size_k + 255) / 256), (unsigned)size_m);
+    if (dtype == B200_F16)
+      launch_pdl(permute_cols_kernel<__half>, grid, dim3(256), 0, st, (__half*)tmp, (const __half*)a, perm, (int)size_k, lda);
+    else
+      launch_pdl(permute_cols_kernel<__nv_bfloat16>, grid, dim3(256), 0, st, (__nv_bfloat16*)tmp, (const __nv_bfloat16*)a, perm, (int)size_k, lda);
+    a = tmp;
+    lda = size_k;
+  }
   GemmArgs ga;
   ga.B = reinterpret_cast<const uint8_t*>(b_q_weight);
   ga.scales = b_scales;
@@ -599,11 +780,10 @@ extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_
   ga.num_groups = num_groups; ga.group_size = gs;
   ga.n_tiles = (int)((size_n + kTileN - 1) / kTileN);
   ga.m_chunks = 1;
-  ga.KS = (int)(size_k / kUnitK);
+  ga.KS = (int)((size_k + kStageK - 1) / kStageK);
   ga.total_units = 0;
-  ga.groups_per_unit = num_groups > 1 ? kUnitK / gs : 0;
+  ga.groups_per_stage = num_groups > 1 ? kStageK / gs : 0;
   { const char* d = getenv("B200_GEMM_DBG"); ga.dbg = d ? atoi(d) : 0; }
-  cudaStream_t st = (cudaStream_t)stream;
   int rc;
   if (dtype == B200_F16) rc = (num_bits == 4) ? dispatch_mpad<__half, 4>(ga, a, lda, st) : dispatch_mpad<__half, 8>(ga, a, lda, st);
   else rc = (num_bits == 4) ? dispatch_mpad<__nv_bfloat16, 4>(ga, a, lda, st) : dispatch_mpad<__nv_bfloat16, 8>(ga, a, lda, st);

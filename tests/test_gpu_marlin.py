@@ -43,12 +43,13 @@ def test_repack_golden(ops, fname):
     assert torch.equal(got.cpu(), as_torch(g["marlin_q"]))
 
 
-def _gemm_case(ops, M, K, N, bits, group, dtype, seed=0):
+def _gemm_case(ops, M, K, N, bits, group, dtype, seed=0, act_order=False):
     w = fixtures.gemm_weights(K, N, seed=seed, dtype=dtype)
     a = fixtures.gemm_acts(M, K, seed=seed, dtype=dtype)
-    w_ref, mq, ms, g_idx, sort_idx, _ = ql.marlin_quantize(w, bits, group)
+    w_ref, mq, ms, g_idx, sort_idx, _ = ql.marlin_quantize(w, bits, group, act_order, seed=seed)
+    g_idx = g_idx.to(torch.int32) if g_idx.numel() else torch.empty(0, dtype=torch.int32)
     ws = torch.zeros((N // 64) * 16, dtype=torch.int32, device=DEV)
-    out = ops.gptq_marlin_gemm(a.to(DEV), mq.to(DEV), ms.to(dtype).to(DEV), g_idx.to(DEV), sort_idx.to(DEV), ws, bits,
+    out = ops.gptq_marlin_gemm(a.to(DEV), mq.to(DEV), ms.to(dtype).to(DEV), g_idx.to(DEV), sort_idx.to(torch.int32).to(DEV), ws, bits,
                                M, N, K, True)
     torch.cuda.synchronize()
     assert torch.all(ws == 0), "workspace must be left zeroed"
@@ -80,13 +81,33 @@ def test_marlin_gemm_8bit(ops, mnk, group, dtype):
     assert err < 1e-2, err
 
 
-@pytest.mark.parametrize("M", [1, 2, 8, 16, 17, 32, 33, 64, 65, 128, 200, 256, 300, 1024])
+@pytest.mark.parametrize("M", [1, 2, 8, 16, 17, 32, 33, 64, 65, 128, 129, 200, 256, 300, 1024])
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
 def test_marlin_gemm_llama_shapes_all_m(ops, M, dtype):
     # Llama-3-8B o_proj-like shape at every M bucket of the kernel (MPAD 16..256, multi-chunk)
     out, ref = _gemm_case(ops, M, 4096, 4096 if M <= 64 else 1024, 4, 128, dtype, seed=M)
     assert ops_ref.rel_mean_err(out, ref) < 1e-2
     assert torch.isfinite(out.float()).all()
+
+
+@pytest.mark.parametrize("mkn", [(1, 256, 128), (13, 1024, 256), (67, 2048, 192), (16, 384, 64)])
+@pytest.mark.parametrize("group", [32, 64, 128])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_marlin_gemm_act_order(ops, mkn, group, dtype):
+    # act-order (desc_act) checkpoints: rows sorted by group at repack time, activation columns gathered by `perm`
+    # (tests/kernels/test_marlin_gemm.py ACT_ORDER_OPTS; gptq_marlin.cu:283-339 permute_cols)
+    M, K, N = mkn
+    out, ref = _gemm_case(ops, M, K, N, 4, group, dtype, seed=M + K, act_order=True)
+    err = ops_ref.rel_mean_err(out, ref)
+    assert err < 1e-2, err
+
+
+def test_marlin_gemm_k_not_multiple_of_stage(ops):
+    # K = 128 * odd: the last 256-deep pipeline stage is half out of bounds (zero-filled by the tensor maps)
+    for K in (128, 384, 640):
+        for group in (-1, 128):
+            out, ref = _gemm_case(ops, 5, K, 256, 4, group, torch.float16, seed=K)
+            assert ops_ref.rel_mean_err(out, ref) < 1e-2
 
 
 def test_marlin_gemm_deterministic_and_repeatable(ops):
