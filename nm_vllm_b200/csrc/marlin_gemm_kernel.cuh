@@ -1,0 +1,720 @@
+// Marlin-layout W4A16 / W8A16 GEMM for sm_100a:  C[M,N] = A[M,K] . (s (.) (Q - 2^(bits-1)))
+//
+// Replaces gptq_marlin_gemm / marlin_gemm of the reference (csrc/quantization/gptq_marlin/gptq_marlin.cu:410-1363
+// kernel, :1577-1731 launcher, :1735-1868 op; csrc/quantization/marlin/dense/marlin_cuda_kernel.cu).  The STORED
+// layouts are the reference's (qweight [K/16, N*16/pf] int32 in 16x64 mma-fragment order, scales permuted by
+// scale_perm / scale_perm_single); everything else is a different machine:
+//
+//   * swap-AB: the 128 weight rows (output channels) are the M=128 side of a tcgen05.mma, the skinny activation
+//     batch (padded to MPAD in {16,32,64,128}) is the N side.  Decode M=1..64 therefore fills the tensor core.
+//   * the dequantised weight operand never touches shared memory: packed int4 tiles arrive by tensor-map TMA
+//     (one 16 KB request = 16 k16-slabs x 1 KB of a 128-column tile), dequant warps expand them in registers
+//     (lop3 magic-number trick, exact zero-point subtraction, group scale in the activation dtype like the
+//     reference :270-278) and write them with tcgen05.st.16x128b straight into TMEM.  The Marlin fragment order
+//     (thread l holds k = {2q,2q+1,2q+8,2q+9}, n = c, c+8 with c = l/4, q = l%4) IS the register layout of that
+//     store shape, so no shuffle is needed and K stays in natural order in TMEM.
+//   * one thread can only issue a small tcgen05.mma every ~50 cycles (measured, tools/mma_rate.cu: N=16..64, K=16),
+//     which is slower than the weight stream needs, while four issuing warps reach one per ~13 cycles.  The k range
+//     of a tile is therefore dealt round-robin, 128 k at a time, to NOWN "own-groups": each has 4 dequant warps (one
+//     per TMEM lane quarter), two 64-k TMEM operand slots, one issuer warp and its own fp32 accumulator; the
+//     epilogue adds the NOWN accumulators.
+//   * activations come by one 3-D tensor-map request per stage (128-byte swizzle, zero-filled rows beyond M) and are
+//     the B operand from shared memory.
+//   * work is split stream-K style: the (tile, 256-deep k-stage) space is cut into one contiguous range per CTA
+//     (grid = #SMs, all CTAs resident).  A tile whose K range is shared by several CTAs is reduced deterministically
+//     by the CTA that owns its first k-stage (the one that finishes last): the others write an fp32 partial to their
+//     own scratch slot and bump the tile counter; the owner's epilogue warps wait for the counter and add the slots
+//     in CTA order WHILE its own MMAs are still running, so the reduction is off the critical path (no float
+//     atomics; counters reset themselves).
+//   * programmatic dependent launch: the kernel only waits for its predecessor (griddepcontrol.wait) before touching
+//     activations / outputs / scratch, so barrier setup, TMEM allocation and the first ring of weight + scale
+//     requests overlap the previous kernel of the decode step.
+//
+// Warp roles: w0-1 TMA producers | w2 TMEM allocator | w4.. issuers (one per own-group) | w8.. dequant (TMEM lane
+// quarter = warp%4) | last 4 warps epilogue (quarter = warp%4).
+#pragma once
+#include "common.cuh"
+#include "ptx.cuh"
+#include "tma_host.cuh"
+#include <stdlib.h>
+#include <type_traits>
+
+namespace b200 {
+using namespace ptx;
+
+constexpr int kTileN = 128;
+constexpr int kStageK = 256;                // one pipeline stage / scheduling unit = 256 (k) x 128 (n) weights
+constexpr int kHalfK = 128;                 // one own-group turn: half a stage
+constexpr int kSlabs = kHalfK / 16;         // 16-row k slabs per half stage
+constexpr int kNumProducers = 2;
+constexpr int kAllocWarp = 2;
+constexpr int kIssuerWarp0 = 4;
+constexpr int kDequantWarp0 = 8;
+
+enum GroupMode { kChannelwise = 0, kGroup128 = 1, kGroupSmall = 2 };
+
+template <int MPAD, int BITS>
+struct GemmCfg {
+  static constexpr int NOWN = MPAD <= 64 ? 4 : 2;                    // own-groups (issuer warps / accumulators)
+  static constexpr int NBUF = MPAD <= 32 ? 2 : 1;                    // accumulator buffers per own-group
+  static constexpr int NDQ = 4 * NOWN;                               // dequant warps
+  static constexpr int EPI_WARP0 = kDequantWarp0 + NDQ;
+  static constexpr int THREADS = (EPI_WARP0 + 4) * 32;
+  static constexpr int ACC_COL0 = 64 * NOWN;                         // TMEM: [own-group operand slots][accumulators]
+  static constexpr int TMEM_COLS = 512;
+  static constexpr int W_ROW_BYTES = kTileN * 16 * BITS / 8;         // one 16(k) x 128(n) slab: 1024 (4-bit) / 2048 (8-bit)
+  static constexpr int W_HALF_BYTES = kSlabs * W_ROW_BYTES;          // 8192 / 16384
+  static constexpr int W_STAGE_BYTES = 2 * W_HALF_BYTES;             // 16384 / 32768
+  static constexpr int A_BOX_BYTES = MPAD * 128;                     // one 64(k) x MPAD chunk, 128-byte swizzle
+  static constexpr int A_STAGE_BYTES = 4 * A_BOX_BYTES;
+  static constexpr int S_STAGE_BYTES = 2048;                         // up to eight 128-column scale rows (group 32)
+  static constexpr int STAGE_BYTES = W_STAGE_BYTES + A_STAGE_BYTES + S_STAGE_BYTES;
+  static constexpr int NSTAGES_RAW = (208 * 1024) / STAGE_BYTES;
+  static constexpr int NSTAGES = NSTAGES_RAW > 8 ? 8 : NSTAGES_RAW;
+  static constexpr int NBARS = 2 * NSTAGES + 4 * NOWN + 2 * NOWN * NBUF;
+  static constexpr int BAR_BYTES = NBARS * 8 + 16;
+  static constexpr int SMEM_BYTES = 1024 /*align slack*/ + NSTAGES * STAGE_BYTES + BAR_BYTES;
+  static_assert(NSTAGES >= 2, "pipeline needs at least two stages");
+  static_assert(ACC_COL0 + NOWN * NBUF * MPAD <= 512, "TMEM budget");
+  static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
+};
+
+struct GemmArgs {
+  const uint8_t* B;      // packed weights
+  const void* scales;    // [num_groups, N]
+  void* C;               // [M, N]
+  float* scratch;        // [grid][MPAD * 128] fp32 partial slots
+  int* counters;         // [tiles], zero between launches
+  int M, N, K;
+  int num_groups, group_size;  // group_size == K when channelwise
+  int n_tiles, m_chunks, KS;   // KS = ceil(K / kStageK)
+  int total_units;
+  int groups_per_stage;        // scale rows staged per stage: 0 (channelwise), 2, 4 or 8
+  long long* prof;             // bring-up cycle counters [grid][16] (B200_GEMM_PROF), nullptr in production
+};
+
+struct Partition {
+  int q, r;
+  __device__ __forceinline__ Partition(int total, int g) : q(total / g), r(total % g) {}
+  __device__ __forceinline__ int start(int b) const { return b * q + min(b, r); }
+  __device__ __forceinline__ int owner(int u) const {
+    const int big = r * (q + 1);
+    return u < big ? u / (q + 1) : r + (u - big) / q;
+  }
+};
+
+// ---- dequantisation ------------------------------------------------------------------------------------------
+// one packed int32 of the 4-bit Marlin layout -> 4 registers in tcgen05.st.16x128b order:
+//   o[0] = (n=c  , k=2q,2q+1)  o[1] = (n=c+8, k=2q,2q+1)  o[2] = (n=c  , k=2q+8,2q+9)  o[3] = (n=c+8, k=2q+8,2q+9)
+// nibble positions (marlin_perms.py:29 interleave [0,2,4,6,1,3,5,7]): p0,p4 -> o[0]; p1,p5 -> o[2]; p2,p6 -> o[1]; p3,p7 -> o[3]
+template <typename T>
+__device__ __forceinline__ void dequant4(uint32_t q, uint32_t* o);
+
+template <>
+__device__ __forceinline__ void dequant4<__half>(uint32_t q, uint32_t* o) {
+  // (q & 0x000f000f) | 0x64006400 = half2(1024 + nib); (q & 0x00f000f0) | 0x6400.. = half2(1024 + 16 nib)
+  constexpr uint32_t LO = 0x000f000f, HI = 0x00f000f0, EX = 0x64006400;
+  constexpr uint32_t SUB = 0x64086408;   // 1032 = 1024 + 8
+  constexpr uint32_t MUL = 0x2c002c00;   // 1/16
+  constexpr uint32_t ADD = 0xd480d480;   // -72 = -(1024/16 + 8)
+  uint32_t lo0, hi0, lo1, hi1;
+  asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(lo0) : "r"(q), "n"(LO), "n"(EX));
+  asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(hi0) : "r"(q), "n"(HI), "n"(EX));
+  q >>= 8;
+  asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(lo1) : "r"(q), "n"(LO), "n"(EX));
+  asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(hi1) : "r"(q), "n"(HI), "n"(EX));
+  __half2 a = __hsub2(*reinterpret_cast<__half2*>(&lo0), *reinterpret_cast<const __half2*>(&SUB));
+  __half2 b = __hsub2(*reinterpret_cast<__half2*>(&lo1), *reinterpret_cast<const __half2*>(&SUB));
+  __half2 c = __hfma2(*reinterpret_cast<__half2*>(&hi0), *reinterpret_cast<const __half2*>(&MUL),
+                      *reinterpret_cast<const __half2*>(&ADD));
+  __half2 d = __hfma2(*reinterpret_cast<__half2*>(&hi1), *reinterpret_cast<const __half2*>(&MUL),
+                      *reinterpret_cast<const __half2*>(&ADD));
+  o[0] = *reinterpret_cast<uint32_t*>(&a);
+  o[1] = *reinterpret_cast<uint32_t*>(&b);
+  o[2] = *reinterpret_cast<uint32_t*>(&c);
+  o[3] = *reinterpret_cast<uint32_t*>(&d);
+}
+
+template <>
+__device__ __forceinline__ void dequant4<__nv_bfloat16>(uint32_t q, uint32_t* o) {
+  // bf16 has 7 mantissa bits: (nib | 0x4300) = 128 + nib exactly; each nibble pair needs its own shift
+  constexpr uint32_t MASK = 0x000f000f, EX = 0x43004300;
+  constexpr uint32_t ONE = 0x3f803f80;   // 1.0
+  constexpr uint32_t ADD = 0xc308c308;   // -136 = -(128 + 8)
+  uint32_t v[4];
+  asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(v[0]) : "r"(q), "n"(MASK), "n"(EX));  // p0,p4 -> o[0]
+  q >>= 4;
+  asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(v[2]) : "r"(q), "n"(MASK), "n"(EX));  // p1,p5 -> o[2]
+  q >>= 4;
+  asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(v[1]) : "r"(q), "n"(MASK), "n"(EX));  // p2,p6 -> o[1]
+  q >>= 4;
+  asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(v[3]) : "r"(q), "n"(MASK), "n"(EX));  // p3,p7 -> o[3]
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    __nv_bfloat162 t = __hfma2(*reinterpret_cast<__nv_bfloat162*>(&v[i]), *reinterpret_cast<const __nv_bfloat162*>(&ONE),
+                               *reinterpret_cast<const __nv_bfloat162*>(&ADD));
+    o[i] = *reinterpret_cast<uint32_t*>(&t);
+  }
+}
+
+// 8-bit: two int32 per fragment (half b = 0/1), byte order [k=2q, 2q+8, 2q+1, 2q+9] (marlin_perms.py:31)
+template <typename T>
+__device__ __forceinline__ void dequant8(uint32_t q0, uint32_t q1, uint32_t* o);
+
+template <>
+__device__ __forceinline__ void dequant8<__half>(uint32_t q0, uint32_t q1, uint32_t* o) {
+  constexpr uint32_t EX = 0x64646464;
+  constexpr uint32_t SUB = 0x64806480;  // 1152 = 1024 + 128
+  uint32_t t[4];
+  t[0] = __byte_perm(q0, EX, 0x4240);  // bytes 0,2 -> (k=2q, 2q+1), n = c
+  t[1] = __byte_perm(q1, EX, 0x4240);  //                             n = c + 8
+  t[2] = __byte_perm(q0, EX, 0x4341);  // bytes 1,3 -> (k=2q+8, 2q+9)
+  t[3] = __byte_perm(q1, EX, 0x4341);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    __half2 v = __hsub2(*reinterpret_cast<__half2*>(&t[i]), *reinterpret_cast<const __half2*>(&SUB));
+    o[i] = *reinterpret_cast<uint32_t*>(&v);
+  }
+}
+
+template <>
+__device__ __forceinline__ void dequant8<__nv_bfloat16>(uint32_t q0, uint32_t q1, uint32_t* o) {
+  // through fp32: (0x4B000000 | byte) = 8388608 + byte exactly; subtract 8388736 = 8388608 + 128
+  constexpr uint32_t EX = 0x4B000000;
+  const float bias = 8388736.0f;
+  auto one = [&](uint32_t q, int sel_lo, int sel_hi) -> uint32_t {
+    float f0 = __uint_as_float(__byte_perm(q, EX, sel_lo)) - bias;
+    float f1 = __uint_as_float(__byte_perm(q, EX, sel_hi)) - bias;
+    __nv_bfloat162 v = __floats2bfloat162_rn(f0, f1);
+    return *reinterpret_cast<uint32_t*>(&v);
+  };
+  o[0] = one(q0, 0x7650, 0x7652);
+  o[1] = one(q1, 0x7650, 0x7652);
+  o[2] = one(q0, 0x7651, 0x7653);
+  o[3] = one(q1, 0x7651, 0x7653);
+}
+
+template <typename T> struct Pack2;
+template <> struct Pack2<__half> {
+  static __device__ __forceinline__ uint32_t mul(uint32_t v, uint32_t s) {
+    __half2 r = __hmul2(*reinterpret_cast<__half2*>(&v), *reinterpret_cast<__half2*>(&s));
+    return *reinterpret_cast<uint32_t*>(&r);
+  }
+  static constexpr uint32_t FMT = 0;  // F16
+};
+template <> struct Pack2<__nv_bfloat16> {
+  static __device__ __forceinline__ uint32_t mul(uint32_t v, uint32_t s) {
+    __nv_bfloat162 r = __hmul2(*reinterpret_cast<__nv_bfloat162*>(&v), *reinterpret_cast<__nv_bfloat162*>(&s));
+    return *reinterpret_cast<uint32_t*>(&r);
+  }
+  static constexpr uint32_t FMT = 1;  // BF16
+};
+__device__ __forceinline__ uint32_t bcast16(uint32_t s) { return __byte_perm(s, 0, 0x1010); }
+__device__ __forceinline__ uint32_t bcast16_hi(uint32_t s) { return __byte_perm(s, 0, 0x3232); }
+
+// position of output column n (0..31 within a 32-chunk) in a scale row permuted by scale_perm_single
+// (gptq_marlin.py:34-38: perm[8 i + jj] = 2 i + {0,1,8,9,16,17,24,25}[jj])
+__device__ __forceinline__ int scale_single_pos(int n32) {
+  const int rem = n32 & 7;
+  return 8 * (rem >> 1) + 2 * (n32 >> 3) + (rem & 1);
+}
+
+// registers -> TMEM, 16 lanes x 128 bit pattern repeated eight times along columns (32 columns = four k16 slabs):
+// register 4 i + j of the list is register j of the .x2 pattern (ptx.cuh) for slab i
+__device__ __forceinline__ void tmem_st_16x128b_x8(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.16x128b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+
+__device__ __forceinline__ int ld_acquire_gpu(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+#define PROF_ACC(var) if (args.prof) { const long long p_t1 = clock64(); var += p_t1 - p_mark; p_mark = p_t1; }
+
+// ---- the kernel --------------------------------------------------------------------------------------------------
+template <typename T, int MPAD, int BITS, int GM>
+__global__ void __launch_bounds__(GemmCfg<MPAD, BITS>::THREADS, 1)
+marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
+                   const __grid_constant__ CUtensorMap tmap_s, const GemmArgs args) {
+  using Cfg = GemmCfg<MPAD, BITS>;
+  constexpr int NS = Cfg::NSTAGES, NOWN = Cfg::NOWN, NBUF = Cfg::NBUF;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  // layout: [activation stages (1024-aligned)] [weight stages] [scale stages] [barriers]
+  const uint32_t act_base = smem_base;
+  const uint32_t w_base = act_base + NS * Cfg::A_STAGE_BYTES;
+  const uint32_t sc_base = w_base + NS * Cfg::W_STAGE_BYTES;
+  const uint32_t bar_base = sc_base + NS * Cfg::S_STAGE_BYTES;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (NS + s); };
+  auto afull_bar = [&](int o, int sub) { return bar_base + 8u * (2 * NS + 2 * o + sub); };
+  auto aempty_bar = [&](int o, int sub) { return bar_base + 8u * (2 * NS + 2 * NOWN + 2 * o + sub); };
+  auto accfull_bar = [&](int o, int b) { return bar_base + 8u * (2 * NS + 4 * NOWN + o * NBUF + b); };
+  auto accempty_bar = [&](int o, int b) { return bar_base + 8u * (2 * NS + 4 * NOWN + NOWN * NBUF + o * NBUF + b); };
+  const uint32_t tmem_slot = bar_base + 8u * Cfg::NBARS;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));  // generic pointer to the aligned base
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long k_t0 = args.prof ? clock64() : 0;
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmap_w);
+    prefetch_tmap(&tmap_a);
+    if (GM != kChannelwise) prefetch_tmap(&tmap_s);
+    for (int s = 0; s < NS; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 8 + 2);   // 2 halves x 4 quarter warps + the two issuers' commits
+    }
+    for (int o = 0; o < NOWN; ++o) {
+      for (int sub = 0; sub < 2; ++sub) {
+        mbar_init(afull_bar(o, sub), 4);
+        mbar_init(aempty_bar(o, sub), 1);
+      }
+      for (int b = 0; b < NBUF; ++b) {
+        mbar_init(accfull_bar(o, b), 1);
+        mbar_init(accempty_bar(o, b), 4);
+      }
+    }
+    fence_barrier_init();
+  }
+  __syncthreads();            // barriers are live: the producers start streaming weights right away
+  pdl_launch_dependents();    // the next kernel of the stream may start its own prologue now
+
+  const Partition part(args.total_units, gridDim.x);
+  const int u_begin = part.start(blockIdx.x), u_end = part.start(blockIdx.x + 1);
+  const int n_units = u_end - u_begin;
+  const int KS = args.KS;
+  const int gps = args.groups_per_stage;
+
+  if (warp < kNumProducers) {
+    // ================= TMA producers: stage `it` belongs to warp it % 2; 3 tensor copies per 256 x 128 stage ==========
+    // (the whole warp runs the loops so that coordinates / descriptors stay warp-uniform; one elected lane issues)
+    const uint64_t pol_w = policy_evict_first();   // weights are streamed exactly once
+    const uint64_t pol_a = policy_evict_last();    // activations / scales are re-read by every CTA
+    const uint32_t tx = Cfg::W_STAGE_BYTES + Cfg::A_STAGE_BYTES + (GM != kChannelwise ? (uint32_t)gps * 256u : 0u);
+    auto coords = [&](int it, int& nt, int& mc, int& ks) {
+      const int u = u_begin + it;
+      const int tile = u / KS;
+      ks = u - tile * KS;
+      nt = tile % args.n_tiles;
+      mc = tile / args.n_tiles;
+    };
+    auto issue_ws = [&](int it) {
+      int nt, mc, ks;
+      coords(it, nt, mc, ks);
+      const int s = it % NS;
+      if (elect_one()) {
+        mbar_arrive_expect_tx(full_bar(s), tx);
+        tma_2d_g2s_hint(w_base + s * Cfg::W_STAGE_BYTES, &tmap_w, nt * (Cfg::W_ROW_BYTES / 8), ks * (kStageK / 16),
+                        full_bar(s), pol_w);
+        if (GM != kChannelwise)
+          tma_2d_g2s_hint(sc_base + s * Cfg::S_STAGE_BYTES, &tmap_s, nt * kTileN, ks * gps, full_bar(s), pol_a);
+      }
+      __syncwarp();
+    };
+    auto issue_a = [&](int it) {
+      int nt, mc, ks;
+      coords(it, nt, mc, ks);
+      const int s = it % NS;
+      if (elect_one())
+        tma_3d_g2s_hint(act_base + s * Cfg::A_STAGE_BYTES, &tmap_a, 0, mc * MPAD, ks * (kStageK / 64), full_bar(s), pol_a);
+      __syncwarp();
+    };
+    // first ring pass: weights + scales do not depend on the previous kernel -> issue them before the PDL wait
+    for (int it = warp; it < n_units && it < NS; it += kNumProducers) issue_ws(it);
+    pdl_wait();
+    for (int it = warp; it < n_units && it < NS; it += kNumProducers) issue_a(it);
+    int it = warp;
+    while (it < NS) it += kNumProducers;
+    for (; it < n_units; it += kNumProducers) {
+      mbar_wait(empty_bar(it % NS), ((it / NS) & 1) ^ 1);
+      issue_ws(it);
+      issue_a(it);
+    }
+  } else if (warp < kIssuerWarp0) {
+    if (warp == kAllocWarp) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
+  }
+  // everyone but the producers needs the TMEM base address
+  if (warp >= kNumProducers) {
+    tc_fence_before();
+    asm volatile("bar.sync 2, %0;" ::"n"(Cfg::THREADS - kNumProducers * 32) : "memory");
+    tc_fence_after();
+  }
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
+
+  if (warp >= kIssuerWarp0 && warp < kIssuerWarp0 + NOWN) {
+    // ================= MMA issuers: own-group o turns half stages hu % NOWN == o into its own accumulator ==========
+    const int o = warp - kIssuerWarp0, h = o & 1;
+    constexpr uint32_t idesc = make_idesc(1 /*F32*/, Pack2<T>::FMT, Pack2<T>::FMT, 128, MPAD);
+    const uint32_t a_tmem0 = tmem_base + 64 * o;
+    uint32_t uo = 0;
+    long long p_mark = args.prof ? clock64() : 0, p_wacc = 0, p_wfull = 0, p_wafull = 0, p_issue = 0;
+    for (int u = u_begin; u < u_end;) {
+      const int ks0 = u % KS;
+      const int len = min(KS - ks0, u_end - u);
+      const int it0 = u - u_begin, it1 = it0 + len;
+      int hu = 2 * it0 + ((o - 2 * it0) & (NOWN - 1));
+      if (hu < 2 * it1) {
+        const int ab = uo % NBUF;
+        mbar_wait(accempty_bar(o, ab), ((uo / NBUF) & 1) ^ 1);
+        PROF_ACC(p_wacc);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + Cfg::ACC_COL0 + (o * NBUF + ab) * MPAD;
+        bool fresh = true;
+        for (; hu < 2 * it1; hu += NOWN) {
+          const int it = hu >> 1, s = it % NS, jc = (hu - o) / NOWN;
+          mbar_wait(full_bar(s), (it / NS) & 1);
+          PROF_ACC(p_wfull);
+          const uint32_t b_smem = act_base + s * Cfg::A_STAGE_BYTES;
+          const bool last = hu + NOWN >= 2 * it1;
+#pragma unroll
+          for (int sub = 0; sub < 2; ++sub) {
+            mbar_wait(afull_bar(o, sub), jc & 1);
+            PROF_ACC(p_wafull);
+            tc_fence_after();
+            if (elect_one()) {
+#pragma unroll
+              for (int rr = 0; rr < 4; ++rr) {
+                const int R = h * kSlabs + sub * 4 + rr;   // k16 slab within the stage
+                mma_f16_ts(d_tmem, a_tmem0 + sub * 32 + rr * 8,
+                           make_kmajor_sw128_desc(b_smem + (R >> 2) * Cfg::A_BOX_BYTES + (R & 3) * 32), idesc,
+                           (fresh && sub == 0 && rr == 0) ? 0u : 1u);
+              }
+              tc_commit(aempty_bar(o, sub));
+              if (sub == 1) {
+                tc_commit(empty_bar(s));
+                if (last) tc_commit(accfull_bar(o, ab));
+              }
+            }
+            __syncwarp();
+            PROF_ACC(p_issue);
+          }
+          fresh = false;
+        }
+        ++uo;
+      }
+      u += len;
+    }
+    if (args.prof && o == 0 && lane == 0) { long long* q = args.prof + blockIdx.x * 16; q[2] = p_wacc; q[3] = p_wfull; q[4] = p_wafull; q[5] = p_issue; }
+  } else if (warp >= kDequantWarp0 && warp < Cfg::EPI_WARP0) {
+    // ================= dequant warps: smem (packed) -> registers -> TMEM =================
+    const int qd = warp & 3;                       // TMEM lane quarter: rows 32 qd .. 32 qd + 31 of the tile
+    const int o = (warp - kDequantWarp0) >> 2;     // own-group: half stages hu % NOWN == o
+    const int h = o & 1;                           // ... which are always the same half of their stage
+    const int t64 = qd >> 1, jpair = qd & 1;
+    const int c = lane >> 2;
+    constexpr int WPT = BITS == 4 ? 2 : 4;         // packed words per thread per slab
+    const int gph = gps >> 1;                      // scale rows per half stage (kGroupSmall: 2 or 4)
+    const int lspg = gph == 4 ? 1 : 2;             // log2(slabs per group) for kGroupSmall
+    const uint32_t a_col = tmem_base + ((uint32_t)(32 * qd) << 16) + 64 * o;
+    const uint8_t* wsm = smem_gen + (w_base - smem_base) + h * Cfg::W_HALF_BYTES + t64 * (Cfg::W_ROW_BYTES / 2) +
+                         lane * (4 * BITS) + jpair * (2 * BITS);
+    const uint8_t* ssm = smem_gen + (sc_base - smem_base) + h * gph * 256 + (64 * t64 + 8 * c + 4 * jpair) * 2;
+    long long p_mark = args.prof ? clock64() : 0, p_wfull = 0, p_lds = 0, p_waempty = 0, p_deq = 0, p_st = 0;
+    int jc = 0;
+    for (int hu = o; hu < 2 * n_units; hu += NOWN, ++jc) {
+      const int it = hu >> 1;
+      const int s = it % NS;
+      mbar_wait(full_bar(s), (it / NS) & 1);
+      PROF_ACC(p_wfull);
+      // packed words of this thread for all 8 slabs: 64-chunk t64, fragment lane, n16-tiles (2 jpair, 2 jpair + 1)
+      uint32_t w[kSlabs][WPT];
+#pragma unroll
+      for (int r = 0; r < kSlabs; ++r) {
+        if (BITS == 4) {
+          const uint2 v = *reinterpret_cast<const uint2*>(wsm + s * Cfg::W_STAGE_BYTES + r * Cfg::W_ROW_BYTES);
+          w[r][0] = v.x; w[r][1] = v.y;
+        } else {
+          const uint4 v = *reinterpret_cast<const uint4*>(wsm + s * Cfg::W_STAGE_BYTES + r * Cfg::W_ROW_BYTES);
+          w[r][0] = v.x; w[r][1] = v.y; w[r][2] = v.z; w[r][3] = v.w;
+        }
+      }
+      // scale_perm (gptq_marlin.py:30-33): position 8 c + b' of a 64-chunk holds column c + 8 b'; this thread needs
+      // b' = 4 jpair .. 4 jpair + 3  ->  one 8-byte read of the scale row the producer staged with the weights
+      uint32_t s2[4] = {0, 0, 0, 0};  // broadcast scales for (jj, b): index 2 jj + b
+      auto load_scales = [&](int row) {
+        const uint2 raw = *reinterpret_cast<const uint2*>(ssm + s * Cfg::S_STAGE_BYTES + row * 256);
+        s2[0] = bcast16(raw.x);
+        s2[1] = bcast16_hi(raw.x);
+        s2[2] = bcast16(raw.y);
+        s2[3] = bcast16_hi(raw.y);
+      };
+      if (GM == kGroup128) load_scales(0);
+      PROF_ACC(p_lds);
+#pragma unroll
+      for (int sub = 0; sub < 2; ++sub) {
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+          uint32_t ov[16];   // 4 slabs x 4 registers of the n16-tile jj
+#pragma unroll
+          for (int rr = 0; rr < 4; ++rr) {
+            const int r = sub * 4 + rr;
+            if (GM == kGroupSmall && (r & ((1 << lspg) - 1)) == 0) load_scales(r >> lspg);
+            uint32_t* o4 = &ov[4 * rr];
+            if (BITS == 4) dequant4<T>(w[r][jj], o4);
+            else dequant8<T>(w[r][2 * jj], w[r][2 * jj + 1], o4);
+            if (GM != kChannelwise) {
+              o4[0] = Pack2<T>::mul(o4[0], s2[2 * jj]);
+              o4[1] = Pack2<T>::mul(o4[1], s2[2 * jj + 1]);
+              o4[2] = Pack2<T>::mul(o4[2], s2[2 * jj]);
+              o4[3] = Pack2<T>::mul(o4[3], s2[2 * jj + 1]);
+            }
+          }
+          PROF_ACC(p_deq);
+          if (jj == 0) {
+            mbar_wait(aempty_bar(o, sub), (jc & 1) ^ 1);
+            PROF_ACC(p_waempty);
+            tc_fence_after();
+          }
+          tmem_st_16x128b_x8(a_col + ((uint32_t)(16 * jj) << 16) + sub * 32, ov);
+        }
+        tc_wait_st();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(afull_bar(o, sub));
+        PROF_ACC(p_st);
+      }
+      if (lane == 0) mbar_arrive(empty_bar(s));  // smem slot consumed (values are in registers and have been used)
+    }
+    if (args.prof && warp == kDequantWarp0 && lane == 0) {
+      long long* q = args.prof + blockIdx.x * 16; q[6] = p_wfull; q[7] = p_lds; q[8] = p_waempty; q[9] = p_deq; q[10] = p_st;
+    }
+  } else if (warp >= Cfg::EPI_WARP0) {
+    // ================= epilogue: TMEM -> registers -> global (direct, split-K partial, or owner-side reduce) ==========
+    const int qd = warp & 3;
+    const int row = 32 * qd + lane;  // output channel within the tile == TMEM lane
+    const int et = threadIdx.x - Cfg::EPI_WARP0 * 32;  // 0..127
+    constexpr bool kPrefetch = MPAD <= 32;   // the owner sums the other CTAs' partials into registers ahead of its MMAs
+    constexpr int NCH = MPAD / 16;
+    pdl_wait();   // C, the partial slots and the tile counters may still be in use by the previous kernel
+    long long p_mark = args.prof ? clock64() : 0, p_wacc = 0, p_epi = 0, p_red = 0;
+    uint32_t uo[NOWN];
+#pragma unroll
+    for (int o = 0; o < NOWN; ++o) uo[o] = 0;
+    for (int u = u_begin; u < u_end;) {
+      const int tile = u / KS, ks0 = u - tile * KS;
+      const int len = min(KS - ks0, u_end - u);
+      const int it0 = u - u_begin, it1 = it0 + len;
+      const int nt = tile % args.n_tiles, mc = tile / args.n_tiles;
+      const int n = nt * kTileN + row;
+      const int m0 = mc * MPAD;
+      const int m_valid = min(MPAD, args.M - m0);
+      const bool n_ok = n < args.N;
+      const bool full_k = (ks0 == 0 && len == KS);
+      const bool owner = (ks0 == 0 && !full_k);   // this CTA reduces the tile; the others only contribute
+      T* cdst = reinterpret_cast<T*>(args.C) + (size_t)m0 * args.N + n;
+      float* part_dst = args.scratch + (size_t)blockIdx.x * (kTileN * MPAD);
+      int n_other = 0;
+      float psum[kPrefetch ? MPAD : 1];
+      if (owner) {
+        // contributors are the CTAs after this one whose unit ranges intersect [tile*KS, (tile+1)*KS); for each of them
+        // the tile is the first segment of its range, so its partial sits in its slot
+        n_other = part.owner(tile * KS + KS - 1) - (int)blockIdx.x;
+        if (et == 0) {
+          while (ld_acquire_gpu(&args.counters[tile]) < n_other) {}
+          args.counters[tile] = 0;   // self-reset: exactly n_other increments ever arrive
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        __threadfence();
+        if constexpr (kPrefetch) {
+#pragma unroll
+          for (int j = 0; j < MPAD; ++j) psum[j] = 0.f;
+          for (int b = 1; b <= n_other; ++b) {
+            const float* src = args.scratch + (size_t)(blockIdx.x + b) * (kTileN * MPAD) + row;
+#pragma unroll
+            for (int j = 0; j < MPAD; ++j)
+              if (j < m_valid) psum[j] += __ldcg(src + j * kTileN);
+          }
+        }
+        PROF_ACC(p_red);
+      }
+      float ch_scale = 1.f;
+      if (GM == kChannelwise && n_ok)
+        ch_scale = to_f32<T>(reinterpret_cast<const T*>(args.scales)[(n & ~31) + scale_single_pos(n & 31)]);
+
+      bool part_o[NOWN];
+      uint32_t acc_addr[NOWN];
+#pragma unroll
+      for (int o = 0; o < NOWN; ++o) {
+        const int hu0 = 2 * it0 + ((o - 2 * it0) & (NOWN - 1));
+        part_o[o] = hu0 < 2 * it1;
+        const int ab = uo[o] % NBUF;
+        acc_addr[o] = tmem_base + ((uint32_t)(32 * qd) << 16) + Cfg::ACC_COL0 + (o * NBUF + ab) * MPAD;
+        if (part_o[o]) mbar_wait(accfull_bar(o, ab), (uo[o] / NBUF) & 1);
+      }
+      PROF_ACC(p_wacc);
+      tc_fence_after();
+#pragma unroll
+      for (int ch = 0; ch < NCH; ++ch) {
+        const int j0 = ch * 16;
+        if (j0 < m_valid) {
+          float v[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] = 0.f;
+#pragma unroll
+          for (int o = 0; o < NOWN; ++o) {
+            if (part_o[o]) {
+              uint32_t t[16];
+              tmem_ld_32x32b_x16(acc_addr[o] + j0, t);
+              tc_wait_ld();
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] += __uint_as_float(t[j]);
+            }
+          }
+          if (full_k || owner) {
+            if (owner) {
+              if constexpr (kPrefetch) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] += psum[j0 + j];
+              } else {
+                for (int b = 1; b <= n_other; ++b) {
+                  const float* src = args.scratch + (size_t)(blockIdx.x + b) * (kTileN * MPAD) + j0 * kTileN + row;
+#pragma unroll
+                  for (int j = 0; j < 16; ++j)
+                    if (j0 + j < m_valid) v[j] += __ldcg(src + j * kTileN);
+                }
+              }
+            }
+            if (n_ok) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                if (j0 + j < m_valid) cdst[(size_t)(j0 + j) * args.N] = from_f32<T>(v[j] * ch_scale);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (j0 + j < m_valid) part_dst[(j0 + j) * kTileN + row] = v[j];
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+#pragma unroll
+      for (int o = 0; o < NOWN; ++o) {
+        if (part_o[o]) {
+          if (lane == 0) mbar_arrive(accempty_bar(o, uo[o] % NBUF));
+          ++uo[o];
+        }
+      }
+      if (!full_k && !owner) {
+        __threadfence();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (et == 0) atomicAdd(&args.counters[tile], 1);
+      }
+      u += len;
+      PROF_ACC(p_epi);
+    }
+    if (args.prof && et == 0) { long long* q = args.prof + blockIdx.x * 16; q[13] = p_wacc; q[14] = p_epi; q[15] = p_red; }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (args.prof && threadIdx.x == 0) { args.prof[blockIdx.x * 16 + 11] = clock64() - k_t0; args.prof[blockIdx.x * 16 + 12] = n_units; }
+  if (warp == kAllocWarp) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+}
+
+// ---- host side: one launch ---------------------------------------------------------------------------------------
+struct GemmScratch {
+  float* partials;
+  int* counters;
+};
+int gemm_ensure_scratch(int dev, size_t partial_floats, int counter_ints, cudaStream_t st, GemmScratch* out);  // marlin_gemm.cu
+
+template <typename T, int MPAD, int BITS, int GM>
+int launch_gemm(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t st) {
+  using Cfg = GemmCfg<MPAD, BITS>;
+  GemmArgs a = a_in;
+  a.m_chunks = (a.M + MPAD - 1) / MPAD;
+  const int tiles = a.n_tiles * a.m_chunks;
+  a.total_units = tiles * a.KS;
+  int grid = num_sms();
+  if (grid > a.total_units) grid = a.total_units;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  GemmScratch sc;
+  if (int e = gemm_ensure_scratch(dev, (size_t)grid * kTileN * MPAD, tiles, st, &sc)) return e;
+  a.scratch = sc.partials;
+  a.counters = sc.counters;
+  CUtensorMap tmap_a, tmap_w, tmap_s;
+  const CUtensorMapDataType dt = std::is_same<T, __half>::value ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  // activations [M, K] (row pitch lda) as {64, M, K/64}: one box = 4 chunks of 64 (k) x MPAD rows, 128-byte swizzle,
+  // rows beyond M and chunks beyond K read as zero
+  bool ok = make_tmap_act3d(&tmap_a, A, dt, (uint64_t)a.M, (uint64_t)a.K, (uint64_t)lda * 2, MPAD, kStageK / 64);
+  // packed weights [K/16, N*16*BITS/8 bytes] viewed as 8-byte elements: box = 16 slabs x one 128-column tile
+  const uint64_t wrow_bytes = (uint64_t)a.N * 16 * BITS / 8;
+  ok = ok && make_tmap_2d(&tmap_w, a.B, CU_TENSOR_MAP_DATA_TYPE_UINT64, 8, (uint64_t)a.K / 16, wrow_bytes / 8, wrow_bytes,
+                          kStageK / 16, Cfg::W_ROW_BYTES / 8, CU_TENSOR_MAP_SWIZZLE_NONE);
+  // group scales [num_groups, N]: box = (scale rows of one stage) x 128 columns
+  if (GM != kChannelwise)
+    ok = ok && make_tmap_2d(&tmap_s, a.scales, dt, 2, (uint64_t)a.num_groups, (uint64_t)a.N, (uint64_t)a.N * 2,
+                            (uint32_t)a.groups_per_stage, kTileN, CU_TENSOR_MAP_SWIZZLE_NONE);
+  else
+    tmap_s = tmap_a;
+  if (!ok)
+    return set_error(B200_ECUDA, "marlin gemm: cuTensorMapEncodeTiled failed (A=%p M=%d K=%d N=%d lda=%lld)", A, a.M, a.K,
+                     a.N, (long long)lda);
+  auto kern = marlin_gemm_kernel<T, MPAD, BITS, GM>;
+  static bool attr_set[64] = {};
+  if (!attr_set[dev & 63]) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    attr_set[dev & 63] = true;
+  }
+  static const bool prof_on = getenv("B200_GEMM_PROF") != nullptr;
+  a.prof = nullptr;
+  if (prof_on) { cudaMallocManaged(&a.prof, sizeof(long long) * 16 * grid); cudaMemset(a.prof, 0, sizeof(long long) * 16 * grid); }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(Cfg::THREADS);
+  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmap_a, tmap_w, tmap_s, a);
+  if (e != cudaSuccess) return set_error(B200_ECUDA, "marlin gemm launch: %s", cudaGetErrorString(e));
+  if (prof_on) {
+    cudaDeviceSynchronize();
+    static const char* names[16] = {"-", "-", "mma.wait_accempty", "mma.wait_full", "mma.wait_afull", "mma.issue",
+                                    "deq.wait_full", "deq.lds", "deq.wait_aempty", "deq.compute", "deq.st", "cta.total", "cta.units",
+                                    "epi.wait_accfull", "epi.work", "epi.reduce_prefetch"};
+    fprintf(stderr, "[gemm prof] M=%d N=%d K=%d MPAD=%d grid=%d stages=%d:", a.M, a.N, a.K, MPAD, grid, Cfg::NSTAGES);
+    for (int i = 2; i < 16; ++i) {
+      double sum = 0, mx = 0;
+      for (int b = 0; b < grid; ++b) { sum += (double)a.prof[b * 16 + i]; if ((double)a.prof[b * 16 + i] > mx) mx = (double)a.prof[b * 16 + i]; }
+      fprintf(stderr, " %s=%.0f(max %.0f)", names[i], sum / grid, mx);
+    }
+    fprintf(stderr, "\n");
+    cudaFree(a.prof);
+  }
+  return B200_OK;
+}
+
+template <typename T, int BITS, int GM>
+int dispatch_mpad(const GemmArgs& a, const void* A, int64_t lda, cudaStream_t st) {
+  if (a.M <= 16) return launch_gemm<T, 16, BITS, GM>(a, A, lda, st);
+  if (a.M <= 32) return launch_gemm<T, 32, BITS, GM>(a, A, lda, st);
+  if (a.M <= 64) return launch_gemm<T, 64, BITS, GM>(a, A, lda, st);
+  return launch_gemm<T, 128, BITS, GM>(a, A, lda, st);
+}
+
+// one translation unit per (T, BITS): marlin_gemm_inst_*.cu
+template <typename T, int BITS>
+int dispatch_gemm(const GemmArgs& a, const void* A, int64_t lda, cudaStream_t st) {
+  if (a.groups_per_stage == 0) return dispatch_mpad<T, BITS, kChannelwise>(a, A, lda, st);
+  if (a.groups_per_stage == 2) return dispatch_mpad<T, BITS, kGroup128>(a, A, lda, st);
+  return dispatch_mpad<T, BITS, kGroupSmall>(a, A, lda, st);
+}
+int dispatch_gemm_f16_4(const GemmArgs& a, const void* A, int64_t lda, cudaStream_t st);
+int dispatch_gemm_f16_8(const GemmArgs& a, const void* A, int64_t lda, cudaStream_t st);
+int dispatch_gemm_bf16_4(const GemmArgs& a, const void* A, int64_t lda, cudaStream_t st);
+int dispatch_gemm_bf16_8(const GemmArgs& a, const void* A, int64_t lda, cudaStream_t st);
+
+}  // namespace b200
