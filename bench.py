@@ -39,6 +39,8 @@ def parse():
     p.add_argument("--layers", type=int, default=None, help="debug: truncate the model (makes the number INVALID)")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--sweep", action="store_true", help="also report tok/s at batch 1,2,4,8,16,32 (extra key)")
+    p.add_argument("--profile-step", action="store_true",
+                   help="bracket ONE extra decode step with cudaProfilerStart/Stop (use with ncu --profile-from-start off)")
     return p.parse_args()
 
 
@@ -253,6 +255,12 @@ def run_b200(a):
     e1.record()
     barrier()
     t_dev = e0.elapsed_time(e1) * 1e-3
+    if a.profile_step:
+        torch.cuda.synchronize()
+        torch.cuda.cudart().cudaProfilerStart()
+        eng.run_device()
+        torch.cuda.synchronize()
+        torch.cuda.cudart().cudaProfilerStop()
     # ---- end to end: pinned host inputs in, sampled ids out, every step -------------------------------------------
     his = [eng.host_inputs(a.ctx, seed=10 + i) for i in range(4)]
     for i in range(3):
