@@ -136,6 +136,7 @@ extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_
   ga.total_units = 0;
   ga.groups_per_stage = num_groups > 1 ? kStageK / gs : 0;
   ga.prof = nullptr;
+  ga.cluster_s = 0;
   int rc;
   if (dtype == B200_F16) rc = (num_bits == 4) ? dispatch_gemm_f16_4(ga, a, lda, st) : dispatch_gemm_f16_8(ga, a, lda, st);
   else rc = (num_bits == 4) ? dispatch_gemm_bf16_4(ga, a, lda, st) : dispatch_gemm_bf16_8(ga, a, lda, st);

@@ -36,6 +36,7 @@
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tma_host.cuh"
+#include "streamk.cuh"
 #include <stdlib.h>
 #include <type_traits>
 
@@ -90,17 +91,8 @@ struct GemmArgs {
   int n_tiles, m_chunks, KS;   // KS = ceil(K / kStageK)
   int total_units;
   int groups_per_stage;        // scale rows staged per stage: 0 (channelwise), 2, 4 or 8
+  int cluster_s;               // > 1: each tile's K range is split over a cluster of this many CTAs (DSMEM reduce)
   long long* prof;             // bring-up cycle counters [grid][16] (B200_GEMM_PROF), nullptr in production
-};
-
-struct Partition {
-  int q, r;
-  __device__ __forceinline__ Partition(int total, int g) : q(total / g), r(total % g) {}
-  __device__ __forceinline__ int start(int b) const { return b * q + min(b, r); }
-  __device__ __forceinline__ int owner(int u) const {
-    const int big = r * (q + 1);
-    return u < big ? u / (q + 1) : r + (u - big) / q;
-  }
 };
 
 // ---- dequantisation ------------------------------------------------------------------------------------------
@@ -286,10 +278,20 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
   __syncthreads();            // barriers are live: the producers start streaming weights right away
   pdl_launch_dependents();    // the next kernel of the stream may start its own prologue now
 
-  const Partition part(args.total_units, gridDim.x);
-  const int u_begin = part.start(blockIdx.x), u_end = part.start(blockIdx.x + 1);
-  const int n_units = u_end - u_begin;
+  // two work decompositions:
+  //   stream-K (cluster_s <= 1): the (tile, k-stage) space is cut into one contiguous range per CTA; shared tiles are
+  //     reduced through global scratch by the CTA that owns the tile's first stage;
+  //   cluster split-K (cluster_s = S > 1, used when there are fewer tiles than SMs): tile = blockIdx / S, the S CTAs of
+  //     one cluster take consecutive K slices of it and reduce through distributed shared memory -- no global round trip.
   const int KS = args.KS;
+  const int CS = args.cluster_s;
+  const bool clustered = CS > 1;
+  const int c_rank = clustered ? (int)cluster_ctarank() : 0;
+  const Partition part(clustered ? KS : args.total_units, clustered ? CS : (int)gridDim.x);
+  const int u_base = clustered ? (int)(blockIdx.x / CS) * KS : 0;
+  const int u_begin = u_base + part.start(clustered ? c_rank : (int)blockIdx.x);
+  const int u_end = u_base + part.start((clustered ? c_rank : (int)blockIdx.x) + 1);
+  const int n_units = u_end - u_begin;
   const int gps = args.groups_per_stage;
 
   if (warp < kNumProducers) {
@@ -507,7 +509,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       const int m_valid = min(MPAD, args.M - m0);
       const bool n_ok = n < args.N;
       const bool full_k = (ks0 == 0 && len == KS);
-      const bool owner = (ks0 == 0 && !full_k);   // this CTA reduces the tile; the others only contribute
+      const bool owner = (ks0 == 0 && !full_k && !clustered);   // this CTA reduces the tile; the others only contribute
       T* cdst = reinterpret_cast<T*>(args.C) + (size_t)m0 * args.N + n;
       float* part_dst = args.scratch + (size_t)blockIdx.x * (kTileN * MPAD);
       int n_other = 0;
@@ -586,6 +588,13 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
               for (int j = 0; j < 16; ++j)
                 if (j0 + j < m_valid) cdst[(size_t)(j0 + j) * args.N] = from_f32<T>(v[j] * ch_scale);
             }
+          } else if (clustered) {
+            // partial of this CTA's K slice -> own shared memory (the activation ring is dead once the last MMA of the
+            // segment has completed), laid out [m][128 channels]
+            float* red = reinterpret_cast<float*>(smem_gen + (act_base - smem_base));
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (j0 + j < m_valid) red[(j0 + j) * kTileN + row] = v[j];
           } else {
 #pragma unroll
             for (int j = 0; j < 16; ++j)
@@ -602,7 +611,17 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
           ++uo[o];
         }
       }
-      if (!full_k && !owner) {
+      if (clustered && !full_k) {
+        // cluster barrier 1: every CTA's partial is in its shared memory; rank r then finishes rows m = r, r + S, ...
+        cluster_arrive();
+        cluster_wait();
+        const uint32_t red_u32 = act_base + (uint32_t)row * 4u;
+        for (int m = c_rank; m < m_valid; m += CS) {
+          float acc = 0.f;
+          for (int c = 0; c < CS; ++c) acc += ld_dsmem_f32(mapa(red_u32 + (uint32_t)m * (kTileN * 4u), (uint32_t)c));
+          if (n_ok) cdst[(size_t)m * args.N] = from_f32<T>(acc * ch_scale);
+        }
+      } else if (!full_k && !owner) {
         __threadfence();
         asm volatile("bar.sync 1, 128;" ::: "memory");
         if (et == 0) atomicAdd(&args.counters[tile], 1);
@@ -613,6 +632,16 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     if (args.prof && et == 0) { long long* q = args.prof + blockIdx.x * 16; q[13] = p_wacc; q[14] = p_epi; q[15] = p_red; }
   }
 
+  if (clustered) {
+    // the epilogue warps passed barrier 1 above; barrier 2 keeps every CTA's shared memory alive until all ranks have
+    // finished reading it
+    if (warp < Cfg::EPI_WARP0) {
+      cluster_arrive();
+      cluster_wait();
+    }
+    cluster_arrive();
+    cluster_wait();
+  }
   tc_fence_before();
   __syncthreads();
   if (args.prof && threadIdx.x == 0) { args.prof[blockIdx.x * 16 + 11] = clock64() - k_t0; args.prof[blockIdx.x * 16 + 12] = n_units; }
@@ -620,12 +649,6 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
 }
 
 // ---- host side: one launch ---------------------------------------------------------------------------------------
-struct GemmScratch {
-  float* partials;
-  int* counters;
-};
-int gemm_ensure_scratch(int dev, size_t partial_floats, int counter_ints, cudaStream_t st, GemmScratch* out);  // marlin_gemm.cu
-
 template <typename T, int MPAD, int BITS, int GM>
 int launch_gemm(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t st) {
   using Cfg = GemmCfg<MPAD, BITS>;
@@ -635,8 +658,48 @@ int launch_gemm(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t s
   a.total_units = tiles * a.KS;
   int grid = num_sms();
   if (grid > a.total_units) grid = a.total_units;
+  // fewer tiles than SMs: split each tile's K range over a cluster (<= 8 CTAs) instead of stream-K with global fixups
+  a.cluster_s = 0;
+  static const int no_cluster = getenv("B200_GEMM_NO_CLUSTER") ? atoi(getenv("B200_GEMM_NO_CLUSTER")) : 0;
+  auto kern = marlin_gemm_kernel<T, MPAD, BITS, GM>;
   int dev = 0;
   cudaGetDevice(&dev);
+  static bool attr_set[64] = {};
+  if (!attr_set[dev & 63]) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    attr_set[dev & 63] = true;
+  }
+  if (!no_cluster && a.m_chunks == 1 && tiles * 2 <= num_sms()) {
+    // largest cluster size whose clusters are all co-resident (GPC boundaries limit this: 45 clusters of 3 on B200)
+    static int max_active[64][9] = {};
+    int cs = num_sms() / tiles;
+    if (cs > 8) cs = 8;
+    if (cs > a.KS) cs = a.KS;
+    for (; cs > 1; --cs) {
+      int& ma = max_active[dev & 63][cs];
+      if (ma == 0) {
+        cudaLaunchConfig_t q = {};
+        q.gridDim = dim3(cs * 64);
+        q.blockDim = dim3(Cfg::THREADS);
+        q.dynamicSmemBytes = Cfg::SMEM_BYTES;
+        cudaLaunchAttribute qa[1];
+        qa[0].id = cudaLaunchAttributeClusterDimension;
+        qa[0].val.clusterDim.x = (unsigned)cs;
+        qa[0].val.clusterDim.y = 1;
+        qa[0].val.clusterDim.z = 1;
+        q.attrs = qa;
+        q.numAttrs = 1;
+        int n = 0;
+        if (cudaOccupancyMaxActiveClusters(&n, kern, &q) != cudaSuccess) { cudaGetLastError(); n = -1; }
+        ma = n > 0 ? n : -1;
+      }
+      if (ma >= tiles) break;
+    }
+    if (cs > 1) {
+      a.cluster_s = cs;
+      grid = tiles * cs;
+    }
+  }
   GemmScratch sc;
   if (int e = gemm_ensure_scratch(dev, (size_t)grid * kTileN * MPAD, tiles, st, &sc)) return e;
   a.scratch = sc.partials;
@@ -659,12 +722,6 @@ int launch_gemm(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t s
   if (!ok)
     return set_error(B200_ECUDA, "marlin gemm: cuTensorMapEncodeTiled failed (A=%p M=%d K=%d N=%d lda=%lld)", A, a.M, a.K,
                      a.N, (long long)lda);
-  auto kern = marlin_gemm_kernel<T, MPAD, BITS, GM>;
-  static bool attr_set[64] = {};
-  if (!attr_set[dev & 63]) {
-    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
-    attr_set[dev & 63] = true;
-  }
   static const bool prof_on = getenv("B200_GEMM_PROF") != nullptr;
   a.prof = nullptr;
   if (prof_on) { cudaMallocManaged(&a.prof, sizeof(long long) * 16 * grid); cudaMemset(a.prof, 0, sizeof(long long) * 16 * grid); }
@@ -673,11 +730,22 @@ int launch_gemm(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t s
   cfg.blockDim = dim3(Cfg::THREADS);
   cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (pdl_enabled()) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (a.cluster_s > 1) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = (unsigned)a.cluster_s;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cfg.numAttrs = na;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmap_a, tmap_w, tmap_s, a);
   if (e != cudaSuccess) return set_error(B200_ECUDA, "marlin gemm launch: %s", cudaGetErrorString(e));
   if (prof_on) {
