@@ -1,0 +1,328 @@
+// Sparse-Marlin (2:4) W4A16 / W8A16 GEMM for sm_100a:  C[M,N] = A[M,K] . W24,  W stored compressed (2 of every 4 along K)
+//
+// Replaces gptq_marlin_24_gemm of the reference (csrc/quantization/marlin/sparse/marlin_24_cuda_kernel.cu:1017-1125 op,
+// :111-856 kernel).  The STORED layouts are the reference's: b_q_weight [K/32, N*16/pf] int32 in the Marlin-24 tile order
+// (marlin_24_perms.py:11-36), b_meta int16 [K/32, 2N] = the CUTLASS sm80 reordered 2-bit indices reinterpreted
+// (marlin_utils.py:161-162, format_24.py:21-46), scales [K/128 or 1, N] permuted in 64-chunks (marlin_24_perms.py:37-43).
+// What those layouts mean for one warp (derived in DESIGN.md "Sparse-Marlin operand map"):
+//   * one (k32 block kb, 64-column tile t) of weights is 32 lanes x 4 int32 (4-bit) / 8 int32 (8-bit); int32 jj of lane
+//     l = 4 col + q dequantises DIRECTLY into the sparse-A registers {a0,a1,a2,a3} of mma.sp m16n8k32 for the 16 output
+//     channels n = 64 t + 8 col' + jj (+4 for rows 8..15), compressed k = {2q,2q+1,2q+8,2q+9};
+//   * the metadata register of lane l for the instruction pair jj in {2h, 2h+1} is the 32-bit word
+//     b_meta32[kb][64 t + 32 h + l], used with sparsity selector jj % 2;
+//   * the two group scales of (jj, rows 0-7 / 8-15) are the adjacent halves 8 col + 2 jj, +1 of the permuted scale row.
+// So the compressed operand goes straight from global memory into the sparse tensor-core instruction: no shared-memory
+// staging of weights, no shuffles.
+//
+// Work decomposition (HBM-bound, M <= 64 per pass): many small CTAs instead of a deep async pipeline.  CTA = (64-column
+// tile, K split s of S); its 8 warps take the k32 blocks of the split round-robin, each streaming its 512 B weight +
+// 256 B metadata rows with a 4-deep register prefetch (ld.global.nc, L1 bypass); 4-6 CTAs are resident per SM.  Warp
+// partials are summed in shared memory; K splits are summed through fp32 slots in CTA order by the last split to arrive
+// (atomic ticket): deterministic, nobody spins.  NOTE this kernel uses the warp-level sparse MMA (HMMA.SP); feeding
+// tcgen05.mma.sp from TMEM is the planned next step.
+#include "marlin_gemm_kernel.cuh"
+
+namespace b200 {
+namespace m24 {
+
+constexpr int kWarps = 8;
+constexpr int kThreads = kWarps * 32;
+constexpr int kPrefetch = 4;
+
+struct Args {
+  const __half* A;
+  const uint32_t* Bq;
+  const uint32_t* meta;
+  const __half* scales;
+  __half* C;
+  float* scratch;
+  int* counters;
+  int M, N, K;
+  int64_t lda;
+  int num_groups;   // 1 = channelwise
+  int splits;       // K splits per tile
+  int kb_per_split; // k32 blocks per split (last split may be shorter)
+  int n_tiles;
+};
+
+__device__ __forceinline__ uint4 ldg_stream(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ uint32_t ldg_stream32(const void* p) {
+  uint32_t v;
+  asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+
+template <int SEL>
+__device__ __forceinline__ void mma_sp(float* c, const uint32_t* a, const uint32_t* b, uint32_t e) {
+  asm volatile(
+      "mma.sp::ordered_metadata.sync.aligned.m16n8k32.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, "
+      "{%8,%9,%10,%11}, {%0,%1,%2,%3}, %12, %13;"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]), "r"(b[2]), "r"(b[3]), "r"(e), "n"(SEL));
+}
+
+template <int BITS>
+struct Stage {
+  uint32_t w[BITS == 4 ? 4 : 8];
+  uint32_t e[2];
+  uint32_t s[4];
+};
+
+}  // namespace m24
+
+template <int BITS, int MB, bool GROUPED>
+__global__ void __launch_bounds__(m24::kThreads)
+marlin24_gemm_kernel(const m24::Args args) {
+  using namespace m24;
+  constexpr int WPL = BITS == 4 ? 4 : 8;   // packed int32 per lane per (k32 block, 64-column tile)
+  constexpr int MC = 16 * MB;              // activation rows per pass
+  constexpr int NACC = 32 * MB;            // fp32 accumulators per thread
+  extern __shared__ __align__(16) uint8_t smem24[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int col = lane >> 2, q = lane & 3;
+  const int t = blockIdx.x / args.splits, sp = blockIdx.x - t * args.splits;
+  const int m0 = blockIdx.y * MC;
+  const int KB = args.K / 32;
+  const int kb0 = sp * args.kb_per_split;
+  const int kb1 = min(KB, kb0 + args.kb_per_split);
+  const int KR = args.kb_per_split * 32;
+  const int a_stride = KR + 8;             // halves per activation row in shared memory (+8: conflict-free fragment reads)
+  const int wrow = args.N * (BITS == 4 ? 2 : 4);
+  const int gblocks = GROUPED ? (args.K / args.num_groups) / 32 : 1;   // k32 blocks per scale group
+
+  const uint32_t* wp = args.Bq + (size_t)t * (32 * WPL) + lane * WPL;
+  const uint32_t* mp = args.meta + (size_t)t * 64 + lane;
+  const __half* sp_ptr = args.scales + (size_t)t * 64 + col * 8;
+
+  Stage<BITS> st[kPrefetch];
+  auto load_stage = [&](Stage<BITS>& s, int kb) {
+    if (kb < kb1) {
+      const uint32_t* w = wp + (size_t)kb * wrow;
+      const uint4 v0 = ldg_stream(w);
+      s.w[0] = v0.x; s.w[1] = v0.y; s.w[2] = v0.z; s.w[3] = v0.w;
+      if (BITS == 8) {
+        const uint4 v1 = ldg_stream(w + 4);
+        s.w[4 % WPL] = v1.x; s.w[5 % WPL] = v1.y; s.w[6 % WPL] = v1.z; s.w[7 % WPL] = v1.w;
+      }
+      s.e[0] = ldg_stream32(mp + (size_t)kb * args.N);
+      s.e[1] = ldg_stream32(mp + (size_t)kb * args.N + 32);
+      if (GROUPED) {
+        const uint4 sv = *reinterpret_cast<const uint4*>(sp_ptr + (size_t)(kb / gblocks) * args.N);
+        s.s[0] = sv.x; s.s[1] = sv.y; s.s[2] = sv.z; s.s[3] = sv.w;
+      }
+    }
+  };
+  // weights / metadata / scales do not depend on the previous kernel: start streaming before the PDL wait
+#pragma unroll
+  for (int u = 0; u < kPrefetch; ++u) load_stage(st[u], kb0 + warp + u * kWarps);
+  pdl_wait();
+  pdl_launch_dependents();
+
+  // activations of this split -> shared memory [MC][KR + 8] (rows beyond M are zero)
+  {
+    __half* sA = reinterpret_cast<__half*>(smem24);
+    const int vec_per_row = (kb1 - kb0) * 4;   // 16-byte vectors
+    for (int i = threadIdx.x; i < MC * vec_per_row; i += kThreads) {
+      const int r = i / vec_per_row, v = i - r * vec_per_row;
+      uint4 val = make_uint4(0, 0, 0, 0);
+      if (m0 + r < args.M) val = *reinterpret_cast<const uint4*>(args.A + (size_t)(m0 + r) * args.lda + (size_t)kb0 * 32 + v * 8);
+      *reinterpret_cast<uint4*>(sA + r * a_stride + v * 8) = val;
+    }
+  }
+  __syncthreads();
+
+  float acc[NACC];
+#pragma unroll
+  for (int i = 0; i < NACC; ++i) acc[i] = 0.f;
+  const uint32_t* sA32 = reinterpret_cast<const uint32_t*>(smem24);
+
+  auto compute = [&](const Stage<BITS>& s, int kb) {
+    const int kbl = kb - kb0;
+    uint32_t b[MB][2][4];
+#pragma unroll
+    for (int mb = 0; mb < MB; ++mb)
+#pragma unroll
+      for (int h = 0; h < 2; ++h)
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          b[mb][h][i] = sA32[(16 * mb + 8 * h + col) * (a_stride / 2) + kbl * 16 + q + 4 * i];
+#pragma unroll
+    for (int jj = 0; jj < 4; ++jj) {
+      uint32_t a[4];
+      if (BITS == 4) dequant4<__half>(s.w[jj], a);
+      else dequant8<__half>(s.w[(2 * jj) % WPL], s.w[(2 * jj + 1) % WPL], a);
+      if (GROUPED) {
+        const uint32_t s0 = bcast16(s.s[jj]), s1 = bcast16_hi(s.s[jj]);   // rows 0-7 (n), rows 8-15 (n + 4)
+        a[0] = Pack2<__half>::mul(a[0], s0);
+        a[2] = Pack2<__half>::mul(a[2], s0);
+        a[1] = Pack2<__half>::mul(a[1], s1);
+        a[3] = Pack2<__half>::mul(a[3], s1);
+      }
+      const uint32_t e = s.e[jj >> 1];
+#pragma unroll
+      for (int mb = 0; mb < MB; ++mb)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          float* c = &acc[((mb * 4 + jj) * 2 + h) * 4];
+          if (jj & 1) mma_sp<1>(c, a, b[mb][h], e);
+          else mma_sp<0>(c, a, b[mb][h], e);
+        }
+    }
+  };
+
+  for (int kb = kb0 + warp; kb < kb1; kb += kPrefetch * kWarps) {
+#pragma unroll
+    for (int u = 0; u < kPrefetch; ++u) {
+      const int k = kb + u * kWarps;
+      if (k < kb1) {
+        compute(st[u], k);
+        load_stage(st[u], k + kPrefetch * kWarps);
+      }
+    }
+  }
+  __syncthreads();   // activations are dead: the same shared memory becomes the cross-warp reduction buffer
+
+  // ---- sum the 8 warps' partials, un-permute into a [MC][64] tile ------------------------------------------------------
+  float* red = reinterpret_cast<float*>(smem24);
+  float* tile = red + kWarps * NACC * 32;
+#pragma unroll
+  for (int i = 0; i < NACC; ++i) red[(warp * NACC + i) * 32 + lane] = acc[i];
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < NACC * 32; idx += kThreads) {
+    const int a = idx >> 5, l = idx & 31;
+    float v = 0.f;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) v += red[(w * NACC + a) * 32 + l];
+    const int ci = a & 3, h = (a >> 2) & 1, jj = (a >> 3) & 3, mb = a >> 5;
+    const int n_local = 8 * (l >> 2) + jj + 4 * (ci >> 1);
+    const int m_local = 16 * mb + 8 * h + 2 * (l & 3) + (ci & 1);
+    tile[m_local * 64 + n_local] = v;
+  }
+  __syncthreads();
+
+  const int m_valid = min(MC, args.M - m0);
+  __half* cdst = args.C + (size_t)m0 * args.N + (size_t)t * 64;
+  auto finish = [&](int idx, float v) {
+    const int m = idx >> 6, n = idx & 63;
+    if (!GROUPED) v *= __half2float(args.scales[(size_t)t * 64 + n]);
+    cdst[(size_t)m * args.N + n] = __float2half_rn(v);
+  };
+  if (args.splits == 1) {
+    for (int idx = threadIdx.x; idx < m_valid * 64; idx += kThreads) finish(idx, tile[idx]);
+    return;
+  }
+  // ---- K splits: fp32 slots + ticket; the last split to arrive sums the slots in split order ------------------------------
+  __shared__ int s_last;
+  const int tile_id = blockIdx.y * args.n_tiles + t;
+  float* slots = args.scratch + (size_t)tile_id * args.splits * (MC * 64);
+  for (int idx = threadIdx.x; idx < m_valid * 64; idx += kThreads) __stcg(slots + (size_t)sp * (MC * 64) + idx, tile[idx]);
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int old = atomicAdd(&args.counters[tile_id], 1);
+    s_last = (old == args.splits - 1);
+    if (s_last) args.counters[tile_id] = 0;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  for (int idx = threadIdx.x; idx < m_valid * 64; idx += kThreads) {
+    float v = 0.f;
+    for (int s = 0; s < args.splits; ++s) v += __ldcg(slots + (size_t)s * (MC * 64) + idx);
+    finish(idx, v);
+  }
+}
+
+// ---- host side -------------------------------------------------------------------------------------------------------
+template <int BITS, int MB, bool GROUPED>
+static int launch_m24(m24::Args a, cudaStream_t st) {
+  using namespace m24;
+  constexpr int MC = 16 * MB;
+  const int KB = a.K / 32;
+  const int m_chunks = (a.M + MC - 1) / MC;
+  a.n_tiles = a.N / 64;
+  // enough CTAs for ~4 per SM; a split is at least 8 k32 blocks (one per warp) and a whole number of scale groups
+  const int target = num_sms() * 4;
+  int splits = (target + a.n_tiles * m_chunks - 1) / (a.n_tiles * m_chunks);
+  int min_kb = 8;
+  if (GROUPED) { const int gb = (a.K / a.num_groups) / 32; if (min_kb % gb) min_kb = ((min_kb + gb - 1) / gb) * gb; }
+  if (splits > KB / min_kb) splits = KB / min_kb;
+  if (splits < 1) splits = 1;
+  int kbps = (KB + splits - 1) / splits;
+  kbps = ((kbps + min_kb - 1) / min_kb) * min_kb;
+  if (kbps * 32 > 4096) kbps = 4096 / 32;      // bound the activation slab in shared memory (MC x 4096 halves)
+  splits = (KB + kbps - 1) / kbps;
+  a.splits = splits;
+  a.kb_per_split = kbps;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  GemmScratch sc;
+  if (int e = gemm_ensure_scratch(dev, (size_t)a.n_tiles * m_chunks * splits * MC * 64, a.n_tiles * m_chunks, st, &sc)) return e;
+  a.scratch = sc.partials;
+  a.counters = sc.counters;
+  const size_t a_bytes = (size_t)MC * (kbps * 32 + 8) * 2;
+  const size_t r_bytes = (size_t)(kWarps * 32 * MB * 32 + MC * 64) * 4;
+  const size_t smem = a_bytes > r_bytes ? a_bytes : r_bytes;
+  auto kern = marlin24_gemm_kernel<BITS, MB, GROUPED>;
+  static bool attr_set[64] = {};
+  if (!attr_set[dev & 63]) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    attr_set[dev & 63] = true;
+  }
+  cudaError_t e = launch_pdl(kern, dim3(a.n_tiles * splits, m_chunks), dim3(kThreads), smem, st, a);
+  if (e != cudaSuccess) return set_error(B200_ECUDA, "gptq_marlin_24_gemm launch: %s", cudaGetErrorString(e));
+  return B200_OK;
+}
+
+template <int BITS, bool GROUPED>
+static int dispatch_m24(const m24::Args& a, cudaStream_t st) {
+  if (a.M <= 16) return launch_m24<BITS, 1, GROUPED>(a, st);
+  if (a.M <= 32) return launch_m24<BITS, 2, GROUPED>(a, st);
+  return launch_m24<BITS, 4, GROUPED>(a, st);
+}
+
+}  // namespace b200
+
+extern "C" int b200_gptq_marlin_24_gemm(void* c, const void* a, const int32_t* b_q_weight, const int16_t* b_meta,
+                                        const void* b_scales, int32_t* workspace, int64_t workspace_numel, int num_bits,
+                                        int64_t size_m, int64_t size_n, int64_t size_k, int64_t lda, int num_groups,
+                                        int dtype, void* stream) {
+  using namespace b200;
+  (void)workspace;
+  // preconditions of the reference op (marlin_24_cuda_kernel.cu:1026-1115)
+  B200_CHECK(num_bits == 4 || num_bits == 8, "num_bits must be 4 or 8. Got = %d", num_bits);
+  B200_CHECK(dtype == B200_F16, "gptq_marlin_24_gemm only supports float16 activations (gptq_marlin_24.py:145-147)");
+  B200_CHECK(size_k % 128 == 0, "size_k = %lld is not divisible by tile_k_size = 128", (long long)size_k);
+  B200_CHECK(size_n % 128 == 0, "size_n = %lld is not divisible by tile_n_size = 128", (long long)size_n);
+  B200_CHECK(num_groups >= 1 && size_k % num_groups == 0, "size_k = %lld is not divisible by b_scales.size(0) = %d",
+             (long long)size_k, num_groups);
+  const int gs = (int)(size_k / num_groups);
+  if (num_groups > 1) B200_CHECK(gs == 128, "Unexpected group_size = %d (Sparse-Marlin supports -1 and 128)", gs);
+  B200_CHECK(workspace_numel >= (size_n / 128) * 64, "workspace.numel = %lld is below min_workspace_size = %lld",
+             (long long)workspace_numel, (long long)((size_n / 128) * 64));
+  B200_CHECK((reinterpret_cast<uintptr_t>(a) & 15) == 0 && (lda * 2) % 16 == 0, "A must be 16-byte aligned with a 16-byte multiple row pitch");
+  if (size_m == 0) return B200_OK;
+  m24::Args ga;
+  ga.A = reinterpret_cast<const __half*>(a);
+  ga.Bq = reinterpret_cast<const uint32_t*>(b_q_weight);
+  ga.meta = reinterpret_cast<const uint32_t*>(b_meta);
+  ga.scales = reinterpret_cast<const __half*>(b_scales);
+  ga.C = reinterpret_cast<__half*>(c);
+  ga.scratch = nullptr;
+  ga.counters = nullptr;
+  ga.M = (int)size_m; ga.N = (int)size_n; ga.K = (int)size_k;
+  ga.lda = lda;
+  ga.num_groups = num_groups;
+  ga.splits = 1; ga.kb_per_split = 0; ga.n_tiles = 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc;
+  if (num_groups > 1) rc = num_bits == 4 ? dispatch_m24<4, true>(ga, st) : dispatch_m24<8, true>(ga, st);
+  else rc = num_bits == 4 ? dispatch_m24<4, false>(ga, st) : dispatch_m24<8, false>(ga, st);
+  if (rc) return rc;
+  B200_LAUNCH_CHECK("gptq_marlin_24_gemm");
+  return B200_OK;
+}
