@@ -25,7 +25,7 @@
 namespace b200 {
 namespace m24 {
 
-constexpr int kWarps = 8;
+constexpr int kWarps = 4;
 constexpr int kThreads = kWarps * 32;
 constexpr int kPrefetch = 4;
 
@@ -74,8 +74,9 @@ struct Stage {
 
 }  // namespace m24
 
-template <int BITS, int MB, bool GROUPED>
-__global__ void __launch_bounds__(m24::kThreads)
+// NH = 8-row activation halves per 16-row block that carry real rows (1 when M <= 8: half the tensor-core work)
+template <int BITS, int MB, bool GROUPED, int NH>
+__global__ void __launch_bounds__(m24::kThreads, 4)
 marlin24_gemm_kernel(const m24::Args args) {
   using namespace m24;
   constexpr int WPL = BITS == 4 ? 4 : 8;   // packed int32 per lane per (k32 block, 64-column tile)
@@ -89,8 +90,6 @@ marlin24_gemm_kernel(const m24::Args args) {
   const int KB = args.K / 32;
   const int kb0 = sp * args.kb_per_split;
   const int kb1 = min(KB, kb0 + args.kb_per_split);
-  const int KR = args.kb_per_split * 32;
-  const int a_stride = KR + 8;             // halves per activation row in shared memory (+8: conflict-free fragment reads)
   const int wrow = args.N * (BITS == 4 ? 2 : 4);
   const int gblocks = GROUPED ? (args.K / args.num_groups) / 32 : 1;   // k32 blocks per scale group
 
@@ -122,34 +121,31 @@ marlin24_gemm_kernel(const m24::Args args) {
   pdl_wait();
   pdl_launch_dependents();
 
-  // activations of this split -> shared memory [MC][KR + 8] (rows beyond M are zero)
-  {
-    __half* sA = reinterpret_cast<__half*>(smem24);
-    const int vec_per_row = (kb1 - kb0) * 4;   // 16-byte vectors
-    for (int i = threadIdx.x; i < MC * vec_per_row; i += kThreads) {
-      const int r = i / vec_per_row, v = i - r * vec_per_row;
-      uint4 val = make_uint4(0, 0, 0, 0);
-      if (m0 + r < args.M) val = *reinterpret_cast<const uint4*>(args.A + (size_t)(m0 + r) * args.lda + (size_t)kb0 * 32 + v * 8);
-      *reinterpret_cast<uint4*>(sA + r * a_stride + v * 8) = val;
-    }
-  }
-  __syncthreads();
-
   float acc[NACC];
 #pragma unroll
   for (int i = 0; i < NACC; ++i) acc[i] = 0.f;
-  const uint32_t* sA32 = reinterpret_cast<const uint32_t*>(smem24);
+  // activation fragments come straight from global memory through L1 (every CTA of the SM re-reads the same few rows, so
+  // they stay L1/L2 resident); rows beyond M read as zero
+  const uint32_t* arow[MB][NH];
+  bool arow_ok[MB][NH];
+#pragma unroll
+  for (int mb = 0; mb < MB; ++mb)
+#pragma unroll
+    for (int h = 0; h < NH; ++h) {
+      const int m = m0 + 16 * mb + 8 * h + col;
+      arow_ok[mb][h] = m < args.M;
+      arow[mb][h] = reinterpret_cast<const uint32_t*>(args.A + (size_t)(arow_ok[mb][h] ? m : 0) * args.lda) + q;
+    }
 
   auto compute = [&](const Stage<BITS>& s, int kb) {
-    const int kbl = kb - kb0;
-    uint32_t b[MB][2][4];
+    uint32_t b[MB][NH][4];
 #pragma unroll
     for (int mb = 0; mb < MB; ++mb)
 #pragma unroll
-      for (int h = 0; h < 2; ++h)
+      for (int h = 0; h < NH; ++h)
 #pragma unroll
         for (int i = 0; i < 4; ++i)
-          b[mb][h][i] = sA32[(16 * mb + 8 * h + col) * (a_stride / 2) + kbl * 16 + q + 4 * i];
+          b[mb][h][i] = arow_ok[mb][h] ? __ldg(arow[mb][h] + kb * 16 + 4 * i) : 0u;
 #pragma unroll
     for (int jj = 0; jj < 4; ++jj) {
       uint32_t a[4];
@@ -166,7 +162,7 @@ marlin24_gemm_kernel(const m24::Args args) {
 #pragma unroll
       for (int mb = 0; mb < MB; ++mb)
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
+        for (int h = 0; h < NH; ++h) {
           float* c = &acc[((mb * 4 + jj) * 2 + h) * 4];
           if (jj & 1) mma_sp<1>(c, a, b[mb][h], e);
           else mma_sp<0>(c, a, b[mb][h], e);
@@ -184,7 +180,6 @@ marlin24_gemm_kernel(const m24::Args args) {
       }
     }
   }
-  __syncthreads();   // activations are dead: the same shared memory becomes the cross-warp reduction buffer
 
   // ---- sum the 8 warps' partials, un-permute into a [MC][64] tile ------------------------------------------------------
   float* red = reinterpret_cast<float*>(smem24);
@@ -238,23 +233,23 @@ marlin24_gemm_kernel(const m24::Args args) {
 }
 
 // ---- host side -------------------------------------------------------------------------------------------------------
-template <int BITS, int MB, bool GROUPED>
+template <int BITS, int MB, bool GROUPED, int NH>
 static int launch_m24(m24::Args a, cudaStream_t st) {
   using namespace m24;
   constexpr int MC = 16 * MB;
   const int KB = a.K / 32;
   const int m_chunks = (a.M + MC - 1) / MC;
   a.n_tiles = a.N / 64;
-  // enough CTAs for ~4 per SM; a split is at least 8 k32 blocks (one per warp) and a whole number of scale groups
+  // ~4 CTAs per SM; a split is at least 8 k32 blocks per warp (amortises the CTA prologue / reduction) and a whole
+  // number of scale groups
   const int target = num_sms() * 4;
-  int splits = (target + a.n_tiles * m_chunks - 1) / (a.n_tiles * m_chunks);
-  int min_kb = 8;
+  int splits = target / (a.n_tiles * m_chunks);
+  int min_kb = 8 * kWarps;
   if (GROUPED) { const int gb = (a.K / a.num_groups) / 32; if (min_kb % gb) min_kb = ((min_kb + gb - 1) / gb) * gb; }
   if (splits > KB / min_kb) splits = KB / min_kb;
   if (splits < 1) splits = 1;
   int kbps = (KB + splits - 1) / splits;
-  kbps = ((kbps + min_kb - 1) / min_kb) * min_kb;
-  if (kbps * 32 > 4096) kbps = 4096 / 32;      // bound the activation slab in shared memory (MC x 4096 halves)
+  if (GROUPED) { const int gb = (a.K / a.num_groups) / 32; kbps = ((kbps + gb - 1) / gb) * gb; }
   splits = (KB + kbps - 1) / kbps;
   a.splits = splits;
   a.kb_per_split = kbps;
@@ -264,10 +259,8 @@ static int launch_m24(m24::Args a, cudaStream_t st) {
   if (int e = gemm_ensure_scratch(dev, (size_t)a.n_tiles * m_chunks * splits * MC * 64, a.n_tiles * m_chunks, st, &sc)) return e;
   a.scratch = sc.partials;
   a.counters = sc.counters;
-  const size_t a_bytes = (size_t)MC * (kbps * 32 + 8) * 2;
-  const size_t r_bytes = (size_t)(kWarps * 32 * MB * 32 + MC * 64) * 4;
-  const size_t smem = a_bytes > r_bytes ? a_bytes : r_bytes;
-  auto kern = marlin24_gemm_kernel<BITS, MB, GROUPED>;
+  const size_t smem = (size_t)(kWarps * 32 * MB * 32 + MC * 64) * 4;
+  auto kern = marlin24_gemm_kernel<BITS, MB, GROUPED, NH>;
   static bool attr_set[64] = {};
   if (!attr_set[dev & 63]) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
@@ -280,9 +273,9 @@ static int launch_m24(m24::Args a, cudaStream_t st) {
 
 template <int BITS, bool GROUPED>
 static int dispatch_m24(const m24::Args& a, cudaStream_t st) {
-  if (a.M <= 16) return launch_m24<BITS, 1, GROUPED>(a, st);
-  if (a.M <= 32) return launch_m24<BITS, 2, GROUPED>(a, st);
-  return launch_m24<BITS, 4, GROUPED>(a, st);
+  if (a.M <= 8) return launch_m24<BITS, 1, GROUPED, 1>(a, st);
+  if (a.M <= 16) return launch_m24<BITS, 1, GROUPED, 2>(a, st);
+  return launch_m24<BITS, 2, GROUPED, 2>(a, st);   // M > 32: passes of 32 rows (grid.y), weights re-read through L2
 }
 
 }  // namespace b200
