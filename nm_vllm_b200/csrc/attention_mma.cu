@@ -19,6 +19,7 @@
 // caller's buffers, merged by the same reduce kernel as the generic path).
 #include "common.cuh"
 #include <stdlib.h>
+#include <type_traits>
 
 namespace b200 {
 namespace amma {
@@ -61,16 +62,41 @@ __device__ __forceinline__ uint32_t ldg32(const void* p) {
   return v;
 }
 
+// four fp8 bytes (little endian v0..v3) -> {half2(v0,v1), half2(v2,v3)}: exact (every e4m3 / e5m2 value is an fp16 value).
+// With an fp8 cache the MMAs run in fp16 whatever the query dtype: K and V need no further conversion, kv_scale is folded
+// into the softmax scale (K) and the final normalisation (V), Q and P are converted once per page.  The reference rounds
+// k * kv_scale to the query dtype before the dot product (quant_utils.cuh:294-360); the difference is one rounding.
+template <int KV>
+__device__ __forceinline__ void fp8x4_to_h2(uint32_t v, uint32_t& lo, uint32_t& hi) {
+  const __half2_raw h01 = __nv_cvt_fp8x2_to_halfraw2((__nv_fp8x2_storage_t)(v & 0xffffu), Fp8Kind<KV>::v);
+  const __half2_raw h23 = __nv_cvt_fp8x2_to_halfraw2((__nv_fp8x2_storage_t)(v >> 16), Fp8Kind<KV>::v);
+  lo = *reinterpret_cast<const uint32_t*>(&h01);
+  hi = *reinterpret_cast<const uint32_t*>(&h23);
+}
+// packed pair of T -> packed pair of MT
+template <typename T, typename MT>
+__device__ __forceinline__ uint32_t repack(uint32_t v) {
+  if constexpr (std::is_same<T, MT>::value) return v;
+  else {
+    const T* t = reinterpret_cast<const T*>(&v);
+    return Mma<MT>::pack(to_f32<T>(t[0]), to_f32<T>(t[1]));
+  }
+}
+
 }  // namespace amma
 
-template <typename T>
+template <typename T, int KV>
 __global__ void __launch_bounds__(amma::kThreads, 3)
 paged_attn_gqa_kernel(float* __restrict__ exp_sums, float* __restrict__ max_logits, T* __restrict__ out,
-                      const T* __restrict__ q, const T* __restrict__ k_cache, const T* __restrict__ v_cache,
+                      const T* __restrict__ q, const void* __restrict__ k_cache_v, const void* __restrict__ v_cache_v,
                       int num_heads, int num_kv_heads, float scale, const int* __restrict__ block_tables,
                       const int* __restrict__ seq_lens, int max_blocks_per_seq, const float* __restrict__ alibi_slopes,
-                      int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride, int partitioned) {
+                      int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride, int partitioned, float kv_scale) {
   using namespace amma;
+  constexpr bool FP8 = KV != B200_KV_AUTO;
+  using MT = typename std::conditional<FP8, __half, T>::type;   // MMA operand type
+  const float s_scale = FP8 ? scale * kv_scale : scale;
+  const float o_scale = FP8 ? kv_scale : 1.f;
   constexpr int OSTR = D + 4;   // padded row of the merge buffer (conflict-free fragment stores)
   __shared__ float sm_m[kWarps][GMAX], sm_l[kWarps][GMAX];
   __shared__ float sm_o[kWarps][GMAX][OSTR];
@@ -90,11 +116,13 @@ paged_attn_gqa_kernel(float* __restrict__ exp_sums, float* __restrict__ max_logi
   // Q^T fragments (B operand): b0 = Q[head g][16c + 2qd, +1], b1 = Q[head g][16c + 8 + 2qd, +1]; heads >= G are zero
   uint32_t qf[8][2];
   {
-    const T* qrow = q + (int64_t)seq * q_stride + (int64_t)(head0 + (g < G ? g : 0)) * D + 2 * qd;
+    // fp8 caches: one 4-byte load holds d = 16c + 4qd .. +3, so MMA k slots (2qd, 2qd+1) / (2qd+8, 2qd+9) carry
+    // d = 16c + 4qd + {0,1} / {2,3}; Q uses the same assignment
+    const T* qrow = q + (int64_t)seq * q_stride + (int64_t)(head0 + (g < G ? g : 0)) * D + (FP8 ? 4 : 2) * qd;
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
-      qf[c][0] = g < G ? *reinterpret_cast<const uint32_t*>(qrow + 16 * c) : 0u;
-      qf[c][1] = g < G ? *reinterpret_cast<const uint32_t*>(qrow + 16 * c + 8) : 0u;
+      qf[c][0] = g < G ? repack<T, MT>(*reinterpret_cast<const uint32_t*>(qrow + 16 * c)) : 0u;
+      qf[c][1] = g < G ? repack<T, MT>(*reinterpret_cast<const uint32_t*>(qrow + 16 * c + (FP8 ? 2 : 8))) : 0u;
     }
   }
   float slope[2] = {0.f, 0.f};
@@ -112,36 +140,66 @@ paged_attn_gqa_kernel(float* __restrict__ exp_sums, float* __restrict__ max_logi
   const int* btab = block_tables + (int64_t)seq * max_blocks_per_seq;
   for (int blk = start_block + warp; blk < end_block; blk += kWarps) {
     const int64_t base = (int64_t)btab[blk] * kv_block_stride + (int64_t)kvh * kv_head_stride;
-    const T* kp = k_cache + base + g * 8 + 2 * qd;          // K [D/8][16][8]
-    const T* vp = v_cache + base + g * BS + 2 * qd;          // V [D][16]
+    const int tok0 = blk * BS;
+    // MMA row r of S^T <-> token: auto: r; fp8: rows 0-7 -> 2r - r%2, rows 8-15 -> that + 2 (so that the transposed P
+    // fragment lines up with the 4-token groups one fp8 V load delivers)
+    const int t_lo = FP8 ? 2 * g - (g & 1) : g;
+    const int t_hi = FP8 ? t_lo + 2 : g + 8;
     uint32_t kf[8][4], vf[8][4];
+    if constexpr (!FP8) {
+      const T* kp = reinterpret_cast<const T*>(k_cache_v) + base + g * 8 + 2 * qd;          // K [D/8][16][8]
+      const T* vp = reinterpret_cast<const T*>(v_cache_v) + base + g * BS + 2 * qd;          // V [D][16]
 #pragma unroll
-    for (int c = 0; c < 8; ++c) {
-      kf[c][0] = ldg32(kp + (2 * c) * (BS * 8));
-      kf[c][1] = ldg32(kp + (2 * c) * (BS * 8) + 64);
-      kf[c][2] = ldg32(kp + (2 * c + 1) * (BS * 8));
-      kf[c][3] = ldg32(kp + (2 * c + 1) * (BS * 8) + 64);
-    }
+      for (int c = 0; c < 8; ++c) {
+        kf[c][0] = ldg32(kp + (2 * c) * (BS * 8));
+        kf[c][1] = ldg32(kp + (2 * c) * (BS * 8) + 64);
+        kf[c][2] = ldg32(kp + (2 * c + 1) * (BS * 8));
+        kf[c][3] = ldg32(kp + (2 * c + 1) * (BS * 8) + 64);
+      }
 #pragma unroll
-    for (int dm = 0; dm < 8; ++dm) {
-      vf[dm][0] = ldg32(vp + (16 * dm) * BS);
-      vf[dm][1] = ldg32(vp + (16 * dm + 8) * BS);
-      vf[dm][2] = ldg32(vp + (16 * dm) * BS + 8);
-      vf[dm][3] = ldg32(vp + (16 * dm + 8) * BS + 8);
+      for (int dm = 0; dm < 8; ++dm) {
+        vf[dm][0] = ldg32(vp + (16 * dm) * BS);
+        vf[dm][1] = ldg32(vp + (16 * dm + 8) * BS);
+        vf[dm][2] = ldg32(vp + (16 * dm) * BS + 8);
+        vf[dm][3] = ldg32(vp + (16 * dm + 8) * BS + 8);
+      }
+    } else {
+      const uint8_t* kp = reinterpret_cast<const uint8_t*>(k_cache_v) + base + 4 * qd;        // K [D/16][16][16]
+      const uint8_t* vp = reinterpret_cast<const uint8_t*>(v_cache_v) + base + g * BS + 4 * qd;  // V [D][16]
+      uint32_t kr[8][2], vr[8][2];
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        kr[c][0] = ldg32(kp + c * (BS * 16) + t_lo * 16);
+        kr[c][1] = ldg32(kp + c * (BS * 16) + t_hi * 16);
+      }
+#pragma unroll
+      for (int dm = 0; dm < 8; ++dm) {
+        vr[dm][0] = ldg32(vp + (16 * dm) * BS);
+        vr[dm][1] = ldg32(vp + (16 * dm + 8) * BS);
+      }
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        fp8x4_to_h2<FP8 ? KV : B200_KV_FP8_E4M3>(kr[c][0], kf[c][0], kf[c][2]);
+        fp8x4_to_h2<FP8 ? KV : B200_KV_FP8_E4M3>(kr[c][1], kf[c][1], kf[c][3]);
+      }
+#pragma unroll
+      for (int dm = 0; dm < 8; ++dm) {
+        fp8x4_to_h2<FP8 ? KV : B200_KV_FP8_E4M3>(vr[dm][0], vf[dm][0], vf[dm][2]);
+        fp8x4_to_h2<FP8 ? KV : B200_KV_FP8_E4M3>(vr[dm][1], vf[dm][1], vf[dm][3]);
+      }
     }
     float s[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-    for (int c = 0; c < 8; ++c) Mma<T>::run(s, kf[c], qf[c][0], qf[c][1]);
+    for (int c = 0; c < 8; ++c) Mma<MT>::run(s, kf[c], qf[c][0], qf[c][1]);
 
-    const int tok0 = blk * BS;
-    const int tk[2] = {tok0 + g, tok0 + g + 8};
+    const int tk[2] = {tok0 + t_lo, tok0 + t_hi};
     const bool ok[2] = {tk[0] < end_token, tk[1] < end_token};
     float pmax[2] = {NEG, NEG};
 #pragma unroll
     for (int r = 0; r < 2; ++r)
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
-        float v = s[2 * r + e] * scale;
+        float v = s[2 * r + e] * s_scale;
         if (alibi_slopes) v += slope[e] * (float)(tk[r] - seq_len + 1);
         s[2 * r + e] = v;
         if (ok[r]) pmax[e] = fmaxf(pmax[e], v);
@@ -165,19 +223,20 @@ paged_attn_gqa_kernel(float* __restrict__ exp_sums, float* __restrict__ max_logi
 #pragma unroll
     for (int e = 0; e < 2; ++e) l_run[e] = l_run[e] * alpha[e] + p[e] + p[2 + e];
     // P (tokens x heads, rounded to the query dtype) -> P^T fragments
-    const uint32_t pb0 = movmatrix_trans(Mma<T>::pack(p[0], p[1]));
-    const uint32_t pb1 = movmatrix_trans(Mma<T>::pack(p[2], p[3]));
+    const uint32_t pb0 = movmatrix_trans(repack<T, MT>(Mma<T>::pack(p[0], p[1])));
+    const uint32_t pb1 = movmatrix_trans(repack<T, MT>(Mma<T>::pack(p[2], p[3])));
     if (tok0 + BS > end_token) {
       // partial page: slots beyond the sequence may hold anything (NaN x 0 = NaN): zero them (attention_kernels.cu:420-430)
-      const uint32_t mlo = ((tok0 + 2 * qd < end_token) ? 0x0000ffffu : 0u) | ((tok0 + 2 * qd + 1 < end_token) ? 0xffff0000u : 0u);
-      const uint32_t mhi = ((tok0 + 2 * qd + 8 < end_token) ? 0x0000ffffu : 0u) | ((tok0 + 2 * qd + 9 < end_token) ? 0xffff0000u : 0u);
+      const int v_lo = tok0 + (FP8 ? 4 * qd : 2 * qd), v_hi = tok0 + (FP8 ? 4 * qd + 2 : 2 * qd + 8);   // tokens of k slots
+      const uint32_t mlo = ((v_lo < end_token) ? 0x0000ffffu : 0u) | ((v_lo + 1 < end_token) ? 0xffff0000u : 0u);
+      const uint32_t mhi = ((v_hi < end_token) ? 0x0000ffffu : 0u) | ((v_hi + 1 < end_token) ? 0xffff0000u : 0u);
 #pragma unroll
       for (int dm = 0; dm < 8; ++dm) { vf[dm][0] &= mlo; vf[dm][1] &= mlo; vf[dm][2] &= mhi; vf[dm][3] &= mhi; }
     }
 #pragma unroll
     for (int dm = 0; dm < 8; ++dm) {
       o[dm][0] *= alpha[0]; o[dm][1] *= alpha[1]; o[dm][2] *= alpha[0]; o[dm][3] *= alpha[1];
-      Mma<T>::run(o[dm], vf[dm], pb0, pb1);
+      Mma<MT>::run(o[dm], vf[dm], pb0, pb1);
     }
   }
 
@@ -214,7 +273,7 @@ paged_attn_gqa_kernel(float* __restrict__ exp_sums, float* __restrict__ max_logi
       L += sm_l[w][h] * f;
       acc += sm_o[w][h][d] * f;
     }
-    const float res = acc * __fdividef(1.f, L + 1e-6f);
+    const float res = acc * __fdividef(o_scale, L + 1e-6f);
     int64_t oi = (int64_t)seq * num_heads + head0 + h;
     if (partitioned) {
       oi = oi * num_parts + part;
@@ -231,28 +290,35 @@ int launch_mma(float* exp_sums, float* max_logits, void* out, void* tmp_out, con
                const float* alibi, int64_t q_stride, int64_t kvbs, int64_t kvhs, int partitioned, int num_parts,
                int dtype, int kv_dtype, float kv_scale, cudaStream_t st) {
   using namespace amma;
-  (void)max_seq_len; (void)kv_scale;
+  (void)max_seq_len;
   static const bool disabled = getenv("B200_ATTN_GENERIC") != nullptr;
   if (disabled) return 0;
   const int G = num_heads / num_kv_heads;
-  if (head_size != D || block_size != BS || kv_dtype != B200_KV_AUTO || G > GMAX) return 0;
+  if (head_size != D || block_size != BS || G > GMAX) return 0;
   if (dtype != B200_F16 && dtype != B200_BF16) return 0;
+  if (kv_dtype != B200_KV_AUTO && kv_dtype != B200_KV_FP8_E4M3 && kv_dtype != B200_KV_FP8_E5M2) return 0;
   // fragment loads are 4-byte: the cache strides (elements) and the query rows must keep them aligned
-  if ((kvbs & 1) || (kvhs & 1) || (q_stride & 1) || (reinterpret_cast<uintptr_t>(q) & 3) ||
+  const int64_t align_el = kv_dtype == B200_KV_AUTO ? 2 : 4;
+  if ((kvbs % align_el) || (kvhs % align_el) || (q_stride & 1) || (reinterpret_cast<uintptr_t>(q) & 3) ||
       (reinterpret_cast<uintptr_t>(kc) & 3) || (reinterpret_cast<uintptr_t>(vc) & 3))
     return 0;
   dim3 grid(num_kv_heads, num_seqs, partitioned ? num_parts : 1);
   void* dst = partitioned ? tmp_out : out;
-  cudaError_t e;
-  if (dtype == B200_F16)
-    e = launch_pdl(paged_attn_gqa_kernel<__half>, grid, dim3(kThreads), 0, st, exp_sums, max_logits, (__half*)dst,
-                   (const __half*)q, (const __half*)kc, (const __half*)vc, num_heads, num_kv_heads, scale, block_tables,
-                   seq_lens, max_blocks_per_seq, alibi, q_stride, kvbs, kvhs, partitioned);
-  else
-    e = launch_pdl(paged_attn_gqa_kernel<__nv_bfloat16>, grid, dim3(kThreads), 0, st, exp_sums, max_logits,
-                   (__nv_bfloat16*)dst, (const __nv_bfloat16*)q, (const __nv_bfloat16*)kc, (const __nv_bfloat16*)vc,
-                   num_heads, num_kv_heads, scale, block_tables, seq_lens, max_blocks_per_seq, alibi, q_stride, kvbs,
-                   kvhs, partitioned);
+  cudaError_t e = cudaSuccess;
+#define GQA_GO(TT, KVV)                                                                                                 \
+  e = launch_pdl(paged_attn_gqa_kernel<TT, KVV>, grid, dim3(kThreads), 0, st, exp_sums, max_logits, (TT*)dst,            \
+                 (const TT*)q, kc, vc, num_heads, num_kv_heads, scale, block_tables, seq_lens, max_blocks_per_seq, alibi, \
+                 q_stride, kvbs, kvhs, partitioned, kv_scale)
+  if (dtype == B200_F16) {
+    if (kv_dtype == B200_KV_AUTO) GQA_GO(__half, B200_KV_AUTO);
+    else if (kv_dtype == B200_KV_FP8_E4M3) GQA_GO(__half, B200_KV_FP8_E4M3);
+    else GQA_GO(__half, B200_KV_FP8_E5M2);
+  } else {
+    if (kv_dtype == B200_KV_AUTO) GQA_GO(__nv_bfloat16, B200_KV_AUTO);
+    else if (kv_dtype == B200_KV_FP8_E4M3) GQA_GO(__nv_bfloat16, B200_KV_FP8_E4M3);
+    else GQA_GO(__nv_bfloat16, B200_KV_FP8_E5M2);
+  }
+#undef GQA_GO
   if (e != cudaSuccess) return set_error(B200_ECUDA, "paged_attention (gqa path) launch: %s", cudaGetErrorString(e));
   return 1;
 }
