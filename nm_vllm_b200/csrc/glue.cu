@@ -62,6 +62,71 @@ __global__ void silu_and_mul_kernel(T* __restrict__ out, const T* __restrict__ i
   }
 }
 
+// 16-byte vectorised variants (hidden % 8 == 0, 16-byte aligned rows): same arithmetic, element order and roundings as
+// the scalar kernels above; a token row stays in registers between the two passes of the norm
+template <typename T, bool FUSED_ADD, int VPT>
+__global__ void __launch_bounds__(256)
+rms_norm_vec_kernel(T* __restrict__ out, T* __restrict__ input, T* __restrict__ residual, const T* __restrict__ weight,
+                    float eps, int hidden) {
+  pdl_wait();
+  pdl_launch_dependents();
+  __shared__ float red[33];
+  const int64_t base = (int64_t)blockIdx.x * hidden;
+  uint4 v[VPT];
+  float var = 0.f;
+#pragma unroll
+  for (int j = 0; j < VPT; ++j) {
+    const int i = (threadIdx.x + j * 256) * 8;
+    if (i < hidden) {
+      v[j] = *reinterpret_cast<const uint4*>(input + base + i);
+      T* z = reinterpret_cast<T*>(&v[j]);
+      if (FUSED_ADD) {
+        const uint4 r = *reinterpret_cast<const uint4*>(residual + base + i);
+        const T* rr = reinterpret_cast<const T*>(&r);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) z[e] = add_t<T>(z[e], rr[e]);
+        *reinterpret_cast<uint4*>(residual + base + i) = v[j];
+      }
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { const float x = to_f32<T>(z[e]); var += x * x; }
+    }
+  }
+  var = block_sum_1024(var, red);
+  const float inv = rsqrtf(var / hidden + eps);
+#pragma unroll
+  for (int j = 0; j < VPT; ++j) {
+    const int i = (threadIdx.x + j * 256) * 8;
+    if (i < hidden) {
+      const uint4 w = *reinterpret_cast<const uint4*>(weight + i);
+      const T* ww = reinterpret_cast<const T*>(&w);
+      T* z = reinterpret_cast<T*>(&v[j]);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) z[e] = mul_t<T>(from_f32<T>(to_f32<T>(z[e]) * inv), ww[e]);
+      *reinterpret_cast<uint4*>(out + base + i) = v[j];
+    }
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+silu_and_mul_vec_kernel(T* __restrict__ out, const T* __restrict__ input, int d) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int64_t tok = blockIdx.y;
+  const int i = (blockIdx.x * 256 + threadIdx.x) * 8;
+  if (i >= d) return;
+  uint4 a = *reinterpret_cast<const uint4*>(input + tok * 2 * d + i);
+  const uint4 b = *reinterpret_cast<const uint4*>(input + tok * 2 * d + d + i);
+  T* x = reinterpret_cast<T*>(&a);
+  const T* y = reinterpret_cast<const T*>(&b);
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const float f = to_f32<T>(x[e]);
+    x[e] = mul_t<T>(from_f32<T>(f / (1.0f + expf(-f))), y[e]);
+  }
+  *reinterpret_cast<uint4*>(out + tok * d + i) = a;
+}
+
 template <typename T, bool NEOX>
 __device__ __forceinline__ void rope_one(T* arr, const T* cos_ptr, const T* sin_ptr, int rot_offset, int embed_dim) {
   int xi, yi;
@@ -94,10 +159,30 @@ static inline int tok_threads(int n, int cap) {
 }
 }  // namespace b200
 
+
+namespace b200 {
+static inline bool vec_ok(int dtype, int n, const void* a, const void* b, const void* c) {
+  return dtype != B200_F32 && n % 8 == 0 && ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) |
+                                               reinterpret_cast<uintptr_t>(c)) & 15) == 0;
+}
+template <typename T, bool FUSED>
+static void launch_rms_vec(T* out, T* in, T* res, const T* w, float eps, int hidden, int64_t tokens, cudaStream_t st) {
+  if (hidden <= 2048) launch_pdl(rms_norm_vec_kernel<T, FUSED, 1>, dim3((unsigned)tokens), dim3(256), 0, st, out, in, res, w, eps, hidden);
+  else if (hidden <= 4096) launch_pdl(rms_norm_vec_kernel<T, FUSED, 2>, dim3((unsigned)tokens), dim3(256), 0, st, out, in, res, w, eps, hidden);
+  else launch_pdl(rms_norm_vec_kernel<T, FUSED, 4>, dim3((unsigned)tokens), dim3(256), 0, st, out, in, res, w, eps, hidden);
+}
+}  // namespace b200
+
 extern "C" int b200_rms_norm(void* out, const void* input, const void* weight, int64_t num_tokens, int hidden_size,
                              float epsilon, int dtype, void* stream) {
   using namespace b200;
   if (num_tokens == 0) return B200_OK;
+  if (vec_ok(dtype, hidden_size, out, input, weight) && hidden_size <= 8192) {
+    if (dtype == B200_F16) launch_rms_vec<__half, false>((__half*)out, (__half*)input, (__half*)input, (const __half*)weight, epsilon, hidden_size, num_tokens, (cudaStream_t)stream);
+    else launch_rms_vec<__nv_bfloat16, false>((__nv_bfloat16*)out, (__nv_bfloat16*)input, (__nv_bfloat16*)input, (const __nv_bfloat16*)weight, epsilon, hidden_size, num_tokens, (cudaStream_t)stream);
+    B200_LAUNCH_CHECK("rms_norm");
+    return B200_OK;
+  }
   B200_DISPATCH_FLOAT(dtype, "rms_norm", {
     launch_pdl(rms_norm_kernel<scalar_t, false>, dim3((unsigned)num_tokens), dim3(tok_threads(hidden_size, 1024)), 0, (cudaStream_t)stream, 
         (scalar_t*)out, (scalar_t*)input, nullptr, (const scalar_t*)weight, epsilon, hidden_size);
@@ -110,6 +195,12 @@ extern "C" int b200_fused_add_rms_norm(void* input, void* residual, const void* 
                                        int hidden_size, float epsilon, int dtype, void* stream) {
   using namespace b200;
   if (num_tokens == 0) return B200_OK;
+  if (vec_ok(dtype, hidden_size, input, residual, weight) && hidden_size <= 8192) {
+    if (dtype == B200_F16) launch_rms_vec<__half, true>((__half*)input, (__half*)input, (__half*)residual, (const __half*)weight, epsilon, hidden_size, num_tokens, (cudaStream_t)stream);
+    else launch_rms_vec<__nv_bfloat16, true>((__nv_bfloat16*)input, (__nv_bfloat16*)input, (__nv_bfloat16*)residual, (const __nv_bfloat16*)weight, epsilon, hidden_size, num_tokens, (cudaStream_t)stream);
+    B200_LAUNCH_CHECK("fused_add_rms_norm");
+    return B200_OK;
+  }
   B200_DISPATCH_FLOAT(dtype, "fused_add_rms_norm", {
     launch_pdl(rms_norm_kernel<scalar_t, true>, dim3((unsigned)num_tokens), dim3(tok_threads(hidden_size, 1024)), 0, (cudaStream_t)stream, 
         (scalar_t*)input, (scalar_t*)input, (scalar_t*)residual, (const scalar_t*)weight, epsilon, hidden_size);
@@ -121,6 +212,13 @@ extern "C" int b200_fused_add_rms_norm(void* input, void* residual, const void* 
 extern "C" int b200_silu_and_mul(void* out, const void* input, int64_t num_tokens, int d, int dtype, void* stream) {
   using namespace b200;
   if (num_tokens == 0) return B200_OK;
+  if (vec_ok(dtype, d, out, input, input)) {
+    const dim3 grid((unsigned)((d + 2047) / 2048), (unsigned)num_tokens);
+    if (dtype == B200_F16) launch_pdl(silu_and_mul_vec_kernel<__half>, grid, dim3(256), 0, (cudaStream_t)stream, (__half*)out, (const __half*)input, d);
+    else launch_pdl(silu_and_mul_vec_kernel<__nv_bfloat16>, grid, dim3(256), 0, (cudaStream_t)stream, (__nv_bfloat16*)out, (const __nv_bfloat16*)input, d);
+    B200_LAUNCH_CHECK("silu_and_mul");
+    return B200_OK;
+  }
   B200_DISPATCH_FLOAT(dtype, "silu_and_mul", {
     launch_pdl(silu_and_mul_kernel<scalar_t>, dim3((unsigned)num_tokens), dim3(tok_threads(d, 1024)), 0, (cudaStream_t)stream, 
         (scalar_t*)out, (const scalar_t*)input, d);
