@@ -616,10 +616,24 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         cluster_arrive();
         cluster_wait();
         const uint32_t red_u32 = act_base + (uint32_t)row * 4u;
-        for (int m = c_rank; m < m_valid; m += CS) {
-          float acc = 0.f;
-          for (int c = 0; c < CS; ++c) acc += ld_dsmem_f32(mapa(red_u32 + (uint32_t)m * (kTileN * 4u), (uint32_t)c));
-          if (n_ok) cdst[(size_t)m * args.N] = from_f32<T>(acc * ch_scale);
+        // all remote loads of a group of rows are issued before the first add: DSMEM latency is paid once per group
+        for (int mb = c_rank; mb < m_valid; mb += 4 * CS) {
+          float pv[4][8];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int m = mb + i * CS;
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+              pv[i][c] = (c < CS && m < m_valid) ? ld_dsmem_f32(mapa(red_u32 + (uint32_t)m * (kTileN * 4u), (uint32_t)c)) : 0.f;
+          }
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int m = mb + i * CS;
+            float acc = 0.f;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) acc += pv[i][c];
+            if (n_ok && m < m_valid) cdst[(size_t)m * args.N] = from_f32<T>(acc * ch_scale);
+          }
         }
       } else if (!full_k && !owner) {
         __threadfence();

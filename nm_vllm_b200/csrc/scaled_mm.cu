@@ -203,12 +203,15 @@ scaled_mm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const float bi = (args.bias && n_ok) ? to_f32<OutT>(reinterpret_cast<const OutT*>(args.bias)[n]) : 0.f;
       OutT* cdst = reinterpret_cast<OutT*>(args.out) + (size_t)m0 * args.ldc + n;
       auto finish = [&](const uint32_t* t, int j0) {
+        float as[16];   // per-token scales first: the loads must not be serialised behind the stores below
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          as[j] = (j0 + j < m_valid) ? __ldg(args.a_scales + (args.a_scales_numel > 1 ? m0 + j0 + j : 0)) : 0.f;
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
           if (j0 + j < m_valid && n_ok) {
             const float a = IS_FP8 ? __uint_as_float(t[j]) : (float)(int)t[j];
-            const float as = args.a_scales[args.a_scales_numel > 1 ? m0 + j0 + j : 0];
-            cdst[(size_t)(j0 + j) * args.ldc] = from_f32<OutT>(fmaf(as, bs * a, bi));
+            cdst[(size_t)(j0 + j) * args.ldc] = from_f32<OutT>(fmaf(as[j], bs * a, bi));
           }
         }
       };
