@@ -61,6 +61,11 @@ struct GemmCfg {
   static constexpr int NDQ = 4 * NOWN;                               // dequant warps
   static constexpr int EPI_WARP0 = kDequantWarp0 + NDQ;
   static constexpr int THREADS = (EPI_WARP0 + 4) * 32;
+  // registers per thread: at launch (what ptxas may use under __launch_bounds__(THREADS, 1)), after setmaxnreg.dec in
+  // warps 0-7, and after setmaxnreg.inc in the 4 epilogue warps (they take exactly what warps 0-7 gave back)
+  static constexpr int REG_LAUNCH = ((65536 / THREADS) / 8) * 8;
+  static constexpr int REG_LOW = 48;
+  static constexpr int REG_EPI = REG_LAUNCH + 2 * (REG_LAUNCH - REG_LOW);
   static constexpr int ACC_COL0 = 64 * NOWN;                         // TMEM: [own-group operand slots][accumulators]
   static constexpr int TMEM_COLS = 512;
   static constexpr int W_ROW_BYTES = kTileN * 16 * BITS / 8;         // one 16(k) x 128(n) slab: 1024 (4-bit) / 2048 (8-bit)
@@ -69,13 +74,16 @@ struct GemmCfg {
   static constexpr int A_BOX_BYTES = MPAD * 128;                     // one 64(k) x MPAD chunk, 128-byte swizzle
   static constexpr int A_STAGE_BYTES = 4 * A_BOX_BYTES;
   static constexpr int S_STAGE_BYTES = 2048;                         // up to eight 128-column scale rows (group 32)
-  static constexpr int STAGE_BYTES = W_STAGE_BYTES + A_STAGE_BYTES + S_STAGE_BYTES;
-  static constexpr int NSTAGES_RAW = (208 * 1024) / STAGE_BYTES;
-  static constexpr int NSTAGES = NSTAGES_RAW > 8 ? 8 : NSTAGES_RAW;
-  static constexpr int NBARS = 2 * NSTAGES + 4 * NOWN + 2 * NOWN * NBUF;
+  // two rings: packed weights (HBM latency, released as soon as the dequant warps hold them in registers) and
+  // activations + group scales (L2 latency, released when the MMAs that read them have completed)
+  static constexpr int NA = MPAD <= 32 ? 4 : (MPAD == 64 ? 3 : 2);
+  static constexpr int AS_STAGE_BYTES = A_STAGE_BYTES + S_STAGE_BYTES;
+  static constexpr int NW_RAW = (208 * 1024 - NA * AS_STAGE_BYTES) / W_STAGE_BYTES;
+  static constexpr int NW = NW_RAW > 12 ? 12 : NW_RAW;
+  static constexpr int NBARS = 2 * NW + 2 * NA + 4 * NOWN + 2 * NOWN * NBUF;
   static constexpr int BAR_BYTES = NBARS * 8 + 16;
-  static constexpr int SMEM_BYTES = 1024 /*align slack*/ + NSTAGES * STAGE_BYTES + BAR_BYTES;
-  static_assert(NSTAGES >= 2, "pipeline needs at least two stages");
+  static constexpr int SMEM_BYTES = 1024 /*align slack*/ + NW * W_STAGE_BYTES + NA * AS_STAGE_BYTES + BAR_BYTES;
+  static_assert(NW >= 2 && NA >= 2, "pipeline needs at least two stages per ring");
   static_assert(ACC_COL0 + NOWN * NBUF * MPAD <= 512, "TMEM budget");
   static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 };
@@ -227,7 +235,14 @@ __device__ __forceinline__ int ld_acquire_gpu(const int* p) {
   return v;
 }
 
+// per-role cycle counters: compiled in only with -DB200_GEMM_PROF (they cost ~4 issue slots per packed word otherwise)
+#ifdef B200_GEMM_PROF
+#define PROF_ON(x) (x)
 #define PROF_ACC(var) if (args.prof) { const long long p_t1 = clock64(); var += p_t1 - p_mark; p_mark = p_t1; }
+#else
+#define PROF_ON(x) false
+#define PROF_ACC(var)
+#endif
 
 // ---- the kernel --------------------------------------------------------------------------------------------------
 template <typename T, int MPAD, int BITS, int GM>
@@ -235,33 +250,42 @@ __global__ void __launch_bounds__(GemmCfg<MPAD, BITS>::THREADS, 1)
 marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
                    const __grid_constant__ CUtensorMap tmap_s, const GemmArgs args) {
   using Cfg = GemmCfg<MPAD, BITS>;
-  constexpr int NS = Cfg::NSTAGES, NOWN = Cfg::NOWN, NBUF = Cfg::NBUF;
+  constexpr int NW = Cfg::NW, NA = Cfg::NA, NOWN = Cfg::NOWN, NBUF = Cfg::NBUF;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   // layout: [activation stages (1024-aligned)] [weight stages] [scale stages] [barriers]
   const uint32_t act_base = smem_base;
-  const uint32_t w_base = act_base + NS * Cfg::A_STAGE_BYTES;
-  const uint32_t sc_base = w_base + NS * Cfg::W_STAGE_BYTES;
-  const uint32_t bar_base = sc_base + NS * Cfg::S_STAGE_BYTES;
-  auto full_bar = [&](int s) { return bar_base + 8u * s; };
-  auto empty_bar = [&](int s) { return bar_base + 8u * (NS + s); };
-  auto afull_bar = [&](int o, int sub) { return bar_base + 8u * (2 * NS + 2 * o + sub); };
-  auto aempty_bar = [&](int o, int sub) { return bar_base + 8u * (2 * NS + 2 * NOWN + 2 * o + sub); };
-  auto accfull_bar = [&](int o, int b) { return bar_base + 8u * (2 * NS + 4 * NOWN + o * NBUF + b); };
-  auto accempty_bar = [&](int o, int b) { return bar_base + 8u * (2 * NS + 4 * NOWN + NOWN * NBUF + o * NBUF + b); };
+  const uint32_t w_base = act_base + NA * Cfg::A_STAGE_BYTES;
+  const uint32_t sc_base = w_base + NW * Cfg::W_STAGE_BYTES;
+  const uint32_t bar_base = sc_base + NA * Cfg::S_STAGE_BYTES;
+  constexpr int NR = 2 * NW + 2 * NA;   // ring barriers
+  auto wfull_bar = [&](int s) { return bar_base + 8u * s; };
+  auto wempty_bar = [&](int s) { return bar_base + 8u * (NW + s); };
+  auto actfull_bar = [&](int s) { return bar_base + 8u * (2 * NW + s); };
+  auto actempty_bar = [&](int s) { return bar_base + 8u * (2 * NW + NA + s); };
+  auto afull_bar = [&](int o, int sub) { return bar_base + 8u * (NR + 2 * o + sub); };
+  auto aempty_bar = [&](int o, int sub) { return bar_base + 8u * (NR + 2 * NOWN + 2 * o + sub); };
+  auto accfull_bar = [&](int o, int b) { return bar_base + 8u * (NR + 4 * NOWN + o * NBUF + b); };
+  auto accempty_bar = [&](int o, int b) { return bar_base + 8u * (NR + 4 * NOWN + NOWN * NBUF + o * NBUF + b); };
   const uint32_t tmem_slot = bar_base + 8u * Cfg::NBARS;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));  // generic pointer to the aligned base
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const long long k_t0 = args.prof ? clock64() : 0;
+  const long long k_t0 = PROF_ON(args.prof) ? clock64() : 0;
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmap_w);
     prefetch_tmap(&tmap_a);
     if (GM != kChannelwise) prefetch_tmap(&tmap_s);
-    for (int s = 0; s < NS; ++s) {
-      mbar_init(full_bar(s), 1);
-      mbar_init(empty_bar(s), 8 + 2);   // 2 halves x 4 quarter warps + the two issuers' commits
+    for (int s = 0; s < NW; ++s) {
+      mbar_init(wfull_bar(s), 1);
+      mbar_init(wempty_bar(s), 8);   // 2 halves x 4 dequant quarter warps
+    }
+    for (int s = 0; s < NA; ++s) {
+      mbar_init(actfull_bar(s), 1);
+      // the two issuers' commits + whoever reads the staged group scales: the 4 epilogue warps (g128) or the 8 dequant
+      // warps of the two halves (small groups)
+      mbar_init(actempty_bar(s), 2 + (GM == kGroup128 ? 4 : (GM == kGroupSmall ? 8 : 0)));
     }
     for (int o = 0; o < NOWN; ++o) {
       for (int sub = 0; sub < 2; ++sub) {
@@ -277,6 +301,9 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
   }
   __syncthreads();            // barriers are live: the producers start streaming weights right away
   pdl_launch_dependents();    // the next kernel of the stream may start its own prologue now
+  // register re-balance (warpgroup-aligned roles): producers / allocator / issuers need few registers, the epilogue
+  // warps hold MPAD fp32 accumulators per thread
+  // (setmaxnreg is the first instruction of each role branch below, so that ptxas sees which code it governs)
 
   // two work decompositions:
   //   stream-K (cluster_s <= 1): the (tile, k-stage) space is cut into one contiguous range per CTA; shared tiles are
@@ -294,12 +321,18 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
   const int n_units = u_end - u_begin;
   const int gps = args.groups_per_stage;
 
+  // everyone but the producers needs the TMEM base address: named barrier 2 after the allocator warp's tcgen05.alloc
+  auto get_tmem_base = [&]() -> uint32_t {
+    tc_fence_before();
+    asm volatile("bar.sync 2, %0;" ::"n"(Cfg::THREADS - kNumProducers * 32) : "memory");
+    tc_fence_after();
+    return *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
+  };
+
   if (warp < kNumProducers) {
-    // ================= TMA producers: stage `it` belongs to warp it % 2; 3 tensor copies per 256 x 128 stage ==========
+    setmaxnreg_dec<Cfg::REG_LOW>();
+    // ================= TMA producers: warp 0 streams packed weights, warp 1 activations + group scales ================
     // (the whole warp runs the loops so that coordinates / descriptors stay warp-uniform; one elected lane issues)
-    const uint64_t pol_w = policy_evict_first();   // weights are streamed exactly once
-    const uint64_t pol_a = policy_evict_last();    // activations / scales are re-read by every CTA
-    const uint32_t tx = Cfg::W_STAGE_BYTES + Cfg::A_STAGE_BYTES + (GM != kChannelwise ? (uint32_t)gps * 256u : 0u);
     auto coords = [&](int it, int& nt, int& mc, int& ks) {
       const int u = u_begin + it;
       const int tile = u / KS;
@@ -307,104 +340,91 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       nt = tile % args.n_tiles;
       mc = tile / args.n_tiles;
     };
-    auto issue_ws = [&](int it) {
-      int nt, mc, ks;
-      coords(it, nt, mc, ks);
-      const int s = it % NS;
-      if (elect_one()) {
-        mbar_arrive_expect_tx(full_bar(s), tx);
-        tma_2d_g2s_hint(w_base + s * Cfg::W_STAGE_BYTES, &tmap_w, nt * (Cfg::W_ROW_BYTES / 8), ks * (kStageK / 16),
-                        full_bar(s), pol_w);
-        if (GM != kChannelwise)
-          tma_2d_g2s_hint(sc_base + s * Cfg::S_STAGE_BYTES, &tmap_s, nt * kTileN, ks * gps, full_bar(s), pol_a);
+    if (warp == 0) {
+      // weights do not depend on the previous kernel of the stream: no PDL wait on this path at all
+      const uint64_t pol_w = policy_evict_first();   // weights are streamed exactly once
+      for (int it = 0; it < n_units; ++it) {
+        const int s = it % NW;
+        if (it >= NW) mbar_wait(wempty_bar(s), ((it / NW) & 1) ^ 1);
+        int nt, mc, ks;
+        coords(it, nt, mc, ks);
+        if (elect_one()) {
+          mbar_arrive_expect_tx(wfull_bar(s), Cfg::W_STAGE_BYTES);
+          tma_2d_g2s_hint(w_base + s * Cfg::W_STAGE_BYTES, &tmap_w, nt * (Cfg::W_ROW_BYTES / 8), ks * (kStageK / 16),
+                          wfull_bar(s), pol_w);
+        }
+        __syncwarp();
       }
-      __syncwarp();
-    };
-    auto issue_a = [&](int it) {
-      int nt, mc, ks;
-      coords(it, nt, mc, ks);
-      const int s = it % NS;
-      if (elect_one())
-        tma_3d_g2s_hint(act_base + s * Cfg::A_STAGE_BYTES, &tmap_a, 0, mc * MPAD, ks * (kStageK / 64), full_bar(s), pol_a);
-      __syncwarp();
-    };
-    // first ring pass: weights + scales do not depend on the previous kernel -> issue them before the PDL wait
-    for (int it = warp; it < n_units && it < NS; it += kNumProducers) issue_ws(it);
-    pdl_wait();
-    for (int it = warp; it < n_units && it < NS; it += kNumProducers) issue_a(it);
-    int it = warp;
-    while (it < NS) it += kNumProducers;
-    for (; it < n_units; it += kNumProducers) {
-      mbar_wait(empty_bar(it % NS), ((it / NS) & 1) ^ 1);
-      issue_ws(it);
-      issue_a(it);
+    } else {
+      const uint64_t pol_a = policy_evict_last();    // activations / scales are re-read by every CTA
+      const uint32_t tx = Cfg::A_STAGE_BYTES + (GM != kChannelwise ? (uint32_t)gps * 256u : 0u);
+      pdl_wait();
+      for (int it = 0; it < n_units; ++it) {
+        const int s = it % NA;
+        if (it >= NA) mbar_wait(actempty_bar(s), ((it / NA) & 1) ^ 1);
+        int nt, mc, ks;
+        coords(it, nt, mc, ks);
+        if (elect_one()) {
+          mbar_arrive_expect_tx(actfull_bar(s), tx);
+          tma_3d_g2s_hint(act_base + s * Cfg::A_STAGE_BYTES, &tmap_a, 0, mc * MPAD, ks * (kStageK / 64), actfull_bar(s), pol_a);
+          if (GM != kChannelwise)
+            tma_2d_g2s_hint(sc_base + s * Cfg::S_STAGE_BYTES, &tmap_s, nt * kTileN, ks * gps, actfull_bar(s), pol_a);
+        }
+        __syncwarp();
+      }
     }
   } else if (warp < kIssuerWarp0) {
+    setmaxnreg_dec<Cfg::REG_LOW>();
     if (warp == kAllocWarp) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
-  }
-  // everyone but the producers needs the TMEM base address
-  if (warp >= kNumProducers) {
-    tc_fence_before();
-    asm volatile("bar.sync 2, %0;" ::"n"(Cfg::THREADS - kNumProducers * 32) : "memory");
-    tc_fence_after();
-  }
-  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
-
-  if (warp >= kIssuerWarp0 && warp < kIssuerWarp0 + NOWN) {
-    // ================= MMA issuers: own-group o turns half stages hu % NOWN == o into its own accumulator ==========
+    (void)get_tmem_base();
+  } else if (warp < kDequantWarp0) {
+    setmaxnreg_dec<Cfg::REG_LOW>();
+    const uint32_t tmem_base = get_tmem_base();
+    if (warp < kIssuerWarp0 + NOWN) {
+    // ================= MMA issuers: own-group o turns half stages hu % NOWN == o, each into a FRESH accumulator ====
+    // (one half stage = 128 k = one quantisation group at g128: the epilogue warps scale and sum the accumulators
+    // in registers, so the issuer knows nothing about tiles)
     const int o = warp - kIssuerWarp0, h = o & 1;
     constexpr uint32_t idesc = make_idesc(1 /*F32*/, Pack2<T>::FMT, Pack2<T>::FMT, 128, MPAD);
     const uint32_t a_tmem0 = tmem_base + 64 * o;
-    uint32_t uo = 0;
-    long long p_mark = args.prof ? clock64() : 0, p_wacc = 0, p_wfull = 0, p_wafull = 0, p_issue = 0;
-    for (int u = u_begin; u < u_end;) {
-      const int ks0 = u % KS;
-      const int len = min(KS - ks0, u_end - u);
-      const int it0 = u - u_begin, it1 = it0 + len;
-      int hu = 2 * it0 + ((o - 2 * it0) & (NOWN - 1));
-      if (hu < 2 * it1) {
-        const int ab = uo % NBUF;
-        mbar_wait(accempty_bar(o, ab), ((uo / NBUF) & 1) ^ 1);
-        PROF_ACC(p_wacc);
+    long long p_mark = PROF_ON(args.prof) ? clock64() : 0, p_wacc = 0, p_wfull = 0, p_wafull = 0, p_issue = 0;
+    int jc = 0;
+    for (int hu = o; hu < 2 * n_units; hu += NOWN, ++jc) {
+      const int ab = jc % NBUF;
+      mbar_wait(accempty_bar(o, ab), ((jc / NBUF) & 1) ^ 1);
+      PROF_ACC(p_wacc);
+      const uint32_t d_tmem = tmem_base + Cfg::ACC_COL0 + (o * NBUF + ab) * MPAD;
+      const int it = hu >> 1, s = it % NA;
+      mbar_wait(actfull_bar(s), (it / NA) & 1);
+      PROF_ACC(p_wfull);
+      const uint32_t b_smem = act_base + s * Cfg::A_STAGE_BYTES;
+#pragma unroll
+      for (int sub = 0; sub < 2; ++sub) {
+        mbar_wait(afull_bar(o, sub), jc & 1);
+        PROF_ACC(p_wafull);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + Cfg::ACC_COL0 + (o * NBUF + ab) * MPAD;
-        bool fresh = true;
-        for (; hu < 2 * it1; hu += NOWN) {
-          const int it = hu >> 1, s = it % NS, jc = (hu - o) / NOWN;
-          mbar_wait(full_bar(s), (it / NS) & 1);
-          PROF_ACC(p_wfull);
-          const uint32_t b_smem = act_base + s * Cfg::A_STAGE_BYTES;
-          const bool last = hu + NOWN >= 2 * it1;
+        if (elect_one()) {
 #pragma unroll
-          for (int sub = 0; sub < 2; ++sub) {
-            mbar_wait(afull_bar(o, sub), jc & 1);
-            PROF_ACC(p_wafull);
-            tc_fence_after();
-            if (elect_one()) {
-#pragma unroll
-              for (int rr = 0; rr < 4; ++rr) {
-                const int R = h * kSlabs + sub * 4 + rr;   // k16 slab within the stage
-                mma_f16_ts(d_tmem, a_tmem0 + sub * 32 + rr * 8,
-                           make_kmajor_sw128_desc(b_smem + (R >> 2) * Cfg::A_BOX_BYTES + (R & 3) * 32), idesc,
-                           (fresh && sub == 0 && rr == 0) ? 0u : 1u);
-              }
-              tc_commit(aempty_bar(o, sub));
-              if (sub == 1) {
-                tc_commit(empty_bar(s));
-                if (last) tc_commit(accfull_bar(o, ab));
-              }
-            }
-            __syncwarp();
-            PROF_ACC(p_issue);
+          for (int rr = 0; rr < 4; ++rr) {
+            const int R = h * kSlabs + sub * 4 + rr;   // k16 slab within the stage
+            mma_f16_ts(d_tmem, a_tmem0 + sub * 32 + rr * 8,
+                       make_kmajor_sw128_desc(b_smem + (R >> 2) * Cfg::A_BOX_BYTES + (R & 3) * 32), idesc,
+                       (sub == 0 && rr == 0) ? 0u : 1u);
           }
-          fresh = false;
+          tc_commit(aempty_bar(o, sub));
+          if (sub == 1) {
+            tc_commit(actempty_bar(s));
+            tc_commit(accfull_bar(o, ab));
+          }
         }
-        ++uo;
+        __syncwarp();
+        PROF_ACC(p_issue);
       }
-      u += len;
     }
-    if (args.prof && o == 0 && lane == 0) { long long* q = args.prof + blockIdx.x * 16; q[2] = p_wacc; q[3] = p_wfull; q[4] = p_wafull; q[5] = p_issue; }
-  } else if (warp >= kDequantWarp0 && warp < Cfg::EPI_WARP0) {
+    if (PROF_ON(args.prof) && o == 0 && lane == 0) { long long* q = args.prof + blockIdx.x * 16; q[2] = p_wacc; q[3] = p_wfull; q[4] = p_wafull; q[5] = p_issue; }
+    }
+  } else if (warp < Cfg::EPI_WARP0) {
+    const uint32_t tmem_base = get_tmem_base();
     // ================= dequant warps: smem (packed) -> registers -> TMEM =================
     const int qd = warp & 3;                       // TMEM lane quarter: rows 32 qd .. 32 qd + 31 of the tile
     const int o = (warp - kDequantWarp0) >> 2;     // own-group: half stages hu % NOWN == o
@@ -418,12 +438,12 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     const uint8_t* wsm = smem_gen + (w_base - smem_base) + h * Cfg::W_HALF_BYTES + t64 * (Cfg::W_ROW_BYTES / 2) +
                          lane * (4 * BITS) + jpair * (2 * BITS);
     const uint8_t* ssm = smem_gen + (sc_base - smem_base) + h * gph * 256 + (64 * t64 + 8 * c + 4 * jpair) * 2;
-    long long p_mark = args.prof ? clock64() : 0, p_wfull = 0, p_lds = 0, p_waempty = 0, p_deq = 0, p_st = 0;
+    long long p_mark = PROF_ON(args.prof) ? clock64() : 0, p_wfull = 0, p_lds = 0, p_waempty = 0, p_deq = 0, p_st = 0;
     int jc = 0;
     for (int hu = o; hu < 2 * n_units; hu += NOWN, ++jc) {
       const int it = hu >> 1;
-      const int s = it % NS;
-      mbar_wait(full_bar(s), (it / NS) & 1);
+      const int s = it % NW, sa = it % NA;
+      mbar_wait(wfull_bar(s), (it / NW) & 1);
       PROF_ACC(p_wfull);
       // packed words of this thread for all 8 slabs: 64-chunk t64, fragment lane, n16-tiles (2 jpair, 2 jpair + 1)
       uint32_t w[kSlabs][WPT];
@@ -437,17 +457,22 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
           w[r][0] = v.x; w[r][1] = v.y; w[r][2] = v.z; w[r][3] = v.w;
         }
       }
-      // scale_perm (gptq_marlin.py:30-33): position 8 c + b' of a 64-chunk holds column c + 8 b'; this thread needs
-      // b' = 4 jpair .. 4 jpair + 3  ->  one 8-byte read of the scale row the producer staged with the weights
+      // kGroupSmall only (groups of 32 / 64 are finer than a half stage, so the scale has to go onto the weights, in
+      // the activation dtype like the reference :270-278).  scale_perm (gptq_marlin.py:30-33): position 8 c + b' of a
+      // 64-chunk holds column c + 8 b'; this thread needs b' = 4 jpair .. 4 jpair + 3 -> one 8-byte read
       uint32_t s2[4] = {0, 0, 0, 0};  // broadcast scales for (jj, b): index 2 jj + b
       auto load_scales = [&](int row) {
-        const uint2 raw = *reinterpret_cast<const uint2*>(ssm + s * Cfg::S_STAGE_BYTES + row * 256);
+        const uint2 raw = *reinterpret_cast<const uint2*>(ssm + sa * Cfg::S_STAGE_BYTES + row * 256);
         s2[0] = bcast16(raw.x);
         s2[1] = bcast16_hi(raw.x);
         s2[2] = bcast16(raw.y);
         s2[3] = bcast16_hi(raw.y);
       };
-      if (GM == kGroup128) load_scales(0);
+      // the packed words are in registers: hand the weight stage back to the producer right away (the arrive has
+      // release semantics, so the shared-memory reads above are performed before it)
+      __syncwarp();
+      if (lane == 0) mbar_arrive(wempty_bar(s));
+      if (GM == kGroupSmall) mbar_wait(actfull_bar(sa), (it / NA) & 1);   // the staged scale rows ride with the activations
       PROF_ACC(p_lds);
 #pragma unroll
       for (int sub = 0; sub < 2; ++sub) {
@@ -461,7 +486,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
             uint32_t* o4 = &ov[4 * rr];
             if (BITS == 4) dequant4<T>(w[r][jj], o4);
             else dequant8<T>(w[r][2 * jj], w[r][2 * jj + 1], o4);
-            if (GM != kChannelwise) {
+            if (GM == kGroupSmall) {
               o4[0] = Pack2<T>::mul(o4[0], s2[2 * jj]);
               o4[1] = Pack2<T>::mul(o4[1], s2[2 * jj + 1]);
               o4[2] = Pack2<T>::mul(o4[2], s2[2 * jj]);
@@ -482,23 +507,31 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         if (lane == 0) mbar_arrive(afull_bar(o, sub));
         PROF_ACC(p_st);
       }
-      if (lane == 0) mbar_arrive(empty_bar(s));  // smem slot consumed (values are in registers and have been used)
+      if (GM == kGroupSmall) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(actempty_bar(sa));   // scale rows consumed
+      }
     }
-    if (args.prof && warp == kDequantWarp0 && lane == 0) {
+    if (PROF_ON(args.prof) && warp == kDequantWarp0 && lane == 0) {
       long long* q = args.prof + blockIdx.x * 16; q[6] = p_wfull; q[7] = p_lds; q[8] = p_waempty; q[9] = p_deq; q[10] = p_st;
     }
-  } else if (warp >= Cfg::EPI_WARP0) {
-    // ================= epilogue: TMEM -> registers -> global (direct, split-K partial, or owner-side reduce) ==========
+  } else {
+    // ================= epilogue warps: per half stage TMEM -> registers, scale, accumulate; per tile segment -> global ===
+    // thread = one output channel (TMEM lane), acc[m] = its MPAD outputs in fp32.  At g128 a half stage is exactly one
+    // quantisation group, so the group scale is applied HERE, once per (group, channel, m), in fp32 -- the dequant warps
+    // never touch scales.  Channelwise scales are applied once at the end; small groups were scaled by the dequant warps.
+    setmaxnreg_inc<Cfg::REG_EPI>();
+    const uint32_t tmem_base = get_tmem_base();
     const int qd = warp & 3;
     const int row = 32 * qd + lane;  // output channel within the tile == TMEM lane
     const int et = threadIdx.x - Cfg::EPI_WARP0 * 32;  // 0..127
-    constexpr bool kPrefetch = MPAD <= 32;   // the owner sums the other CTAs' partials into registers ahead of its MMAs
-    constexpr int NCH = MPAD / 16;
+    constexpr int CH = MPAD < 32 ? MPAD : 32;          // accumulator columns per TMEM read batch
+    // position of this channel's scale in a staged 128-column scale row (scale_perm, 64-chunks: pos 8 c + b' <-> col c + 8 b')
+    const uint8_t* ssm_e = smem_gen + (sc_base - smem_base) + 2 * (64 * (row >> 6) + 8 * (row & 7) + ((row & 63) >> 3));
+    const uint32_t acc_lane = tmem_base + ((uint32_t)(32 * qd) << 16) + Cfg::ACC_COL0;
     pdl_wait();   // C, the partial slots and the tile counters may still be in use by the previous kernel
-    long long p_mark = args.prof ? clock64() : 0, p_wacc = 0, p_epi = 0, p_red = 0;
-    uint32_t uo[NOWN];
-#pragma unroll
-    for (int o = 0; o < NOWN; ++o) uo[o] = 0;
+    long long p_mark = PROF_ON(args.prof) ? clock64() : 0, p_wacc = 0, p_epi = 0, p_red = 0;
+    float sc_h[2] = {1.f, 1.f};
     for (int u = u_begin; u < u_end;) {
       const int tile = u / KS, ks0 = u - tile * KS;
       const int len = min(KS - ks0, u_end - u);
@@ -511,107 +544,82 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       const bool full_k = (ks0 == 0 && len == KS);
       const bool owner = (ks0 == 0 && !full_k && !clustered);   // this CTA reduces the tile; the others only contribute
       T* cdst = reinterpret_cast<T*>(args.C) + (size_t)m0 * args.N + n;
-      float* part_dst = args.scratch + (size_t)blockIdx.x * (kTileN * MPAD);
-      int n_other = 0;
-      float psum[kPrefetch ? MPAD : 1];
-      if (owner) {
+      float acc[MPAD];
+#pragma unroll
+      for (int j = 0; j < MPAD; ++j) acc[j] = 0.f;
+      for (int hu = 2 * it0; hu < 2 * it1; ++hu) {
+        const int o = hu & (NOWN - 1), jc = hu / NOWN, ab = jc % NBUF;
+        if (GM == kGroup128 && (hu & 1) == 0) {
+          // both group scales of this stage, then release the stage (the full barrier completed long ago: the MMAs
+          // of the previous half stage, which this thread has just consumed, were issued after it)
+          const int it = hu >> 1, s = it % NA;
+          mbar_wait(actfull_bar(s), (it / NA) & 1);
+          sc_h[0] = to_f32<T>(*reinterpret_cast<const T*>(ssm_e + s * Cfg::S_STAGE_BYTES));
+          sc_h[1] = to_f32<T>(*reinterpret_cast<const T*>(ssm_e + s * Cfg::S_STAGE_BYTES + 256));
+          __syncwarp();
+          if (lane == 0) mbar_arrive(actempty_bar(s));
+        }
+        const float sc = sc_h[hu & 1];
+        mbar_wait(accfull_bar(o, ab), (jc / NBUF) & 1);
+        PROF_ACC(p_wacc);
+        tc_fence_after();
+        const uint32_t src = acc_lane + (o * NBUF + ab) * MPAD;
+#pragma unroll
+        for (int c0 = 0; c0 < MPAD; c0 += CH) {
+          uint32_t t[CH];
+#pragma unroll
+          for (int c1 = 0; c1 < CH; c1 += 16) tmem_ld_32x32b_x16(src + c0 + c1, *reinterpret_cast<uint32_t(*)[16]>(&t[c1]));
+          tc_wait_ld();
+          if (c0 + CH == MPAD) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(accempty_bar(o, ab));
+          }
+#pragma unroll
+          for (int j = 0; j < CH; ++j) acc[c0 + j] = fmaf(sc, __uint_as_float(t[j]), acc[c0 + j]);
+        }
+        PROF_ACC(p_epi);
+      }
+      float ch_scale = 1.f;
+      if (GM == kChannelwise && n_ok)
+        ch_scale = to_f32<T>(reinterpret_cast<const T*>(args.scales)[(n & ~31) + scale_single_pos(n & 31)]);
+
+      if (full_k) {
+        if (n_ok) {
+#pragma unroll
+          for (int j = 0; j < MPAD; ++j)
+            if (j < m_valid) cdst[(size_t)j * args.N] = from_f32<T>(acc[j] * ch_scale);
+        }
+      } else if (owner) {
         // contributors are the CTAs after this one whose unit ranges intersect [tile*KS, (tile+1)*KS); for each of them
-        // the tile is the first segment of its range, so its partial sits in its slot
-        n_other = part.owner(tile * KS + KS - 1) - (int)blockIdx.x;
+        // the tile is the FIRST segment of its range, so its partial has long been in its slot when this CTA (whose
+        // LAST segment this is) gets here
+        const int n_other = part.owner(tile * KS + KS - 1) - (int)blockIdx.x;
         if (et == 0) {
           while (ld_acquire_gpu(&args.counters[tile]) < n_other) {}
           args.counters[tile] = 0;   // self-reset: exactly n_other increments ever arrive
         }
         asm volatile("bar.sync 1, 128;" ::: "memory");
         __threadfence();
-        if constexpr (kPrefetch) {
+        for (int b = 1; b <= n_other; ++b) {
+          const float* src = args.scratch + (size_t)(blockIdx.x + b) * (kTileN * MPAD) + row;
 #pragma unroll
-          for (int j = 0; j < MPAD; ++j) psum[j] = 0.f;
-          for (int b = 1; b <= n_other; ++b) {
-            const float* src = args.scratch + (size_t)(blockIdx.x + b) * (kTileN * MPAD) + row;
-#pragma unroll
-            for (int j = 0; j < MPAD; ++j)
-              if (j < m_valid) psum[j] += __ldcg(src + j * kTileN);
-          }
+          for (int j = 0; j < MPAD; ++j)
+            if (j < m_valid) acc[j] += __ldcg(src + j * kTileN);
         }
         PROF_ACC(p_red);
-      }
-      float ch_scale = 1.f;
-      if (GM == kChannelwise && n_ok)
-        ch_scale = to_f32<T>(reinterpret_cast<const T*>(args.scales)[(n & ~31) + scale_single_pos(n & 31)]);
-
-      bool part_o[NOWN];
-      uint32_t acc_addr[NOWN];
+        if (n_ok) {
 #pragma unroll
-      for (int o = 0; o < NOWN; ++o) {
-        const int hu0 = 2 * it0 + ((o - 2 * it0) & (NOWN - 1));
-        part_o[o] = hu0 < 2 * it1;
-        const int ab = uo[o] % NBUF;
-        acc_addr[o] = tmem_base + ((uint32_t)(32 * qd) << 16) + Cfg::ACC_COL0 + (o * NBUF + ab) * MPAD;
-        if (part_o[o]) mbar_wait(accfull_bar(o, ab), (uo[o] / NBUF) & 1);
-      }
-      PROF_ACC(p_wacc);
-      tc_fence_after();
-#pragma unroll
-      for (int ch = 0; ch < NCH; ++ch) {
-        const int j0 = ch * 16;
-        if (j0 < m_valid) {
-          float v[16];
-#pragma unroll
-          for (int j = 0; j < 16; ++j) v[j] = 0.f;
-#pragma unroll
-          for (int o = 0; o < NOWN; ++o) {
-            if (part_o[o]) {
-              uint32_t t[16];
-              tmem_ld_32x32b_x16(acc_addr[o] + j0, t);
-              tc_wait_ld();
-#pragma unroll
-              for (int j = 0; j < 16; ++j) v[j] += __uint_as_float(t[j]);
-            }
-          }
-          if (full_k || owner) {
-            if (owner) {
-              if constexpr (kPrefetch) {
-#pragma unroll
-                for (int j = 0; j < 16; ++j) v[j] += psum[j0 + j];
-              } else {
-                for (int b = 1; b <= n_other; ++b) {
-                  const float* src = args.scratch + (size_t)(blockIdx.x + b) * (kTileN * MPAD) + j0 * kTileN + row;
-#pragma unroll
-                  for (int j = 0; j < 16; ++j)
-                    if (j0 + j < m_valid) v[j] += __ldcg(src + j * kTileN);
-                }
-              }
-            }
-            if (n_ok) {
-#pragma unroll
-              for (int j = 0; j < 16; ++j)
-                if (j0 + j < m_valid) cdst[(size_t)(j0 + j) * args.N] = from_f32<T>(v[j] * ch_scale);
-            }
-          } else if (clustered) {
-            // partial of this CTA's K slice -> own shared memory (the activation ring is dead once the last MMA of the
-            // segment has completed), laid out [m][128 channels]
-            float* red = reinterpret_cast<float*>(smem_gen + (act_base - smem_base));
-#pragma unroll
-            for (int j = 0; j < 16; ++j)
-              if (j0 + j < m_valid) red[(j0 + j) * kTileN + row] = v[j];
-          } else {
-#pragma unroll
-            for (int j = 0; j < 16; ++j)
-              if (j0 + j < m_valid) part_dst[(j0 + j) * kTileN + row] = v[j];
-          }
+          for (int j = 0; j < MPAD; ++j)
+            if (j < m_valid) cdst[(size_t)j * args.N] = from_f32<T>(acc[j] * ch_scale);
         }
-      }
-      tc_fence_before();
-      __syncwarp();
+      } else if (clustered) {
+        // partial of this CTA's K slice -> own shared memory (the activation ring is dead: every MMA of this CTA has
+        // completed, or the accumulators above could not have been read), laid out [m][128 channels]
+        float* red = reinterpret_cast<float*>(smem_gen + (act_base - smem_base));
 #pragma unroll
-      for (int o = 0; o < NOWN; ++o) {
-        if (part_o[o]) {
-          if (lane == 0) mbar_arrive(accempty_bar(o, uo[o] % NBUF));
-          ++uo[o];
-        }
-      }
-      if (clustered && !full_k) {
+        for (int j = 0; j < MPAD; ++j)
+          if (j < m_valid) red[j * kTileN + row] = acc[j];
         // cluster barrier 1: every CTA's partial is in its shared memory; rank r then finishes rows m = r, r + S, ...
         cluster_arrive();
         cluster_wait();
@@ -629,21 +637,25 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
             const int m = mb + i * CS;
-            float acc = 0.f;
+            float a2 = 0.f;
 #pragma unroll
-            for (int c = 0; c < 8; ++c) acc += pv[i][c];
-            if (n_ok && m < m_valid) cdst[(size_t)m * args.N] = from_f32<T>(acc * ch_scale);
+            for (int c = 0; c < 8; ++c) a2 += pv[i][c];
+            if (n_ok && m < m_valid) cdst[(size_t)m * args.N] = from_f32<T>(a2 * ch_scale);
           }
         }
-      } else if (!full_k && !owner) {
+      } else {
+        float* part_dst = args.scratch + (size_t)blockIdx.x * (kTileN * MPAD);
+#pragma unroll
+        for (int j = 0; j < MPAD; ++j)
+          if (j < m_valid) part_dst[j * kTileN + row] = acc[j];
         __threadfence();
         asm volatile("bar.sync 1, 128;" ::: "memory");
         if (et == 0) atomicAdd(&args.counters[tile], 1);
       }
       u += len;
-      PROF_ACC(p_epi);
+      PROF_ACC(p_red);
     }
-    if (args.prof && et == 0) { long long* q = args.prof + blockIdx.x * 16; q[13] = p_wacc; q[14] = p_epi; q[15] = p_red; }
+    if (PROF_ON(args.prof) && et == 0) { long long* q = args.prof + blockIdx.x * 16; q[13] = p_wacc; q[14] = p_epi; q[15] = p_red; }
   }
 
   if (clustered) {
@@ -658,8 +670,8 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
   }
   tc_fence_before();
   __syncthreads();
-  if (args.prof && threadIdx.x == 0) { args.prof[blockIdx.x * 16 + 11] = clock64() - k_t0; args.prof[blockIdx.x * 16 + 12] = n_units; }
-  if (warp == kAllocWarp) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+  if (PROF_ON(args.prof) && threadIdx.x == 0) { args.prof[blockIdx.x * 16 + 11] = clock64() - k_t0; args.prof[blockIdx.x * 16 + 12] = n_units; }
+  if (warp == kAllocWarp) tmem_dealloc<Cfg::TMEM_COLS>(*reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base)));
 }
 
 // ---- host side: one launch ---------------------------------------------------------------------------------------
@@ -680,6 +692,11 @@ int launch_gemm(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t s
   cudaGetDevice(&dev);
   static bool attr_set[64] = {};
   if (!attr_set[dev & 63]) {
+    // setmaxnreg.inc in the epilogue warps can only be satisfied if the launch really reserves REG_LAUNCH per thread
+    cudaFuncAttributes fa;
+    if (cudaFuncGetAttributes(&fa, kern) != cudaSuccess || fa.numRegs != Cfg::REG_LAUNCH)
+      return set_error(B200_ECUDA, "marlin gemm: kernel built with %d registers per thread, the register re-balance needs %d",
+                       fa.numRegs, Cfg::REG_LAUNCH);
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
     attr_set[dev & 63] = true;
   }
@@ -736,7 +753,11 @@ int launch_gemm(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t s
   if (!ok)
     return set_error(B200_ECUDA, "marlin gemm: cuTensorMapEncodeTiled failed (A=%p M=%d K=%d N=%d lda=%lld)", A, a.M, a.K,
                      a.N, (long long)lda);
+#ifdef B200_GEMM_PROF
   static const bool prof_on = getenv("B200_GEMM_PROF") != nullptr;
+#else
+  static const bool prof_on = false;
+#endif
   a.prof = nullptr;
   if (prof_on) { cudaMallocManaged(&a.prof, sizeof(long long) * 16 * grid); cudaMemset(a.prof, 0, sizeof(long long) * 16 * grid); }
   cudaLaunchConfig_t cfg = {};
@@ -767,7 +788,7 @@ int launch_gemm(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t s
     static const char* names[16] = {"-", "-", "mma.wait_accempty", "mma.wait_full", "mma.wait_afull", "mma.issue",
                                     "deq.wait_full", "deq.lds", "deq.wait_aempty", "deq.compute", "deq.st", "cta.total", "cta.units",
                                     "epi.wait_accfull", "epi.work", "epi.reduce_prefetch"};
-    fprintf(stderr, "[gemm prof] M=%d N=%d K=%d MPAD=%d grid=%d stages=%d:", a.M, a.N, a.K, MPAD, grid, Cfg::NSTAGES);
+    fprintf(stderr, "[gemm prof] M=%d N=%d K=%d MPAD=%d grid=%d stages=%d:", a.M, a.N, a.K, MPAD, grid, Cfg::NW);
     for (int i = 2; i < 16; ++i) {
       double sum = 0, mx = 0;
       for (int b = 0; b < grid; ++b) { sum += (double)a.prof[b * 16 + i]; if ((double)a.prof[b * 16 + i] > mx) mx = (double)a.prof[b * 16 + i]; }
