@@ -60,12 +60,15 @@ struct GemmCfg {
   static constexpr int NBUF = MPAD <= 32 ? 2 : 1;                    // accumulator buffers per own-group
   static constexpr int NDQ = 4 * NOWN;                               // dequant warps
   static constexpr int EPI_WARP0 = kDequantWarp0 + NDQ;
-  static constexpr int THREADS = (EPI_WARP0 + 4) * 32;
+  static constexpr int NEG = MPAD >= 64 ? 2 : 1;                     // epilogue warpgroups: each takes MPAD / NEG of the columns
+  static constexpr int NEPI = 4 * NEG;                               // epilogue warps
+  static constexpr int ACCW = MPAD / NEG;                            // fp32 accumulators per epilogue thread
+  static constexpr int THREADS = (EPI_WARP0 + NEPI) * 32;
   // registers per thread: at launch (what ptxas may use under __launch_bounds__(THREADS, 1)), after setmaxnreg.dec in
-  // warps 0-7, and after setmaxnreg.inc in the 4 epilogue warps (they take exactly what warps 0-7 gave back)
+  // warps 0-7, and after setmaxnreg.inc in the epilogue warps (they take what warps 0-7 gave back)
   static constexpr int REG_LAUNCH = ((65536 / THREADS) / 8) * 8;
-  static constexpr int REG_LOW = 48;
-  static constexpr int REG_EPI = REG_LAUNCH + 2 * (REG_LAUNCH - REG_LOW);
+  static constexpr int REG_LOW = 40;
+  static constexpr int REG_EPI = ((REG_LAUNCH + (256 * (REG_LAUNCH - REG_LOW)) / (NEPI * 32)) / 8) * 8;
   static constexpr int ACC_COL0 = 64 * NOWN;                         // TMEM: [own-group operand slots][accumulators]
   static constexpr int TMEM_COLS = 512;
   static constexpr int W_ROW_BYTES = kTileN * 16 * BITS / 8;         // one 16(k) x 128(n) slab: 1024 (4-bit) / 2048 (8-bit)
@@ -285,7 +288,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       mbar_init(actfull_bar(s), 1);
       // the two issuers' commits + whoever reads the staged group scales: the 4 epilogue warps (g128) or the 8 dequant
       // warps of the two halves (small groups)
-      mbar_init(actempty_bar(s), 2 + (GM == kGroup128 ? 4 : (GM == kGroupSmall ? 8 : 0)));
+      mbar_init(actempty_bar(s), 2 + (GM == kGroup128 ? Cfg::NEPI : (GM == kGroupSmall ? 8 : 0)));
     }
     for (int o = 0; o < NOWN; ++o) {
       for (int sub = 0; sub < 2; ++sub) {
@@ -294,7 +297,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       }
       for (int b = 0; b < NBUF; ++b) {
         mbar_init(accfull_bar(o, b), 1);
-        mbar_init(accempty_bar(o, b), 4);
+        mbar_init(accempty_bar(o, b), Cfg::NEPI);
       }
     }
     fence_barrier_init();
@@ -524,8 +527,10 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     const uint32_t tmem_base = get_tmem_base();
     const int qd = warp & 3;
     const int row = 32 * qd + lane;  // output channel within the tile == TMEM lane
-    const int et = threadIdx.x - Cfg::EPI_WARP0 * 32;  // 0..127
-    constexpr int CH = MPAD < 32 ? MPAD : 32;          // accumulator columns per TMEM read batch
+    const int et = threadIdx.x - Cfg::EPI_WARP0 * 32;  // 0 .. 32 NEPI - 1
+    constexpr int ACCW = Cfg::ACCW;                    // this thread's share of the MPAD columns (m) of its channel:
+    const int jb = (et >> 7) * ACCW;                   // columns jb .. jb + ACCW - 1 (two warpgroups split them at MPAD >= 64)
+    constexpr int CH = ACCW < 32 ? ACCW : 32;          // accumulator columns per TMEM read batch
     // position of this channel's scale in a staged 128-column scale row (scale_perm, 64-chunks: pos 8 c + b' <-> col c + 8 b')
     const uint8_t* ssm_e = smem_gen + (sc_base - smem_base) + 2 * (64 * (row >> 6) + 8 * (row & 7) + ((row & 63) >> 3));
     const uint32_t acc_lane = tmem_base + ((uint32_t)(32 * qd) << 16) + Cfg::ACC_COL0;
@@ -544,9 +549,9 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       const bool full_k = (ks0 == 0 && len == KS);
       const bool owner = (ks0 == 0 && !full_k && !clustered);   // this CTA reduces the tile; the others only contribute
       T* cdst = reinterpret_cast<T*>(args.C) + (size_t)m0 * args.N + n;
-      float acc[MPAD];
+      float acc[ACCW];
 #pragma unroll
-      for (int j = 0; j < MPAD; ++j) acc[j] = 0.f;
+      for (int j = 0; j < ACCW; ++j) acc[j] = 0.f;
       for (int hu = 2 * it0; hu < 2 * it1; ++hu) {
         const int o = hu & (NOWN - 1), jc = hu / NOWN, ab = jc % NBUF;
         if (GM == kGroup128 && (hu & 1) == 0) {
@@ -563,14 +568,14 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         mbar_wait(accfull_bar(o, ab), (jc / NBUF) & 1);
         PROF_ACC(p_wacc);
         tc_fence_after();
-        const uint32_t src = acc_lane + (o * NBUF + ab) * MPAD;
+        const uint32_t src = acc_lane + (o * NBUF + ab) * MPAD + jb;
 #pragma unroll
-        for (int c0 = 0; c0 < MPAD; c0 += CH) {
+        for (int c0 = 0; c0 < ACCW; c0 += CH) {
           uint32_t t[CH];
 #pragma unroll
           for (int c1 = 0; c1 < CH; c1 += 16) tmem_ld_32x32b_x16(src + c0 + c1, *reinterpret_cast<uint32_t(*)[16]>(&t[c1]));
           tc_wait_ld();
-          if (c0 + CH == MPAD) {
+          if (c0 + CH == ACCW) {
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(accempty_bar(o, ab));
@@ -587,8 +592,8 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       if (full_k) {
         if (n_ok) {
 #pragma unroll
-          for (int j = 0; j < MPAD; ++j)
-            if (j < m_valid) cdst[(size_t)j * args.N] = from_f32<T>(acc[j] * ch_scale);
+          for (int j = 0; j < ACCW; ++j)
+            if (jb + j < m_valid) cdst[(size_t)(jb + j) * args.N] = from_f32<T>(acc[j] * ch_scale);
         }
       } else if (owner) {
         // contributors are the CTAs after this one whose unit ranges intersect [tile*KS, (tile+1)*KS); for each of them
@@ -599,33 +604,33 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
           while (ld_acquire_gpu(&args.counters[tile]) < n_other) {}
           args.counters[tile] = 0;   // self-reset: exactly n_other increments ever arrive
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, %0;" ::"n"(Cfg::NEPI * 32) : "memory");
         __threadfence();
         for (int b = 1; b <= n_other; ++b) {
           const float* src = args.scratch + (size_t)(blockIdx.x + b) * (kTileN * MPAD) + row;
 #pragma unroll
-          for (int j = 0; j < MPAD; ++j)
-            if (j < m_valid) acc[j] += __ldcg(src + j * kTileN);
+          for (int j = 0; j < ACCW; ++j)
+            if (jb + j < m_valid) acc[j] += __ldcg(src + (jb + j) * kTileN);
         }
         PROF_ACC(p_red);
         if (n_ok) {
 #pragma unroll
-          for (int j = 0; j < MPAD; ++j)
-            if (j < m_valid) cdst[(size_t)j * args.N] = from_f32<T>(acc[j] * ch_scale);
+          for (int j = 0; j < ACCW; ++j)
+            if (jb + j < m_valid) cdst[(size_t)(jb + j) * args.N] = from_f32<T>(acc[j] * ch_scale);
         }
       } else if (clustered) {
         // partial of this CTA's K slice -> own shared memory (the activation ring is dead: every MMA of this CTA has
         // completed, or the accumulators above could not have been read), laid out [m][128 channels]
         float* red = reinterpret_cast<float*>(smem_gen + (act_base - smem_base));
 #pragma unroll
-        for (int j = 0; j < MPAD; ++j)
-          if (j < m_valid) red[j * kTileN + row] = acc[j];
+        for (int j = 0; j < ACCW; ++j)
+          if (jb + j < m_valid) red[(jb + j) * kTileN + row] = acc[j];
         // cluster barrier 1: every CTA's partial is in its shared memory; rank r then finishes rows m = r, r + S, ...
         cluster_arrive();
         cluster_wait();
         const uint32_t red_u32 = act_base + (uint32_t)row * 4u;
         // all remote loads of a group of rows are issued before the first add: DSMEM latency is paid once per group
-        for (int mb = c_rank; mb < m_valid; mb += 4 * CS) {
+        for (int mb = c_rank + (et >> 7) * 4 * CS; mb < m_valid; mb += 4 * CS * Cfg::NEG) {
           float pv[4][8];
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
@@ -646,10 +651,10 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       } else {
         float* part_dst = args.scratch + (size_t)blockIdx.x * (kTileN * MPAD);
 #pragma unroll
-        for (int j = 0; j < MPAD; ++j)
-          if (j < m_valid) part_dst[j * kTileN + row] = acc[j];
+        for (int j = 0; j < ACCW; ++j)
+          if (jb + j < m_valid) part_dst[(jb + j) * kTileN + row] = acc[j];
         __threadfence();
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, %0;" ::"n"(Cfg::NEPI * 32) : "memory");
         if (et == 0) atomicAdd(&args.counters[tile], 1);
       }
       u += len;
