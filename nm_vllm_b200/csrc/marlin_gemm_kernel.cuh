@@ -81,11 +81,15 @@ struct GemmCfg {
   // activations + group scales (L2 latency, released when the MMAs that read them have completed)
   static constexpr int NA = MPAD <= 32 ? 4 : (MPAD == 64 ? 3 : 2);
   static constexpr int AS_STAGE_BYTES = A_STAGE_BYTES + S_STAGE_BYTES;
-  static constexpr int NW_RAW = (208 * 1024 - NA * AS_STAGE_BYTES) / W_STAGE_BYTES;
+  // a third, small ring: the two g128 scale rows of each stage (512 B), read by the epilogue warps -- deep enough that
+  // neither the weight producer (at most NW stages ahead of the dequant warps) nor the epilogue ever waits on it
+  static constexpr int NSC = 16;
+  static constexpr int SCQ_STAGE_BYTES = 512;
+  static constexpr int NW_RAW = (218 * 1024 - NA * AS_STAGE_BYTES - NSC * SCQ_STAGE_BYTES) / W_STAGE_BYTES;
   static constexpr int NW = NW_RAW > 12 ? 12 : NW_RAW;
-  static constexpr int NBARS = 2 * NW + 2 * NA + 4 * NOWN + 2 * NOWN * NBUF;
+  static constexpr int NBARS = 2 * NW + 2 * NA + 4 * NOWN + 2 * NOWN * NBUF + 2 * NSC;
   static constexpr int BAR_BYTES = NBARS * 8 + 16;
-  static constexpr int SMEM_BYTES = 1024 /*align slack*/ + NW * W_STAGE_BYTES + NA * AS_STAGE_BYTES + BAR_BYTES;
+  static constexpr int SMEM_BYTES = 1024 /*align slack*/ + NW * W_STAGE_BYTES + NA * AS_STAGE_BYTES + NSC * SCQ_STAGE_BYTES + BAR_BYTES;
   static_assert(NW >= 2 && NA >= 2, "pipeline needs at least two stages per ring");
   static_assert(ACC_COL0 + NOWN * NBUF * MPAD <= 512, "TMEM budget");
   static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
@@ -104,6 +108,8 @@ struct GemmArgs {
   int groups_per_stage;        // scale rows staged per stage: 0 (channelwise), 2, 4 or 8
   int cluster_s;               // > 1: each tile's K range is split over a cluster of this many CTAs (DSMEM reduce)
   long long* prof;             // bring-up cycle counters [grid][16] (B200_GEMM_PROF), nullptr in production
+  long long* trace;            // bring-up event trace of CTA trace_cta [11 roles][64][8]
+  int trace_cta;
 };
 
 // ---- dequantisation ------------------------------------------------------------------------------------------
@@ -242,7 +248,10 @@ __device__ __forceinline__ int ld_acquire_gpu(const int* p) {
 #ifdef B200_GEMM_PROF
 #define PROF_ON(x) (x)
 #define PROF_ACC(var) if (args.prof) { const long long p_t1 = clock64(); var += p_t1 - p_mark; p_mark = p_t1; }
+// event trace of ONE CTA (B200_GEMM_TRACE=<cta>): trace[role][idx][ev] = clock64()
+#define TRACE(role, idx, ev) if (args.trace && (int)blockIdx.x == args.trace_cta && lane == 0 && (idx) < 64) { args.trace[((role) * 64 + (idx)) * 8 + (ev)] = clock64(); }
 #else
+#define TRACE(role, idx, ev)
 #define PROF_ON(x) false
 #define PROF_ACC(var)
 #endif
@@ -260,7 +269,9 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
   const uint32_t act_base = smem_base;
   const uint32_t w_base = act_base + NA * Cfg::A_STAGE_BYTES;
   const uint32_t sc_base = w_base + NW * Cfg::W_STAGE_BYTES;
-  const uint32_t bar_base = sc_base + NA * Cfg::S_STAGE_BYTES;
+  const uint32_t scq_base = sc_base + NA * Cfg::S_STAGE_BYTES;
+  const uint32_t bar_base = scq_base + Cfg::NSC * Cfg::SCQ_STAGE_BYTES;
+  constexpr int NSC = Cfg::NSC;
   constexpr int NR = 2 * NW + 2 * NA;   // ring barriers
   auto wfull_bar = [&](int s) { return bar_base + 8u * s; };
   auto wempty_bar = [&](int s) { return bar_base + 8u * (NW + s); };
@@ -270,36 +281,39 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
   auto aempty_bar = [&](int o, int sub) { return bar_base + 8u * (NR + 2 * NOWN + 2 * o + sub); };
   auto accfull_bar = [&](int o, int b) { return bar_base + 8u * (NR + 4 * NOWN + o * NBUF + b); };
   auto accempty_bar = [&](int o, int b) { return bar_base + 8u * (NR + 4 * NOWN + NOWN * NBUF + o * NBUF + b); };
+  auto scfull_bar = [&](int s) { return bar_base + 8u * (NR + 4 * NOWN + 2 * NOWN * NBUF + s); };
+  auto scempty_bar = [&](int s) { return bar_base + 8u * (NR + 4 * NOWN + 2 * NOWN * NBUF + NSC + s); };
   const uint32_t tmem_slot = bar_base + 8u * Cfg::NBARS;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));  // generic pointer to the aligned base
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long k_t0 = PROF_ON(args.prof) ? clock64() : 0;
+  if (threadIdx.x == 0) { TRACE(9, 63, 7); }
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmap_w);
     prefetch_tmap(&tmap_a);
     if (GM != kChannelwise) prefetch_tmap(&tmap_s);
-    for (int s = 0; s < NW; ++s) {
-      mbar_init(wfull_bar(s), 1);
-      mbar_init(wempty_bar(s), 8);   // 2 halves x 4 dequant quarter warps
+  }
+  if (threadIdx.x >= 32 && threadIdx.x < 32 + Cfg::NBARS) {
+    // one barrier per thread (a serial loop over ~60 barriers costs more than a microsecond of every launch)
+    const int i = threadIdx.x - 32;
+    uint32_t cnt;
+    if (i < NW) cnt = 1;                       // wfull: the producer's expect_tx arrive
+    else if (i < 2 * NW) cnt = 8;              // wempty: 2 halves x 4 dequant quarter warps
+    else if (i < 2 * NW + NA) cnt = 1;         // actfull
+    else if (i < NR) cnt = 2 + (GM == kGroupSmall ? 8 : 0);   // actempty: the two issuers' commits (+ the 8 dequant
+                                               // warps of the two halves, which read the staged small-group scales)
+    else {
+      const int k = i - NR;
+      if (k < 2 * NOWN) cnt = 4;                              // afull: 4 dequant quarter warps
+      else if (k < 4 * NOWN) cnt = 1;                         // aempty: issuer commit
+      else if (k < 4 * NOWN + NOWN * NBUF) cnt = 1;           // accfull: issuer commit
+      else if (k < 4 * NOWN + 2 * NOWN * NBUF) cnt = Cfg::NEPI;   // accempty: every epilogue warp
+      else if (k < 4 * NOWN + 2 * NOWN * NBUF + NSC) cnt = 1;     // scfull
+      else cnt = Cfg::NEPI;                                       // scempty: every epilogue warp
     }
-    for (int s = 0; s < NA; ++s) {
-      mbar_init(actfull_bar(s), 1);
-      // the two issuers' commits + whoever reads the staged group scales: the 4 epilogue warps (g128) or the 8 dequant
-      // warps of the two halves (small groups)
-      mbar_init(actempty_bar(s), 2 + (GM == kGroup128 ? Cfg::NEPI : (GM == kGroupSmall ? 8 : 0)));
-    }
-    for (int o = 0; o < NOWN; ++o) {
-      for (int sub = 0; sub < 2; ++sub) {
-        mbar_init(afull_bar(o, sub), 4);
-        mbar_init(aempty_bar(o, sub), 1);
-      }
-      for (int b = 0; b < NBUF; ++b) {
-        mbar_init(accfull_bar(o, b), 1);
-        mbar_init(accempty_bar(o, b), Cfg::NEPI);
-      }
-    }
+    mbar_init(bar_base + 8u * i, cnt);
     fence_barrier_init();
   }
   __syncthreads();            // barriers are live: the producers start streaming weights right away
@@ -346,9 +360,11 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     if (warp == 0) {
       // weights do not depend on the previous kernel of the stream: no PDL wait on this path at all
       const uint64_t pol_w = policy_evict_first();   // weights are streamed exactly once
+      const uint64_t pol_s = policy_evict_first();
       for (int it = 0; it < n_units; ++it) {
         const int s = it % NW;
         if (it >= NW) mbar_wait(wempty_bar(s), ((it / NW) & 1) ^ 1);
+        TRACE(9, it, 0);
         int nt, mc, ks;
         coords(it, nt, mc, ks);
         if (elect_one()) {
@@ -357,20 +373,31 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
                           wfull_bar(s), pol_w);
         }
         __syncwarp();
+        if (GM == kGroup128) {
+          // the stage's two group-scale rows (static data like the weights) -> the epilogue's scale ring
+          const int q = it % NSC;
+          if (it >= NSC) mbar_wait(scempty_bar(q), ((it / NSC) & 1) ^ 1);
+          if (elect_one()) {
+            mbar_arrive_expect_tx(scfull_bar(q), Cfg::SCQ_STAGE_BYTES);
+            tma_2d_g2s_hint(scq_base + q * Cfg::SCQ_STAGE_BYTES, &tmap_s, nt * kTileN, ks * 2, scfull_bar(q), pol_s);
+          }
+          __syncwarp();
+        }
       }
     } else {
       const uint64_t pol_a = policy_evict_last();    // activations / scales are re-read by every CTA
-      const uint32_t tx = Cfg::A_STAGE_BYTES + (GM != kChannelwise ? (uint32_t)gps * 256u : 0u);
+      const uint32_t tx = Cfg::A_STAGE_BYTES + (GM == kGroupSmall ? (uint32_t)gps * 256u : 0u);
       pdl_wait();
       for (int it = 0; it < n_units; ++it) {
         const int s = it % NA;
         if (it >= NA) mbar_wait(actempty_bar(s), ((it / NA) & 1) ^ 1);
+        TRACE(10, it, 0);
         int nt, mc, ks;
         coords(it, nt, mc, ks);
         if (elect_one()) {
           mbar_arrive_expect_tx(actfull_bar(s), tx);
           tma_3d_g2s_hint(act_base + s * Cfg::A_STAGE_BYTES, &tmap_a, 0, mc * MPAD, ks * (kStageK / 64), actfull_bar(s), pol_a);
-          if (GM != kChannelwise)
+          if (GM == kGroupSmall)
             tma_2d_g2s_hint(sc_base + s * Cfg::S_STAGE_BYTES, &tmap_s, nt * kTileN, ks * gps, actfull_bar(s), pol_a);
         }
         __syncwarp();
@@ -380,6 +407,16 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     setmaxnreg_dec<Cfg::REG_LOW>();
     if (warp == kAllocWarp) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
     (void)get_tmem_base();
+    if (warp == kAllocWarp + 1 && !clustered && n_units > 0 && (u_begin % KS) != 0) {
+      // stream-K contributor: this CTA's first segment starts inside a tile, so its partial goes to the tile's owner.
+      // The epilogue warps store it and arrive on named barrier 3; this warp publishes it.
+      pdl_wait();
+      asm volatile("bar.sync 3, %0;" ::"n"(Cfg::NEPI * 32 + 32) : "memory");
+      if (lane == 0) {
+        __threadfence();
+        atomicAdd(&args.counters[u_begin / KS], 1);
+      }
+    }
   } else if (warp < kDequantWarp0) {
     setmaxnreg_dec<Cfg::REG_LOW>();
     const uint32_t tmem_base = get_tmem_base();
@@ -396,15 +433,18 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       const int ab = jc % NBUF;
       mbar_wait(accempty_bar(o, ab), ((jc / NBUF) & 1) ^ 1);
       PROF_ACC(p_wacc);
+      TRACE(o, jc, 0);
       const uint32_t d_tmem = tmem_base + Cfg::ACC_COL0 + (o * NBUF + ab) * MPAD;
       const int it = hu >> 1, s = it % NA;
       mbar_wait(actfull_bar(s), (it / NA) & 1);
       PROF_ACC(p_wfull);
+      TRACE(o, jc, 1);
       const uint32_t b_smem = act_base + s * Cfg::A_STAGE_BYTES;
 #pragma unroll
       for (int sub = 0; sub < 2; ++sub) {
         mbar_wait(afull_bar(o, sub), jc & 1);
         PROF_ACC(p_wafull);
+        TRACE(o, jc, 2 + 2 * sub);
         tc_fence_after();
         if (elect_one()) {
 #pragma unroll
@@ -422,6 +462,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         }
         __syncwarp();
         PROF_ACC(p_issue);
+        TRACE(o, jc, 3 + 2 * sub);
       }
     }
     if (PROF_ON(args.prof) && o == 0 && lane == 0) { long long* q = args.prof + blockIdx.x * 16; q[2] = p_wacc; q[3] = p_wfull; q[4] = p_wafull; q[5] = p_issue; }
@@ -448,6 +489,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       const int s = it % NW, sa = it % NA;
       mbar_wait(wfull_bar(s), (it / NW) & 1);
       PROF_ACC(p_wfull);
+      if (qd == 0) TRACE(4 + o, jc, 0);
       // packed words of this thread for all 8 slabs: 64-chunk t64, fragment lane, n16-tiles (2 jpair, 2 jpair + 1)
       uint32_t w[kSlabs][WPT];
 #pragma unroll
@@ -477,6 +519,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       if (lane == 0) mbar_arrive(wempty_bar(s));
       if (GM == kGroupSmall) mbar_wait(actfull_bar(sa), (it / NA) & 1);   // the staged scale rows ride with the activations
       PROF_ACC(p_lds);
+      if (qd == 0) TRACE(4 + o, jc, 1);
 #pragma unroll
       for (int sub = 0; sub < 2; ++sub) {
 #pragma unroll
@@ -500,6 +543,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
           if (jj == 0) {
             mbar_wait(aempty_bar(o, sub), (jc & 1) ^ 1);
             PROF_ACC(p_waempty);
+            if (qd == 0) TRACE(4 + o, jc, 2 + 2 * sub);
             tc_fence_after();
           }
           tmem_st_16x128b_x8(a_col + ((uint32_t)(16 * jj) << 16) + sub * 32, ov);
@@ -509,6 +553,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         __syncwarp();
         if (lane == 0) mbar_arrive(afull_bar(o, sub));
         PROF_ACC(p_st);
+        if (qd == 0) TRACE(4 + o, jc, 3 + 2 * sub);
       }
       if (GM == kGroupSmall) {
         __syncwarp();
@@ -531,12 +576,11 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     constexpr int ACCW = Cfg::ACCW;                    // this thread's share of the MPAD columns (m) of its channel:
     const int jb = (et >> 7) * ACCW;                   // columns jb .. jb + ACCW - 1 (two warpgroups split them at MPAD >= 64)
     constexpr int CH = ACCW < 32 ? ACCW : 32;          // accumulator columns per TMEM read batch
-    // position of this channel's scale in a staged 128-column scale row (scale_perm, 64-chunks: pos 8 c + b' <-> col c + 8 b')
-    const uint8_t* ssm_e = smem_gen + (sc_base - smem_base) + 2 * (64 * (row >> 6) + 8 * (row & 7) + ((row & 63) >> 3));
+    // position of this channel's scale in a 128-column slice of a scale row (scale_perm, 64-chunks: pos 8 c + b' <-> col c + 8 b')
+    const int sc_pos = 64 * (row >> 6) + 8 * (row & 7) + ((row & 63) >> 3);
     const uint32_t acc_lane = tmem_base + ((uint32_t)(32 * qd) << 16) + Cfg::ACC_COL0;
     pdl_wait();   // C, the partial slots and the tile counters may still be in use by the previous kernel
     long long p_mark = PROF_ON(args.prof) ? clock64() : 0, p_wacc = 0, p_epi = 0, p_red = 0;
-    float sc_h[2] = {1.f, 1.f};
     for (int u = u_begin; u < u_end;) {
       const int tile = u / KS, ks0 = u - tile * KS;
       const int len = min(KS - ks0, u_end - u);
@@ -552,21 +596,24 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       float acc[ACCW];
 #pragma unroll
       for (int j = 0; j < ACCW; ++j) acc[j] = 0.f;
+      float sc_h[2] = {1.f, 1.f};
       for (int hu = 2 * it0; hu < 2 * it1; ++hu) {
         const int o = hu & (NOWN - 1), jc = hu / NOWN, ab = jc % NBUF;
         if (GM == kGroup128 && (hu & 1) == 0) {
-          // both group scales of this stage, then release the stage (the full barrier completed long ago: the MMAs
-          // of the previous half stage, which this thread has just consumed, were issued after it)
-          const int it = hu >> 1, s = it % NA;
-          mbar_wait(actfull_bar(s), (it / NA) & 1);
-          sc_h[0] = to_f32<T>(*reinterpret_cast<const T*>(ssm_e + s * Cfg::S_STAGE_BYTES));
-          sc_h[1] = to_f32<T>(*reinterpret_cast<const T*>(ssm_e + s * Cfg::S_STAGE_BYTES + 256));
+          // both group scales of this stage from the scale ring, then release the slot
+          const int it = hu >> 1, q = it % NSC;
+          mbar_wait(scfull_bar(q), (it / NSC) & 1);
+          const uint8_t* sp = smem_gen + (scq_base - smem_base) + q * Cfg::SCQ_STAGE_BYTES + 2 * sc_pos;
+          sc_h[0] = to_f32<T>(*reinterpret_cast<const T*>(sp));
+          sc_h[1] = to_f32<T>(*reinterpret_cast<const T*>(sp + 256));
           __syncwarp();
-          if (lane == 0) mbar_arrive(actempty_bar(s));
+          if (lane == 0) mbar_arrive(scempty_bar(q));
         }
         const float sc = sc_h[hu & 1];
+        if (et < 32) TRACE(8, hu, 0);
         mbar_wait(accfull_bar(o, ab), (jc / NBUF) & 1);
         PROF_ACC(p_wacc);
+        if (et < 32) TRACE(8, hu, 1);
         tc_fence_after();
         const uint32_t src = acc_lane + (o * NBUF + ab) * MPAD + jb;
 #pragma unroll
@@ -576,6 +623,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
           for (int c1 = 0; c1 < CH; c1 += 16) tmem_ld_32x32b_x16(src + c0 + c1, *reinterpret_cast<uint32_t(*)[16]>(&t[c1]));
           tc_wait_ld();
           if (c0 + CH == ACCW) {
+            if (et < 32) TRACE(8, hu, 2);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(accempty_bar(o, ab));
@@ -584,6 +632,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
           for (int j = 0; j < CH; ++j) acc[c0 + j] = fmaf(sc, __uint_as_float(t[j]), acc[c0 + j]);
         }
         PROF_ACC(p_epi);
+        if (et < 32) TRACE(8, hu, 3);
       }
       float ch_scale = 1.f;
       if (GM == kChannelwise && n_ok)
@@ -653,9 +702,9 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
 #pragma unroll
         for (int j = 0; j < ACCW; ++j)
           if (jb + j < m_valid) part_dst[(jb + j) * kTileN + row] = acc[j];
-        __threadfence();
-        asm volatile("bar.sync 1, %0;" ::"n"(Cfg::NEPI * 32) : "memory");
-        if (et == 0) atomicAdd(&args.counters[tile], 1);
+        // hand the "partial is complete" signal to the idle warp 3 (named barrier 3: arrive here, sync there): the
+        // gpu-scope fence costs microseconds under load and these warps have accumulators to drain
+        asm volatile("bar.arrive 3, %0;" ::"n"(Cfg::NEPI * 32 + 32) : "memory");
       }
       u += len;
       PROF_ACC(p_red);
@@ -675,6 +724,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
   }
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) { TRACE(10, 63, 7); }
   if (PROF_ON(args.prof) && threadIdx.x == 0) { args.prof[blockIdx.x * 16 + 11] = clock64() - k_t0; args.prof[blockIdx.x * 16 + 12] = n_units; }
   if (warp == kAllocWarp) tmem_dealloc<Cfg::TMEM_COLS>(*reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base)));
 }
@@ -764,6 +814,15 @@ int launch_gemm(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t s
   static const bool prof_on = false;
 #endif
   a.prof = nullptr;
+  a.trace = nullptr;
+  a.trace_cta = 0;
+#ifdef B200_GEMM_PROF
+  if (prof_on && getenv("B200_GEMM_TRACE")) {
+    a.trace_cta = atoi(getenv("B200_GEMM_TRACE"));
+    cudaMallocManaged(&a.trace, sizeof(long long) * 11 * 64 * 8);
+    cudaMemset(a.trace, 0, sizeof(long long) * 11 * 64 * 8);
+  }
+#endif
   if (prof_on) { cudaMallocManaged(&a.prof, sizeof(long long) * 16 * grid); cudaMemset(a.prof, 0, sizeof(long long) * 16 * grid); }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
@@ -800,6 +859,14 @@ int launch_gemm(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t s
       fprintf(stderr, " %s=%.0f(max %.0f)", names[i], sum / grid, mx);
     }
     fprintf(stderr, "\n");
+    if (a.trace) {
+      const long long t0 = a.trace[(9 * 64 + 63) * 8 + 7];
+      for (int r = 0; r < 11; ++r)
+        for (int i = 0; i < 64; ++i)
+          for (int e = 0; e < 8; ++e)
+            if (a.trace[(r * 64 + i) * 8 + e]) fprintf(stderr, "[gemm trace] %d %d %d %lld\n", r, i, e, a.trace[(r * 64 + i) * 8 + e] - t0);
+      cudaFree(a.trace);
+    }
     cudaFree(a.prof);
   }
   return B200_OK;
