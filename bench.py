@@ -151,6 +151,16 @@ def count_launches(fn):
     return sum(counts.values()), counts
 
 
+def ncu_traffic():
+    """dram read+write bytes per launch of the dominant kernel from the committed `ncu --set full` capture
+    (profiles/r1_gemm_traffic.json, batch-64 decode step); None when the file is absent."""
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_gemm_traffic.json")) as f:
+            return float(json.load(f)["traffic_bytes_per_launch"])
+    except Exception:
+        return None
+
+
 def gemm_roofline(model, batch, peaks):
     """The dominant kernel timed ALONE: every Marlin GEMM of one step (4 per layer, distinct weights -> cold L2: the
     packed weights of one pass are 3.6 GB vs 126 MB of L2), CUDA events on the launching stream, 3 passes, median."""
@@ -199,7 +209,7 @@ def gemm_roofline(model, batch, peaks):
     peak = peaks.get("hbm_gbs", 6650.0)
     ach = alg / t / 1e9
     return {"bound": "hbm", "kernel": "marlin_gemm_kernel (gptq_marlin_gemm W4A16 g128)", "achieved": ach, "peak": peak,
-            "unit": "GB/s", "frac": ach / peak, "traffic": None,
+            "unit": "GB/s", "frac": ach / peak, "traffic": ncu_traffic(),
             "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650",
             "launches": len(lin), "alg_bytes_per_launch": alg / len(lin), "avg_launch_us": t / len(lin) * 1e6,
             "gemm_ms_per_step": t * 1e3}

@@ -135,7 +135,7 @@ extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_
   ga.KS = (int)((size_k + kStageK - 1) / kStageK);
   ga.total_units = 0;
   ga.groups_per_stage = num_groups > 1 ? kStageK / gs : 0;
-  ga.prof = nullptr; ga.trace = nullptr; ga.trace_cta = 0;
+  ga.prof = nullptr; ga.trace = nullptr; ga.trace_cta = 0; ga.exp = 0;
   ga.cluster_s = 0;
   int rc;
   if (dtype == B200_F16) rc = (num_bits == 4) ? dispatch_gemm_f16_4(ga, a, lda, st) : dispatch_gemm_f16_8(ga, a, lda, st);

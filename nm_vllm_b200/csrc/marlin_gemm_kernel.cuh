@@ -69,6 +69,7 @@ struct GemmCfg {
   static constexpr int REG_LAUNCH = ((65536 / THREADS) / 8) * 8;
   static constexpr int REG_LOW = 40;
   static constexpr int REG_EPI = ((REG_LAUNCH + (256 * (REG_LAUNCH - REG_LOW)) / (NEPI * 32)) / 8) * 8;
+  static constexpr bool DEFER_ST = MPAD <= 32;                       // needs 16 more registers in the dequant warps
   static constexpr int ACC_COL0 = 64 * NOWN;                         // TMEM: [own-group operand slots][accumulators]
   static constexpr int TMEM_COLS = 512;
   static constexpr int W_ROW_BYTES = kTileN * 16 * BITS / 8;         // one 16(k) x 128(n) slab: 1024 (4-bit) / 2048 (8-bit)
@@ -110,6 +111,7 @@ struct GemmArgs {
   long long* prof;             // bring-up cycle counters [grid][16] (B200_GEMM_PROF), nullptr in production
   long long* trace;            // bring-up event trace of CTA trace_cta [11 roles][64][8]
   int trace_cta;
+  int exp;                     // bring-up ablations (B200_GEMM_EXP, prof builds only): 1 no dequant ALU, 2 no MMAs, 3 no epilogue reads, 4 no TMEM stores
 };
 
 // ---- dequantisation ------------------------------------------------------------------------------------------
@@ -249,8 +251,10 @@ __device__ __forceinline__ int ld_acquire_gpu(const int* p) {
 #define PROF_ON(x) (x)
 #define PROF_ACC(var) if (args.prof) { const long long p_t1 = clock64(); var += p_t1 - p_mark; p_mark = p_t1; }
 // event trace of ONE CTA (B200_GEMM_TRACE=<cta>): trace[role][idx][ev] = clock64()
+#define EXP_IS(x) (args.exp == (x))
 #define TRACE(role, idx, ev) if (args.trace && (int)blockIdx.x == args.trace_cta && lane == 0 && (idx) < 64) { args.trace[((role) * 64 + (idx)) * 8 + (ev)] = clock64(); }
 #else
+#define EXP_IS(x) false
 #define TRACE(role, idx, ev)
 #define PROF_ON(x) false
 #define PROF_ACC(var)
@@ -262,6 +266,10 @@ __global__ void __launch_bounds__(GemmCfg<MPAD, BITS>::THREADS, 1)
 marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
                    const __grid_constant__ CUtensorMap tmap_s, const GemmArgs args) {
   using Cfg = GemmCfg<MPAD, BITS>;
+  // element type of the dequantised weight operand in TMEM: the activation dtype.  (kind::f16 encodes the A and B
+  // formats separately, but fp16 weights x bf16 activations traps with an illegal-instruction error on sm_100a --
+  // tried, B200 -- so bf16 pays the more expensive bf16 expansion.)
+  using WT = T;
   constexpr int NW = Cfg::NW, NA = Cfg::NA, NOWN = Cfg::NOWN, NBUF = Cfg::NBUF;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -425,7 +433,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     // (one half stage = 128 k = one quantisation group at g128: the epilogue warps scale and sum the accumulators
     // in registers, so the issuer knows nothing about tiles)
     const int o = warp - kIssuerWarp0, h = o & 1;
-    constexpr uint32_t idesc = make_idesc(1 /*F32*/, Pack2<T>::FMT, Pack2<T>::FMT, 128, MPAD);
+    constexpr uint32_t idesc = make_idesc(1 /*F32*/, Pack2<WT>::FMT, Pack2<T>::FMT, 128, MPAD);
     const uint32_t a_tmem0 = tmem_base + 64 * o;
     long long p_mark = PROF_ON(args.prof) ? clock64() : 0, p_wacc = 0, p_wfull = 0, p_wafull = 0, p_issue = 0;
     int jc = 0;
@@ -450,7 +458,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
 #pragma unroll
           for (int rr = 0; rr < 4; ++rr) {
             const int R = h * kSlabs + sub * 4 + rr;   // k16 slab within the stage
-            mma_f16_ts(d_tmem, a_tmem0 + sub * 32 + rr * 8,
+            if (!EXP_IS(2)) mma_f16_ts(d_tmem, a_tmem0 + sub * 32 + rr * 8,
                        make_kmajor_sw128_desc(b_smem + (R >> 2) * Cfg::A_BOX_BYTES + (R & 3) * 32), idesc,
                        (sub == 0 && rr == 0) ? 0u : 1u);
           }
@@ -520,40 +528,67 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       if (GM == kGroupSmall) mbar_wait(actfull_bar(sa), (it / NA) & 1);   // the staged scale rows ride with the activations
       PROF_ACC(p_lds);
       if (qd == 0) TRACE(4 + o, jc, 1);
+      // one n16-tile (jj) of one 64-k sub-slot: 4 slabs x 4 registers in tcgen05.st order
+      auto deq = [&](const int sub, const int jj, uint32_t* ov) {
 #pragma unroll
-      for (int sub = 0; sub < 2; ++sub) {
-#pragma unroll
-        for (int jj = 0; jj < 2; ++jj) {
-          uint32_t ov[16];   // 4 slabs x 4 registers of the n16-tile jj
-#pragma unroll
-          for (int rr = 0; rr < 4; ++rr) {
-            const int r = sub * 4 + rr;
-            if (GM == kGroupSmall && (r & ((1 << lspg) - 1)) == 0) load_scales(r >> lspg);
-            uint32_t* o4 = &ov[4 * rr];
-            if (BITS == 4) dequant4<T>(w[r][jj], o4);
-            else dequant8<T>(w[r][2 * jj], w[r][2 * jj + 1], o4);
-            if (GM == kGroupSmall) {
-              o4[0] = Pack2<T>::mul(o4[0], s2[2 * jj]);
-              o4[1] = Pack2<T>::mul(o4[1], s2[2 * jj + 1]);
-              o4[2] = Pack2<T>::mul(o4[2], s2[2 * jj]);
-              o4[3] = Pack2<T>::mul(o4[3], s2[2 * jj + 1]);
-            }
+        for (int rr = 0; rr < 4; ++rr) {
+          const int r = sub * 4 + rr;
+          if (GM == kGroupSmall && (r & ((1 << lspg) - 1)) == 0) load_scales(r >> lspg);
+          uint32_t* o4 = &ov[4 * rr];
+          if (EXP_IS(1)) { o4[0] = o4[1] = o4[2] = o4[3] = w[r][jj]; }
+          else if (BITS == 4) dequant4<WT>(w[r][jj], o4);
+          else dequant8<WT>(w[r][2 * jj], w[r][2 * jj + 1], o4);
+          if (GM == kGroupSmall) {
+            o4[0] = Pack2<T>::mul(o4[0], s2[2 * jj]);
+            o4[1] = Pack2<T>::mul(o4[1], s2[2 * jj + 1]);
+            o4[2] = Pack2<T>::mul(o4[2], s2[2 * jj]);
+            o4[3] = Pack2<T>::mul(o4[3], s2[2 * jj + 1]);
           }
-          PROF_ACC(p_deq);
-          if (jj == 0) {
-            mbar_wait(aempty_bar(o, sub), (jc & 1) ^ 1);
-            PROF_ACC(p_waempty);
-            if (qd == 0) TRACE(4 + o, jc, 2 + 2 * sub);
-            tc_fence_after();
-          }
-          tmem_st_16x128b_x8(a_col + ((uint32_t)(16 * jj) << 16) + sub * 32, ov);
         }
+      };
+      auto slot_wait = [&](const int sub) {
+        mbar_wait(aempty_bar(o, sub), (jc & 1) ^ 1);
+        PROF_ACC(p_waempty);
+        if (qd == 0) TRACE(4 + o, jc, 2 + 2 * sub);
+        tc_fence_after();
+      };
+      auto slot_publish = [&](const int sub) {
         tc_wait_st();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(afull_bar(o, sub));
         PROF_ACC(p_st);
         if (qd == 0) TRACE(4 + o, jc, 3 + 2 * sub);
+      };
+      auto st = [&](const int sub, const int jj, const uint32_t* ov) {
+        if (!EXP_IS(4)) tmem_st_16x128b_x8(a_col + ((uint32_t)(16 * jj) << 16) + sub * 32, ov);
+      };
+      if constexpr (Cfg::DEFER_ST) {
+        // the first n16-tile of sub-slot 1 is expanded while sub-slot 0's TMEM stores are still in flight
+        uint32_t ova[16], ovb[16], ovc[16];
+        deq(0, 0, ova);
+        slot_wait(0);
+        st(0, 0, ova);
+        deq(0, 1, ovb);
+        st(0, 1, ovb);
+        deq(1, 0, ovc);
+        slot_publish(0);
+        slot_wait(1);
+        st(1, 0, ovc);
+        deq(1, 1, ova);
+        st(1, 1, ova);
+        slot_publish(1);
+      } else {
+#pragma unroll
+        for (int sub = 0; sub < 2; ++sub) {
+          uint32_t ova[16], ovb[16];
+          deq(sub, 0, ova);
+          slot_wait(sub);
+          st(sub, 0, ova);
+          deq(sub, 1, ovb);
+          st(sub, 1, ovb);
+          slot_publish(sub);
+        }
       }
       if (GM == kGroupSmall) {
         __syncwarp();
@@ -620,7 +655,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         for (int c0 = 0; c0 < ACCW; c0 += CH) {
           uint32_t t[CH];
 #pragma unroll
-          for (int c1 = 0; c1 < CH; c1 += 16) tmem_ld_32x32b_x16(src + c0 + c1, *reinterpret_cast<uint32_t(*)[16]>(&t[c1]));
+          for (int c1 = 0; c1 < CH; c1 += 16) if (!EXP_IS(3)) tmem_ld_32x32b_x16(src + c0 + c1, *reinterpret_cast<uint32_t(*)[16]>(&t[c1]));
           tc_wait_ld();
           if (c0 + CH == ACCW) {
             if (et < 32) TRACE(8, hu, 2);
@@ -816,6 +851,8 @@ int launch_gemm(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t s
   a.prof = nullptr;
   a.trace = nullptr;
   a.trace_cta = 0;
+  a.exp = 0;
+  if (getenv("B200_GEMM_EXP")) a.exp = atoi(getenv("B200_GEMM_EXP"));
 #ifdef B200_GEMM_PROF
   if (prof_on && getenv("B200_GEMM_TRACE")) {
     a.trace_cta = atoi(getenv("B200_GEMM_TRACE"));
