@@ -331,7 +331,14 @@ def run_b200(a):
     if rank == 0:
         print(json.dumps(out), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        # The decode graph holds captured NCCL all-reduces: tearing the communicator down while the graph execs are
+        # alive (destroy_process_group, or interpreter teardown in arbitrary order) blocks forever on B200 / NCCL 2.28.
+        # Ranks meet once more (rank 0 may still have been timing the GEMMs alone), then leave without the destructors.
+        dist.barrier()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 if __name__ == "__main__":
