@@ -37,6 +37,9 @@ def parse():
     p.add_argument("--quant", default="w4a16", choices=["w4a16", "w4a16_24", "fp8", "int8"])
     p.add_argument("--kv", default="auto", choices=["auto", "fp8", "fp8_e5m2"])
     p.add_argument("--layers", type=int, default=None, help="debug: truncate the model (makes the number INVALID)")
+    p.add_argument("--allreduce", default="auto", choices=["auto", "custom", "nccl"],
+                   help="N>1: row-parallel all-reduce through the one-shot NVLink kernel (custom), NCCL, or custom with "
+                        "NCCL as the loud fallback when peer memory cannot be mapped (auto)")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--sweep", action="store_true", help="also report tok/s at batch 1,2,4,8,16,32 (extra key)")
     p.add_argument("--profile-step", action="store_true",
@@ -241,11 +244,31 @@ def run_b200(a):
     model = decoder.SyntheticLlama(shape, quant=a.quant, dtype=dtype, device=dev, tp_size=world, tp_rank=rank,
                                    kv_cache_dtype=a.kv, kv_scale=1.0 if a.kv == "auto" else 0.0376,
                                    num_blocks=num_blocks, max_pos=max(a.ctx + 1, 512), layers=a.layers)
+    ar_kind = "none"
+    if world > 1:
+        ar_kind = "nccl"
+        if a.allreduce != "nccl":
+            try:
+                model.enable_custom_all_reduce()
+                ar_kind = "one-shot NVLink peer-memory kernel (csrc/all_reduce.cu), NCCL for logits all-gather"
+            except Exception as e:  # peer memory not mappable on this box
+                if a.allreduce == "custom":
+                    raise
+                sys.stderr.write("[bench] rank %d: custom all-reduce unavailable (%s); using NCCL\n" % (rank, e))
+            # all ranks must agree, otherwise the collectives would not match
+            ok = torch.tensor([1 if model.custom_ar is not None else 0], device=dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if int(ok) == 0:
+                model.custom_ar = None
+                ar_kind = "nccl"
     eng = decoder.DecodeEngine(model, a.batch, a.ctx)
     hi = eng.host_inputs(a.ctx, seed=1)
     eng.load_inputs(hi)
     torch.cuda.synchronize()
     launches, per_op = count_launches(lambda: eng._device_step(a.ctx))
+    if model.custom_ar is not None:   # one-shot all-reduce kernel after every row-parallel GEMM (o, down)
+        per_op["custom_all_reduce"] = 2 * model.nlayers
+        launches += 2 * model.nlayers
     eng.prepare(a.ctx)
 
     def barrier():
@@ -293,6 +316,7 @@ def run_b200(a):
            "scaling": "strong", "vs_baseline": None, "dtype": "bf16" if dtype == torch.bfloat16 else "f16",
            "data": "synthetic",
            "config": {"workload": workload_name(a), "parallelism": "tp%d" % world, "layers": model.nlayers,
+                      "allreduce": ar_kind,
                       "l2": "inputs larger than L2: %.2f GB of packed weights + lm_head and %.2f GB of KV are streamed "
                             "every step (L2 = 126 MB), no flush needed" %
                             ((model.linear_weight_bytes() + model.lm_head.weight_bytes()) / 1e9,

@@ -148,6 +148,24 @@ int b200_rotary_embedding(const int64_t* positions, void* query, void* key, int 
                           int num_heads, int num_kv_heads, int64_t query_stride, int64_t key_stride,
                           int dtype, void* stream);
 
+/* ---- one-shot all-reduce over NVLink peer memory -----------------
+ * Replaces csrc/custom_all_reduce.cu (init_custom_ar / all_reduce_reg / dispose, torch_bindings.cpp:262-293)
+ * for the row-parallel GEMM outputs of TP decode.  Every rank allocates one region with b200_ar_alloc
+ * (cudaMalloc + IPC handle, zero-filled), exchanges the 64-byte handles out of band (torch.distributed),
+ * maps the peers' regions with b200_ar_open and builds a context with b200_ar_init(region_ptrs[world],
+ * own region at index `rank`).  b200_ar_all_reduce sums `numel` elements of `in` over the ranks into `out`
+ * (may alias `in`), fp32 accumulation in rank order (bit-identical on every rank); asynchronous on
+ * `stream`, CUDA-graph capturable; B200_ENOTSUP when numel*sizeof > max_bytes (caller falls back to NCCL,
+ * like should_custom_ar, custom_all_reduce.cu:32-50).  Every rank must issue the same sequence of calls. */
+int b200_ar_region_bytes(int world, int64_t max_bytes, int64_t* bytes_out);
+int b200_ar_alloc(int64_t bytes, void** ptr_out, void* handle_out64);
+int b200_ar_open(const void* handle64, void** ptr_out);
+int b200_ar_close(void* ptr);
+int b200_ar_free(void* ptr);
+int b200_ar_init(int rank, int world, void* const* region_ptrs, int64_t max_bytes, int64_t* ctx_out);
+int b200_ar_all_reduce(int64_t ctx, const void* in, void* out, int64_t numel, int dtype, void* stream);
+int b200_ar_dispose(int64_t ctx);
+
 #ifdef __cplusplus
 }
 #endif

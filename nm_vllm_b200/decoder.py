@@ -119,6 +119,7 @@ class SyntheticLlama:
         self.tp, self.rank = tp_size, tp_rank
         self.kv_cache_dtype, self.kv_scale, self.block_size, self.num_blocks = kv_cache_dtype, kv_scale, block_size, num_blocks
         self.group = group  # torch.distributed process group (None -> default) when tp > 1
+        self.custom_ar = None  # CustomAllreduce once enable_custom_all_reduce() has been called
         s = shape
         self.nlayers = layers if layers is not None else s.layers
         assert s.heads % tp_size == 0
@@ -174,8 +175,19 @@ class SyntheticLlama:
         es = self.kv[0][0].element_size()
         return int(sum(seq_lens)) * self.Hkv * self.shape.head_dim * 2 * es * self.nlayers
 
+    def enable_custom_all_reduce(self, max_size=8192 * 1024):
+        """Route the row-parallel all-reduces through the one-shot NVLink kernel (csrc/all_reduce.cu); tensors it does
+        not take (too large / unaligned) still go to NCCL, like tensor_model_parallel_all_reduce in the reference
+        (parallel_state.py:273-293)."""
+        from .custom_all_reduce import CustomAllreduce
+        if self.tp > 1 and self.custom_ar is None:
+            self.custom_ar = CustomAllreduce(self.group, torch.device(self.device), max_size)
+        return self.custom_ar
+
     def _all_reduce(self, t):
         if self.tp > 1:
+            if self.custom_ar is not None and self.custom_ar.should_custom_ar(t):
+                return self.custom_ar.all_reduce_(t)
             torch.distributed.all_reduce(t, group=self.group)
         return t
 

@@ -17,12 +17,15 @@ try:
     peak = json.load(open("MEASURED_PEAKS.json"))["hbm_gbs"]
 except Exception:
     pass
+HOT = len(sys.argv) > 4 and sys.argv[4] == "hot"
 res = {}
 if len(sys.argv) > 3:
     SHAPES = {k: v for k, v in SHAPES.items() if k in sys.argv[3].split(",")}
 for name, (K, N) in SHAPES.items():
     wbytes = K * N // 2
     ncopy = max(3, int(400e6 // wbytes) + 1)
+    if HOT:
+        ncopy = 1   # same weights every launch: L2-resident when they fit (what an L2 prefetch could give)
     g = torch.Generator(device=DEV).manual_seed(0)
     ws_ = [torch.randint(-2**31, 2**31 - 1, (K // 16, N * 2), generator=g, dtype=torch.int32, device=DEV) for _ in range(ncopy)]
     ss_ = [(torch.rand((K // 128, N), generator=g, device=DEV) * 0.01 + 0.005).to(dt) for _ in range(ncopy)]
@@ -34,7 +37,7 @@ for name, (K, N) in SHAPES.items():
             ops.gptq_marlin_gemm(a, ws_[i % ncopy], ss_[i % ncopy], e, e, wk, 4, M, N, K, True)
         torch.cuda.synchronize()
         # one CUDA graph = `reps` GEMMs over rotating weight buffers (removes host launch overhead from the timing)
-        reps = ncopy * 2
+        reps = max(ncopy * 2, 8)
         st = torch.cuda.Stream()
         with torch.cuda.stream(st):
             gr = torch.cuda.CUDAGraph()
@@ -58,4 +61,4 @@ for name, (K, N) in SHAPES.items():
         res[f"{name}_M{M}"] = dict(us=med * 1e3, gbs=gbs, frac=gbs / peak)
         print(f"{name:8s} M={M:3d} K={K} N={N}: {med*1e3:8.2f} us  {gbs:7.1f} GB/s  {gbs/peak*100:5.1f}% of measured {peak:.0f}", flush=True)
     del ws_, ss_
-json.dump(res, open("gpurun_out/gemm_perf.json", "w"), indent=1)
+json.dump(res, open("gpurun_out/gemm_perf%s.json" % ("_hot" if HOT else ""), "w"), indent=1)
