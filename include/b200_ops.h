@@ -148,6 +148,24 @@ int b200_rotary_embedding(const int64_t* positions, void* query, void* key, int 
                           int num_heads, int num_kv_heads, int64_t query_stride, int64_t key_stride,
                           int dtype, void* stream);
 
+/* ---- KV block maintenance: csrc/cache.h:8-32 ----------------------------
+ * copy_blocks (cache_kernels.cu:64-148): key_cache_ptrs / value_cache_ptrs are DEVICE arrays of
+ * num_layers device pointers, block_mapping a DEVICE int64 [num_pairs, 2] of (src, dst) block numbers;
+ * block_bytes = bytes of one block of one layer's key (== value) cache. */
+int b200_copy_blocks(const int64_t* key_cache_ptrs, const int64_t* value_cache_ptrs,
+                     const int64_t* block_mapping, int num_layers, int64_t num_pairs,
+                     int64_t block_bytes, void* stream);
+/* swap_blocks (cache_kernels.cu:24-62): block_mapping_host is a HOST int64 [num_pairs, 2];
+ * direction 0 = device->device, 1 = device->host, 2 = host->device. */
+int b200_swap_blocks(const void* src, void* dst, const int64_t* block_mapping_host, int64_t num_pairs,
+                     int64_t block_bytes, int direction, void* stream);
+/* reshape_and_cache_flash (cache_kernels.cu:207-236, 280-314): caches [NB, BS, H, D], kv dtype auto only. */
+int b200_reshape_and_cache_flash(const void* key, const void* value, void* k_cache, void* v_cache,
+                                 const int64_t* slot_mapping, int64_t num_tokens, int num_heads,
+                                 int head_size, int block_size, int64_t block_stride,
+                                 int64_t key_stride, int64_t value_stride, int dtype, int kv_dtype,
+                                 void* stream);
+
 /* ---- one-shot all-reduce over NVLink peer memory -----------------
  * Replaces csrc/custom_all_reduce.cu (init_custom_ar / all_reduce_reg / dispose, torch_bindings.cpp:262-293)
  * for the row-parallel GEMM outputs of TP decode.  Every rank allocates one region with b200_ar_alloc

@@ -137,6 +137,19 @@ def reshape_and_cache(key: torch.Tensor, value: torch.Tensor, key_cache: torch.T
     _cache_ops().reshape_and_cache(key, value, key_cache, value_cache, slot_mapping, kv_cache_dtype, kv_scale)
 
 
+def reshape_and_cache_flash(key: torch.Tensor, value: torch.Tensor, key_cache: torch.Tensor, value_cache: torch.Tensor,
+                            slot_mapping: torch.Tensor, kv_cache_dtype: str) -> None:
+    _cache_ops().reshape_and_cache_flash(key, value, key_cache, value_cache, slot_mapping, kv_cache_dtype)
+
+
+def copy_blocks(key_caches, value_caches, block_mapping: torch.Tensor) -> None:
+    _cache_ops().copy_blocks(key_caches, value_caches, block_mapping)
+
+
+def swap_blocks(src: torch.Tensor, dst: torch.Tensor, block_mapping: torch.Tensor) -> None:
+    _cache_ops().swap_blocks(src, dst, block_mapping)
+
+
 def convert_fp8(output: torch.Tensor, input: torch.Tensor, scale: float = 1.0, kv_dtype: str = "fp8") -> None:
     _cache_ops().convert_fp8(output, input, scale, kv_dtype)
 
@@ -155,6 +168,7 @@ _HOT_PATH_OPS = [
     "paged_attention_v1", "paged_attention_v2", "silu_and_mul", "rotary_embedding", "rms_norm", "fused_add_rms_norm",
     "marlin_gemm", "gptq_marlin_24_gemm", "cutlass_scaled_mm_supports_fp8", "cutlass_scaled_mm", "gptq_marlin_repack",
     "gptq_marlin_gemm", "scaled_fp8_quant", "scaled_int8_quant", "reshape_and_cache", "convert_fp8",
+    "reshape_and_cache_flash", "copy_blocks", "swap_blocks",
     "get_device_attribute", "get_max_shared_memory_per_block_device_attribute",
 ]
 

@@ -32,14 +32,14 @@ constexpr size_t kArLLMaxBytes = 1u << 20;   // payloads up to 1 MiB take the fl
 
 struct ArLayout {
   // region = [flags: 2 x W x kArMaxBlocks u32][call counter u32, finished-CTA ticket u32][pad to 4096]
-  //          [LL area: 2 x W x ll_slot][data: 2 x W x slot_bytes]
+  //          [LL area: 2 parities x 2 phases x W x ll_slot][data: 2 x W x slot_bytes]
   static __host__ __device__ size_t flags_bytes(int world) { return (size_t)2 * world * kArMaxBlocks * 4; }
   static __host__ __device__ size_t ll_offset(int world) { return (flags_bytes(world) + 64 + 4095) / 4096 * 4096; }
   static __host__ __device__ size_t ll_slot(size_t slot_bytes) {
     return 2 * (slot_bytes < kArLLMaxBytes ? slot_bytes : kArLLMaxBytes);   // 8 payload bytes per 16-byte store
   }
   static __host__ __device__ size_t data_offset(int world, size_t slot_bytes) {
-    return ll_offset(world) + (size_t)2 * world * ll_slot(slot_bytes);
+    return ll_offset(world) + (size_t)2 * 2 * world * ll_slot(slot_bytes);   // [parity][phase][rank]
   }
   static __host__ __device__ size_t region_bytes(int world, size_t slot_bytes) {
     return data_offset(world, slot_bytes) + (size_t)2 * world * slot_bytes;
@@ -55,6 +55,7 @@ struct ArCtx {
   size_t slot_bytes = 0;
   ArPtrs ptrs;
   bool live = false;
+  size_t two_shot_bytes = 256 * 1024;   // W > 2: payload x (W-1) above this goes two-shot (B200_AR_TWO_SHOT_BYTES)
   bool no_ll = false;   // B200_AR_NO_LL=1: always the fence + flag kernel (bring-up / comparison)
 };
 
@@ -209,7 +210,7 @@ ar_ll_kernel(const ArPtrs p, const int rank, const size_t slot_bytes, const uint
   const uint32_t epoch = ctr[0] + 1;
   const uint32_t par = epoch & 1u;
   const size_t ll_slot = ArLayout::ll_slot(slot_bytes);
-  const size_t area = ArLayout::ll_offset(W) + (size_t)par * W * ll_slot;
+  const size_t area = ArLayout::ll_offset(W) + (size_t)par * 2 * W * ll_slot;
   const size_t my_off = area + (size_t)rank * ll_slot;
   const int stride = gridDim.x * kArThreads;
   for (int v = b * kArThreads + t; v < nvec; v += stride) {
@@ -245,14 +246,99 @@ ar_ll_kernel(const ArPtrs p, const int rank, const size_t slot_bytes, const uint
   ar_finish_call(ctr, epoch);
 }
 
+// ---- two-shot LL variant (W > 2, larger payloads): reduce-scatter + all-gather inside one kernel ----------------------
+// One-shot moves (W-1) x payload per rank; here rank j owns the j-th 1/W of the vectors: everyone pushes its copy of
+// chunk j to rank j (phase area 0), rank j sums the W copies in rank order and pushes the result to everyone (phase
+// area 1).  2 x (W-1)/W x payload on the wire per rank and two NVLink traversals; results are still bit-identical on
+// all ranks (one rank computes each element).
+__device__ __forceinline__ uint4 poll_ll(const uint8_t* src, uint32_t epoch) {
+  uint4 lo, hi;
+  do {
+    lo = ld_ll(src);
+    hi = ld_ll(src + 16);
+  } while (lo.y != epoch || lo.w != epoch || hi.y != epoch || hi.w != epoch);
+  return make_uint4(lo.x, lo.z, hi.x, hi.z);
+}
+
+template <typename T, int W>
+__global__ void __launch_bounds__(kArThreads)
+ar_ll2_kernel(const ArPtrs p, const int rank, const size_t slot_bytes, const uint4* in, uint4* out, const int nvec) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int b = blockIdx.x, t = threadIdx.x;
+  uint8_t* self = nullptr;
+#pragma unroll
+  for (int q = 0; q < W; ++q)
+    if (q == rank) self = p.region[q];
+  volatile uint32_t* ctr = reinterpret_cast<volatile uint32_t*>(self + ArLayout::flags_bytes(W));
+  const uint32_t epoch = ctr[0] + 1;
+  const uint32_t par = epoch & 1u;
+  const size_t ll_slot = ArLayout::ll_slot(slot_bytes);
+  const size_t area1 = ArLayout::ll_offset(W) + (size_t)par * 2 * W * ll_slot;
+  const size_t area2 = area1 + (size_t)W * ll_slot;
+  const int c = (nvec + W - 1) / W;   // vectors per owner
+  const int stride = gridDim.x * kArThreads;
+  // phase 1: my copy of chunk q -> rank q
+  for (int i = b * kArThreads + t; i < c; i += stride) {
+#pragma unroll
+    for (int q = 0; q < W; ++q) {
+      const int v = q * c + i;
+      if (q != rank && v < nvec) {
+        const uint4 x = in[v];
+        uint8_t* d = p.region[q] + area1 + (size_t)rank * ll_slot + (size_t)i * 32;
+        st_ll(d, x.x, x.y, epoch);
+        st_ll(d + 16, x.z, x.w, epoch);
+      }
+    }
+  }
+  // phase 2: reduce my chunk in rank order, publish the result
+  for (int i = b * kArThreads + t; i < c; i += stride) {
+    const int v = rank * c + i;
+    if (v < nvec) {
+      const uint4 x = in[v];
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int q = 0; q < W; ++q) {
+        uint4 y = x;
+        if (q != rank) y = poll_ll(self + area1 + (size_t)q * ll_slot + (size_t)i * 32, epoch);
+        ArVec<T>::add(acc, y);
+      }
+      const uint4 r = ArVec<T>::pack(acc);
+      out[v] = r;
+#pragma unroll
+      for (int q = 0; q < W; ++q) {
+        if (q != rank) {
+          uint8_t* d = p.region[q] + area2 + (size_t)rank * ll_slot + (size_t)i * 32;
+          st_ll(d, r.x, r.y, epoch);
+          st_ll(d + 16, r.z, r.w, epoch);
+        }
+      }
+    }
+  }
+  // phase 3: collect the other owners' results
+  for (int i = b * kArThreads + t; i < c; i += stride) {
+#pragma unroll
+    for (int q = 0; q < W; ++q) {
+      const int v = q * c + i;
+      if (q != rank && v < nvec) out[v] = poll_ll(self + area2 + (size_t)q * ll_slot + (size_t)i * 32, epoch);
+    }
+  }
+  ar_finish_call(ctr, epoch);
+}
+
 template <typename T>
 static cudaError_t ar_launch(const ArCtx& c, const void* in, void* out, int nvec, cudaStream_t st) {
-  int grid = (nvec + kArThreads - 1) / kArThreads;
+  const bool ll = (size_t)nvec * 16 <= kArLLMaxBytes && !c.no_ll;
+  const bool two_shot = ll && c.world > 2 && (size_t)nvec * 16 * (c.world - 1) > c.two_shot_bytes;
+  const int work = two_shot ? (nvec + c.world - 1) / c.world : nvec;   // vectors per thread-grid pass
+  int grid = (work + kArThreads - 1) / kArThreads;
   if (grid > kArMaxBlocks) grid = kArMaxBlocks;
   if (grid < 1) grid = 1;
-  const bool ll = (size_t)nvec * 16 <= kArLLMaxBytes && !c.no_ll;
 #define AR_CASE(W)                                                                                              \
   case W:                                                                                                       \
+    if (two_shot)                                                                                                \
+      return launch_pdl(ar_ll2_kernel<T, W>, dim3(grid), dim3(kArThreads), 0, st, c.ptrs, c.rank, c.slot_bytes,  \
+                        (const uint4*)in, (uint4*)out, nvec);                                                   \
     return ll ? launch_pdl(ar_ll_kernel<T, W>, dim3(grid), dim3(kArThreads), 0, st, c.ptrs, c.rank, c.slot_bytes, \
                            (const uint4*)in, (uint4*)out, nvec)                                                 \
               : launch_pdl(ar_oneshot_kernel<T, W>, dim3(grid), dim3(kArThreads), 0, st, c.ptrs, c.rank,          \
@@ -329,6 +415,7 @@ int b200_ar_init(int rank, int world, void* const* region_ptrs, int64_t max_byte
     if (!c.ptrs.region[i]) return set_error(B200_EINVAL, "ar_init: region pointer %d is null", i);
   c.live = true;
   { const char* e = getenv("B200_AR_NO_LL"); c.no_ll = e && atoi(e) != 0; }
+  { const char* e = getenv("B200_AR_TWO_SHOT_BYTES"); if (e && atoll(e) >= 0) c.two_shot_bytes = (size_t)atoll(e); }
   std::lock_guard<std::mutex> g(g_ar_mu);
   g_ar.push_back(c);
   *ctx_out = (int64_t)g_ar.size();   // 1-based handle

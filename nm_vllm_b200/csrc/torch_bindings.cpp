@@ -105,6 +105,66 @@ void reshape_and_cache(torch::Tensor& key, torch::Tensor& value, torch::Tensor& 
            "reshape_and_cache");
 }
 
+// ---------------------------------------------------------------- block maintenance (cache_kernels.cu:24-148, 280-314)
+void swap_blocks(torch::Tensor& src, torch::Tensor& dst, const torch::Tensor& block_mapping) {
+  int direction;
+  if (src.device().is_cuda() && dst.device().is_cuda()) {
+    TORCH_CHECK(src.device().index() == dst.device().index(), "src and dst must be on the same GPU");
+    direction = 0;
+  } else if (src.device().is_cuda() && dst.device().is_cpu()) {
+    direction = 1;
+  } else if (src.device().is_cpu() && dst.device().is_cuda()) {
+    direction = 2;
+  } else {
+    TORCH_CHECK(false, "Invalid device combination");
+  }
+  TORCH_CHECK(block_mapping.device().is_cpu(), "block_mapping must be on CPU");
+  TORCH_CHECK(block_mapping.scalar_type() == at::ScalarType::Long && block_mapping.dim() == 2 && block_mapping.size(1) == 2,
+              "block_mapping must be int64 [num_pairs, 2]");
+  const torch::Tensor bm = block_mapping.contiguous();
+  const int64_t block_bytes = src.element_size() * src[0].numel();
+  const torch::Tensor& on_gpu = src.device().is_cuda() ? src : dst;
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(on_gpu));
+  raise_if(b200_swap_blocks(src.data_ptr(), dst.data_ptr(), bm.data_ptr<int64_t>(), bm.size(0), block_bytes, direction,
+                            cur_stream(on_gpu)),
+           "swap_blocks");
+}
+
+void copy_blocks(std::vector<torch::Tensor> const& key_caches, std::vector<torch::Tensor> const& value_caches,
+                 const torch::Tensor& block_mapping) {
+  const int num_layers = (int)key_caches.size();
+  TORCH_CHECK(num_layers == (int)value_caches.size());
+  if (num_layers == 0) return;
+  TORCH_CHECK(key_caches[0].device().is_cuda());
+  TORCH_CHECK(block_mapping.scalar_type() == at::ScalarType::Long, "block_mapping must be int64");
+  std::vector<int64_t> ptrs(2 * num_layers);
+  for (int i = 0; i < num_layers; ++i) {
+    ptrs[i] = reinterpret_cast<int64_t>(key_caches[i].data_ptr());
+    ptrs[num_layers + i] = reinterpret_cast<int64_t>(value_caches[i].data_ptr());
+  }
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(key_caches[0]));
+  torch::Tensor dptrs = torch::from_blob(ptrs.data(), {2 * num_layers}, torch::kInt64).to(key_caches[0].device());
+  const torch::Tensor bm = block_mapping.contiguous();
+  const int64_t block_bytes = key_caches[0].element_size() * key_caches[0][0].numel();
+  raise_if(b200_copy_blocks(dptrs.data_ptr<int64_t>(), dptrs.data_ptr<int64_t>() + num_layers, bm.data_ptr<int64_t>(),
+                            num_layers, bm.size(0), block_bytes, cur_stream(key_caches[0])),
+           "copy_blocks");
+}
+
+void reshape_and_cache_flash(torch::Tensor& key, torch::Tensor& value, torch::Tensor& k_cache, torch::Tensor& v_cache,
+                             torch::Tensor& slot_mapping, const std::string& kv_cache_dtype) {
+  TORCH_CHECK(kv_cache_dtype == "auto", "Unsupported data type of kv cache: ", kv_cache_dtype);
+  TORCH_CHECK(k_cache.stride(0) == v_cache.stride(0));
+  TORCH_CHECK(slot_mapping.scalar_type() == at::ScalarType::Long, "slot_mapping must be int64");
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(key));
+  raise_if(b200_reshape_and_cache_flash(key.data_ptr(), value.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
+                                        slot_mapping.data_ptr<int64_t>(), key.size(0), (int)key.size(1), (int)key.size(2),
+                                        (int)k_cache.size(1), k_cache.stride(0), key.stride(0), value.stride(0),
+                                        dtype_enum(key.scalar_type(), "reshape_and_cache_flash"), B200_KV_AUTO,
+                                        cur_stream(key)),
+           "reshape_and_cache_flash");
+}
+
 void convert_fp8(torch::Tensor& dst_cache, torch::Tensor& src_cache, const double kv_scale,
                  const std::string& kv_cache_dtype) {
   TORCH_CHECK(src_cache.device().is_cuda(), "src must be on a GPU");
@@ -488,6 +548,20 @@ TORCH_LIBRARY(_b200_C_cache_ops, cache_ops) {
       "                  str kv_cache_dtype,"
       "                  float kv_scale) -> ()");
   cache_ops.impl("reshape_and_cache", torch::kCUDA, &reshape_and_cache);
+  cache_ops.def("swap_blocks(Tensor src, Tensor! dst, Tensor block_mapping) -> ()");
+  cache_ops.impl("swap_blocks", torch::kCUDA, &swap_blocks);
+  cache_ops.impl("swap_blocks", torch::kCPU, &swap_blocks);   // host -> device swaps dispatch on the CPU source
+  cache_ops.def(
+      "copy_blocks(Tensor[]! key_caches, Tensor[]! value_caches, Tensor "
+      "block_mapping) -> ()");
+  cache_ops.impl("copy_blocks", torch::kCUDA, &copy_blocks);
+  cache_ops.def(
+      "reshape_and_cache_flash(Tensor key, Tensor value,"
+      "                        Tensor! key_cache,"
+      "                        Tensor! value_cache,"
+      "                        Tensor slot_mapping,"
+      "                        str kv_cache_dtype) -> ()");
+  cache_ops.impl("reshape_and_cache_flash", torch::kCUDA, &reshape_and_cache_flash);
   cache_ops.def(
       "convert_fp8(Tensor! dst_cache, Tensor src_cache, float scale, str "
       "kv_cache_dtype) -> ()");
