@@ -40,6 +40,7 @@ def parse():
     p.add_argument("--allreduce", default="auto", choices=["auto", "custom", "nccl"],
                    help="N>1: row-parallel all-reduce through the one-shot NVLink kernel (custom), NCCL, or custom with "
                         "NCCL as the loud fallback when peer memory cannot be mapped (auto)")
+    p.add_argument("--no-fuse", action="store_true", help="N>1: keep GEMM and all-reduce as two kernels")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--sweep", action="store_true", help="also report tok/s at batch 1,2,4,8,16,32 (extra key)")
     p.add_argument("--profile-step", action="store_true",
@@ -245,6 +246,7 @@ def run_b200(a):
                                    kv_cache_dtype=a.kv, kv_scale=1.0 if a.kv == "auto" else 0.0376,
                                    num_blocks=num_blocks, max_pos=max(a.ctx + 1, 512), layers=a.layers)
     ar_kind = "none"
+    model.fuse_gemm_all_reduce = not a.no_fuse
     if world > 1:
         ar_kind = "nccl"
         if a.allreduce != "nccl":
@@ -265,10 +267,13 @@ def run_b200(a):
     hi = eng.host_inputs(a.ctx, seed=1)
     eng.load_inputs(hi)
     torch.cuda.synchronize()
+    model.n_custom_ar_calls = 0
     launches, per_op = count_launches(lambda: eng._device_step(a.ctx))
-    if model.custom_ar is not None:   # one-shot all-reduce kernel after every row-parallel GEMM (o, down)
-        per_op["custom_all_reduce"] = 2 * model.nlayers
-        launches += 2 * model.nlayers
+    if model.custom_ar is not None:   # stand-alone all-reduce kernels (0 when every row-parallel GEMM fused its own)
+        per_op["custom_all_reduce"] = model.n_custom_ar_calls
+        launches += model.n_custom_ar_calls
+        if model.n_custom_ar_calls == 0:
+            ar_kind = "fused into the row-parallel W4A16 GEMM epilogue (LL exchange over NVLink peer memory)"
     eng.prepare(a.ctx)
 
     def barrier():

@@ -17,6 +17,7 @@
 //     they publish after their own call n has completed in stream order).
 //   * programmatic dependent launch like every other kernel of the step.
 #include "common.cuh"
+#include "ar_fuse.cuh"
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include <mutex>
@@ -24,11 +25,11 @@
 
 namespace b200 {
 
-constexpr int kArMaxWorld = 8;
 constexpr int kArMaxBlocks = 512;
 constexpr int kArThreads = 256;
 
-constexpr size_t kArLLMaxBytes = 1u << 20;   // payloads up to 1 MiB take the flag-in-data (LL) kernel
+constexpr size_t kArLLMaxBytes = 1u << 20;   // payloads up to 1 MiB take the flag-in-data (LL) kernels
+constexpr size_t kArLLSlotPayload = 2u << 20;   // LL slot capacity (payload bytes): room for the GEMM-fused exchange layout
 
 struct ArLayout {
   // region = [flags: 2 x W x kArMaxBlocks u32][call counter u32, finished-CTA ticket u32][pad to 4096]
@@ -36,7 +37,7 @@ struct ArLayout {
   static __host__ __device__ size_t flags_bytes(int world) { return (size_t)2 * world * kArMaxBlocks * 4; }
   static __host__ __device__ size_t ll_offset(int world) { return (flags_bytes(world) + 64 + 4095) / 4096 * 4096; }
   static __host__ __device__ size_t ll_slot(size_t slot_bytes) {
-    return 2 * (slot_bytes < kArLLMaxBytes ? slot_bytes : kArLLMaxBytes);   // 8 payload bytes per 16-byte store
+    return 2 * (slot_bytes < kArLLSlotPayload ? slot_bytes : kArLLSlotPayload);   // 8 payload bytes per 16-byte store
   }
   static __host__ __device__ size_t data_offset(int world, size_t slot_bytes) {
     return ll_offset(world) + (size_t)2 * 2 * world * ll_slot(slot_bytes);   // [parity][phase][rank]
@@ -56,6 +57,7 @@ struct ArCtx {
   ArPtrs ptrs;
   bool live = false;
   size_t two_shot_bytes = 256 * 1024;   // W > 2: payload x (W-1) above this goes two-shot (B200_AR_TWO_SHOT_BYTES)
+  size_t fuse_max_bytes = 2u << 20;     // GEMM-fused one-shot exchange: payload x (W-1) limit (B200_AR_FUSE_MAX_BYTES)
   bool no_ll = false;   // B200_AR_NO_LL=1: always the fence + flag kernel (bring-up / comparison)
 };
 
@@ -115,19 +117,9 @@ template <> struct ArVec<float> {
   static constexpr int N = 4;
 };
 
-// the last CTA of a call to get here bumps the call counter: the next call (which cannot pass griddepcontrol.wait /
-// stream order before this kernel has completed) reads epoch + 1.  ctr[0] = epoch of the last finished call,
-// ctr[1] = finished-CTA ticket.
 __device__ __forceinline__ void ar_finish_call(volatile uint32_t* ctr, uint32_t epoch) {
   __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence();
-    const uint32_t ticket = atomicAdd(const_cast<uint32_t*>(ctr) + 1, 1u);
-    if (ticket == gridDim.x - 1) {
-      ctr[1] = 0;
-      ctr[0] = epoch;
-    }
-  }
+  if (threadIdx.x == 0) ar_ticket(ctr, epoch);
 }
 
 // in/out: nvec 16-byte vectors (out may alias in).  grid <= kArMaxBlocks; CTA b owns vectors b*T + t + i*grid*T.
@@ -187,15 +179,6 @@ ar_oneshot_kernel(const ArPtrs p, const int rank, const size_t slot_bytes, const
 // Every 16-byte store carries 8 payload bytes and the call epoch twice: {d0, epoch, d1, epoch}.  The receiver polls the
 // data itself until both epochs match (only 8-byte store atomicity is assumed), so there is no fence and no separate
 // flag round trip: the latency of a call is ONE NVLink traversal.  A rank's own contribution stays in registers.
-__device__ __forceinline__ void st_ll(uint8_t* p, uint32_t d0, uint32_t d1, uint32_t e) {
-  asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(d0), "r"(e), "r"(d1), "r"(e) : "memory");
-}
-__device__ __forceinline__ uint4 ld_ll(const uint8_t* p) {
-  uint4 v;
-  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
-  return v;
-}
-
 template <typename T, int W>
 __global__ void __launch_bounds__(kArThreads)
 ar_ll_kernel(const ArPtrs p, const int rank, const size_t slot_bytes, const uint4* in, uint4* out, const int nvec) {
@@ -350,6 +333,32 @@ static cudaError_t ar_launch(const ArCtx& c, const void* in, void* out, int nvec
 #undef AR_CASE
 }
 
+
+static thread_local long long g_pending_ctx = 0, g_pending_m = 0, g_pending_n = 0;
+
+// rows of 16-byte LL cells per output channel the fused GEMM epilogue may use (marlin_gemm_kernel.cuh: MPAD/4 groups,
+// plus up to one partly filled group per cluster rank)
+static size_t fused_cells(long long m) {
+  const long long mpad = m <= 16 ? 16 : m <= 32 ? 32 : m <= 64 ? 64 : 128;
+  return (size_t)(mpad / 4 + 8);
+}
+
+bool ar_take_pending(ArFuse* out, long long* m_out, long long* n_out) {
+  if (g_pending_ctx == 0) return false;
+  std::lock_guard<std::mutex> g(g_ar_mu);
+  const ArCtx& c = g_ar[g_pending_ctx - 1];
+  for (int i = 0; i < kArMaxWorld; ++i) out->region[i] = c.ptrs.region[i];
+  out->rank = c.rank;
+  out->world = c.world;
+  out->ll_off = ArLayout::ll_offset(c.world);
+  out->ll_slot = ArLayout::ll_slot(c.slot_bytes);
+  out->ctr_off = ArLayout::flags_bytes(c.world);
+  *m_out = g_pending_m;
+  *n_out = g_pending_n;
+  g_pending_ctx = 0;
+  return true;
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -415,10 +424,28 @@ int b200_ar_init(int rank, int world, void* const* region_ptrs, int64_t max_byte
     if (!c.ptrs.region[i]) return set_error(B200_EINVAL, "ar_init: region pointer %d is null", i);
   c.live = true;
   { const char* e = getenv("B200_AR_NO_LL"); c.no_ll = e && atoi(e) != 0; }
+  { const char* e = getenv("B200_AR_FUSE_MAX_BYTES"); if (e && atoll(e) >= 0) c.fuse_max_bytes = (size_t)atoll(e); }
   { const char* e = getenv("B200_AR_TWO_SHOT_BYTES"); if (e && atoll(e) >= 0) c.two_shot_bytes = (size_t)atoll(e); }
   std::lock_guard<std::mutex> g(g_ar_mu);
   g_ar.push_back(c);
   *ctx_out = (int64_t)g_ar.size();   // 1-based handle
+  return B200_OK;
+}
+
+/* The NEXT b200_gptq_marlin_gemm issued by this host thread ([m, n] output) exchanges its output tiles with the peers
+ * inside its epilogue and writes the all-reduced result: one kernel instead of GEMM + all-reduce.  B200_ENOTSUP when
+ * the shape does not fit the exchange area (the caller then runs GEMM and b200_ar_all_reduce separately). */
+int b200_ar_fuse_next_gemm(int64_t ctx, int64_t m, int64_t n) {
+  std::lock_guard<std::mutex> g(g_ar_mu);
+  if (ctx < 1 || ctx > (int64_t)g_ar.size() || !g_ar[ctx - 1].live) return set_error(B200_EINVAL, "ar_fuse_next_gemm: bad handle");
+  const ArCtx& c = g_ar[ctx - 1];
+  const size_t npad = (size_t)((n + 127) / 128) * 128;
+  if (m < 1 || m > 128 || fused_cells(m) * npad * 16 > ArLayout::ll_slot(c.slot_bytes))
+    return set_error(B200_ENOTSUP, "ar_fuse_next_gemm: [%lld, %lld] does not fit the exchange area", (long long)m, (long long)n);
+  // one-shot exchange: every rank sends its whole output to every peer; above this the two-shot kernel wins
+  if ((size_t)m * n * 2 * (c.world - 1) > c.fuse_max_bytes)
+    return set_error(B200_ENOTSUP, "ar_fuse_next_gemm: payload too large for the one-shot exchange at world %d", c.world);
+  g_pending_ctx = ctx; g_pending_m = m; g_pending_n = n;
   return B200_OK;
 }
 

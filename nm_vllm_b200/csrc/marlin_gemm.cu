@@ -137,6 +137,17 @@ extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_
   ga.groups_per_stage = num_groups > 1 ? kStageK / gs : 0;
   ga.prof = nullptr; ga.trace = nullptr; ga.trace_cta = 0; ga.exp = 0;
   ga.cluster_s = 0;
+  ga.ar.world = 0;
+  {
+    long long fm = 0, fn = 0;
+    ArFuse f;
+    if (ar_take_pending(&f, &fm, &fn)) {   // b200_ar_fuse_next_gemm: all-reduce this GEMM's output in its epilogue
+      if (fm != size_m || fn != size_n)
+        return set_error(B200_EINVAL, "gptq_marlin_gemm: fused all-reduce was requested for [%lld, %lld], the GEMM is [%lld, %lld]",
+                         fm, fn, (long long)size_m, (long long)size_n);
+      ga.ar = f;
+    }
+  }
   int rc;
   if (dtype == B200_F16) rc = (num_bits == 4) ? dispatch_gemm_f16_4(ga, a, lda, st) : dispatch_gemm_f16_8(ga, a, lda, st);
   else rc = (num_bits == 4) ? dispatch_gemm_bf16_4(ga, a, lda, st) : dispatch_gemm_bf16_8(ga, a, lda, st);

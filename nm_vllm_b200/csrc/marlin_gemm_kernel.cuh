@@ -37,6 +37,7 @@
 #include "ptx.cuh"
 #include "tma_host.cuh"
 #include "streamk.cuh"
+#include "ar_fuse.cuh"
 #include <stdlib.h>
 #include <type_traits>
 
@@ -111,6 +112,7 @@ struct GemmArgs {
   long long* prof;             // bring-up cycle counters [grid][16] (B200_GEMM_PROF), nullptr in production
   long long* trace;            // bring-up event trace of CTA trace_cta [11 roles][64][8]
   int trace_cta;
+  ArFuse ar;                   // ar.world > 1: the epilogue all-reduces the output over the TP ranks (row-parallel layers)
   int exp;                     // bring-up ablations (B200_GEMM_EXP, prof builds only): 1 no dequant ALU, 2 no MMAs, 3 no epilogue reads, 4 no TMEM stores
 };
 
@@ -260,8 +262,58 @@ __device__ __forceinline__ int ld_acquire_gpu(const int* p) {
 #define PROF_ACC(var)
 #endif
 
+// ---- fused all-reduce in the epilogue (row-parallel layers under tensor parallelism) -----------------------------------
+// A thread that holds 4 final outputs of one channel rounds them to T (what the unfused GEMM would have stored), pushes
+// them as ONE LL cell {2 x T, epoch, 2 x T, epoch} into cell `idx` of its slot in every peer's region, later polls the
+// peers' cells of the same index in its own region and sums the W contributions in rank order in fp32: bit-identical on
+// every rank and identical to GEMM -> b200_ar_all_reduce.  Every rank runs the same schedule, so `idx` only has to be
+// unique per (channel, group of rows) within a launch.
+template <typename T>
+__device__ __forceinline__ uint32_t ar_pack2(float a, float b) {
+  const T x = from_f32<T>(a), y = from_f32<T>(b);
+  return (uint32_t)(*reinterpret_cast<const unsigned short*>(&x)) | ((uint32_t)(*reinterpret_cast<const unsigned short*>(&y)) << 16);
+}
+template <typename T>
+__device__ __forceinline__ float ar_unpack(uint32_t w, int hi) {
+  const unsigned short b = (unsigned short)(hi ? (w >> 16) : (w & 0xffffu));
+  return to_f32<T>(*reinterpret_cast<const T*>(&b));
+}
+template <typename T>
+__device__ __forceinline__ void ar_push4(const ArFuse& ar, uint32_t epoch, size_t idx, const float (&v)[4]) {
+  const uint32_t w0 = ar_pack2<T>(v[0], v[1]), w1 = ar_pack2<T>(v[2], v[3]);
+  const size_t off = ar.ll_off + ((size_t)(epoch & 1u) * 2 * ar.world + ar.rank) * ar.ll_slot + idx * 16;
+#pragma unroll
+  for (int q = 0; q < kArMaxWorld; ++q)
+    if (q < ar.world && q != ar.rank) st_ll(ar.region[q] + off, w0, w1, epoch);
+}
+template <typename T>
+__device__ __forceinline__ void ar_sum4(const ArFuse& ar, uint32_t epoch, size_t idx, float (&v)[4]) {
+  const uint32_t w0 = ar_pack2<T>(v[0], v[1]), w1 = ar_pack2<T>(v[2], v[3]);
+  uint8_t* self = nullptr;
+#pragma unroll
+  for (int q = 0; q < kArMaxWorld; ++q)
+    if (q == ar.rank) self = ar.region[q];
+  const uint8_t* base = self + ar.ll_off + (size_t)(epoch & 1u) * 2 * ar.world * ar.ll_slot + idx * 16;
+  float s[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int q = 0; q < kArMaxWorld; ++q) {
+    if (q < ar.world) {
+      uint32_t a0 = w0, a1 = w1;
+      if (q != ar.rank) {
+        uint4 x;
+        do { x = ld_ll(base + (size_t)q * ar.ll_slot); } while (x.y != epoch || x.w != epoch);
+        a0 = x.x; a1 = x.z;
+      }
+      s[0] += ar_unpack<T>(a0, 0); s[1] += ar_unpack<T>(a0, 1);
+      s[2] += ar_unpack<T>(a1, 0); s[3] += ar_unpack<T>(a1, 1);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) v[i] = s[i];
+}
+
 // ---- the kernel --------------------------------------------------------------------------------------------------
-template <typename T, int MPAD, int BITS, int GM>
+template <typename T, int MPAD, int BITS, int GM, bool FUSE>
 __global__ void __launch_bounds__(GemmCfg<MPAD, BITS>::THREADS, 1)
 marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
                    const __grid_constant__ CUtensorMap tmap_s, const GemmArgs args) {
@@ -615,6 +667,39 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     const int sc_pos = 64 * (row >> 6) + 8 * (row & 7) + ((row & 63) >> 3);
     const uint32_t acc_lane = tmem_base + ((uint32_t)(32 * qd) << 16) + Cfg::ACC_COL0;
     pdl_wait();   // C, the partial slots and the tile counters may still be in use by the previous kernel
+    constexpr bool fuse = FUSE;   // separate instantiation: the plain kernel carries none of the exchange code
+    uint32_t ar_epoch = 0;
+    if constexpr (FUSE) {
+      uint8_t* self = nullptr;
+#pragma unroll
+      for (int q = 0; q < kArMaxWorld; ++q)
+        if (q == args.ar.rank) self = args.ar.region[q];
+      ar_epoch = *reinterpret_cast<volatile uint32_t*>(self + args.ar.ctr_off) + 1;
+    }
+    const size_t ar_npad = (size_t)args.n_tiles * kTileN;
+    // stores this thread's ACCW final outputs (or, fused, exchanges them with the peers first): rows jb .. jb + ACCW - 1
+    auto store_rows = [&](float (&acc)[ACCW], float ch_scale, T* cdst, int n, bool n_ok, int m_valid) {
+      if (!n_ok) return;
+      if constexpr (FUSE) {
+#pragma unroll
+        for (int g = 0; g < ACCW / 4; ++g) {
+          const float v[4] = {acc[4 * g] * ch_scale, acc[4 * g + 1] * ch_scale, acc[4 * g + 2] * ch_scale, acc[4 * g + 3] * ch_scale};
+          ar_push4<T>(args.ar, ar_epoch, (size_t)(jb / 4 + g) * ar_npad + n, v);
+        }
+#pragma unroll
+        for (int g = 0; g < ACCW / 4; ++g) {
+          float v[4] = {acc[4 * g] * ch_scale, acc[4 * g + 1] * ch_scale, acc[4 * g + 2] * ch_scale, acc[4 * g + 3] * ch_scale};
+          ar_sum4<T>(args.ar, ar_epoch, (size_t)(jb / 4 + g) * ar_npad + n, v);
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            if (jb + 4 * g + i < m_valid) cdst[(size_t)(jb + 4 * g + i) * args.N] = from_f32<T>(v[i]);
+        }
+        return;
+      }
+#pragma unroll
+      for (int j = 0; j < ACCW; ++j)
+        if (jb + j < m_valid) cdst[(size_t)(jb + j) * args.N] = from_f32<T>(acc[j] * ch_scale);
+    };
     long long p_mark = PROF_ON(args.prof) ? clock64() : 0, p_wacc = 0, p_epi = 0, p_red = 0;
     for (int u = u_begin; u < u_end;) {
       const int tile = u / KS, ks0 = u - tile * KS;
@@ -674,11 +759,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         ch_scale = to_f32<T>(reinterpret_cast<const T*>(args.scales)[(n & ~31) + scale_single_pos(n & 31)]);
 
       if (full_k) {
-        if (n_ok) {
-#pragma unroll
-          for (int j = 0; j < ACCW; ++j)
-            if (jb + j < m_valid) cdst[(size_t)(jb + j) * args.N] = from_f32<T>(acc[j] * ch_scale);
-        }
+        store_rows(acc, ch_scale, cdst, n, n_ok, m_valid);
       } else if (owner) {
         // contributors are the CTAs after this one whose unit ranges intersect [tile*KS, (tile+1)*KS); for each of them
         // the tile is the FIRST segment of its range, so its partial has long been in its slot when this CTA (whose
@@ -697,11 +778,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
             if (jb + j < m_valid) acc[j] += __ldcg(src + (jb + j) * kTileN);
         }
         PROF_ACC(p_red);
-        if (n_ok) {
-#pragma unroll
-          for (int j = 0; j < ACCW; ++j)
-            if (jb + j < m_valid) cdst[(size_t)(jb + j) * args.N] = from_f32<T>(acc[j] * ch_scale);
-        }
+        store_rows(acc, ch_scale, cdst, n, n_ok, m_valid);
       } else if (clustered) {
         // partial of this CTA's K slice -> own shared memory (the activation ring is dead: every MMA of this CTA has
         // completed, or the accumulators above could not have been read), laid out [m][128 channels]
@@ -714,7 +791,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         cluster_wait();
         const uint32_t red_u32 = act_base + (uint32_t)row * 4u;
         // all remote loads of a group of rows are issued before the first add: DSMEM latency is paid once per group
-        for (int mb = c_rank + (et >> 7) * 4 * CS; mb < m_valid; mb += 4 * CS * Cfg::NEG) {
+        auto row_group = [&](int mb, float (&out4)[4]) {   // rows mb, mb + CS, mb + 2 CS, mb + 3 CS of this channel, summed over the cluster
           float pv[4][8];
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
@@ -725,11 +802,44 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
           }
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
-            const int m = mb + i * CS;
             float a2 = 0.f;
 #pragma unroll
             for (int c = 0; c < 8; ++c) a2 += pv[i][c];
-            if (n_ok && m < m_valid) cdst[(size_t)m * args.N] = from_f32<T>(a2 * ch_scale);
+            out4[i] = a2 * ch_scale;
+          }
+        };
+        if constexpr (FUSE) {
+          // push every row group first, then collect: one NVLink traversal for the whole tile, not one per group
+          constexpr int MAXIT = (MPAD / (8 * Cfg::NEG)) > 0 ? MPAD / (8 * Cfg::NEG) : 1;
+          const int G = (MPAD + 4 * CS - 1) / (4 * CS);
+          float keep[MAXIT][4];
+#pragma unroll
+          for (int it = 0; it < MAXIT; ++it) {
+            const int k = (et >> 7) + it * Cfg::NEG;
+            const int mb = c_rank + k * 4 * CS;
+            if (mb < m_valid) {
+              row_group(mb, keep[it]);
+              if (n_ok) ar_push4<T>(args.ar, ar_epoch, ((size_t)c_rank * G + k) * ar_npad + n, keep[it]);
+            }
+          }
+#pragma unroll
+          for (int it = 0; it < MAXIT; ++it) {
+            const int k = (et >> 7) + it * Cfg::NEG;
+            const int mb = c_rank + k * 4 * CS;
+            if (mb < m_valid && n_ok) {
+              ar_sum4<T>(args.ar, ar_epoch, ((size_t)c_rank * G + k) * ar_npad + n, keep[it]);
+#pragma unroll
+              for (int i = 0; i < 4; ++i)
+                if (mb + i * CS < m_valid) cdst[(size_t)(mb + i * CS) * args.N] = from_f32<T>(keep[it][i]);
+            }
+          }
+        } else {
+          for (int mb = c_rank + (et >> 7) * 4 * CS; mb < m_valid; mb += 4 * CS * Cfg::NEG) {
+            float r4[4];
+            row_group(mb, r4);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              if (n_ok && mb + i * CS < m_valid) cdst[(size_t)(mb + i * CS) * args.N] = from_f32<T>(r4[i]);
           }
         }
       } else {
@@ -759,13 +869,22 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
   }
   tc_fence_before();
   __syncthreads();
+  if (FUSE && threadIdx.x == 0) {
+    // every CTA is past its exchanges: the last one to get here closes the call (see ar_ticket)
+    uint8_t* self = nullptr;
+#pragma unroll
+    for (int q = 0; q < kArMaxWorld; ++q)
+      if (q == args.ar.rank) self = args.ar.region[q];
+    volatile uint32_t* ctr = reinterpret_cast<volatile uint32_t*>(self + args.ar.ctr_off);
+    ar_ticket(ctr, ctr[0] + 1);
+  }
   if (threadIdx.x == 0) { TRACE(10, 63, 7); }
   if (PROF_ON(args.prof) && threadIdx.x == 0) { args.prof[blockIdx.x * 16 + 11] = clock64() - k_t0; args.prof[blockIdx.x * 16 + 12] = n_units; }
   if (warp == kAllocWarp) tmem_dealloc<Cfg::TMEM_COLS>(*reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base)));
 }
 
 // ---- host side: one launch ---------------------------------------------------------------------------------------
-template <typename T, int MPAD, int BITS, int GM>
+template <typename T, int MPAD, int BITS, int GM, bool FUSE>
 int launch_gemm(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t st) {
   using Cfg = GemmCfg<MPAD, BITS>;
   GemmArgs a = a_in;
@@ -777,7 +896,7 @@ int launch_gemm(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t s
   // fewer tiles than SMs: split each tile's K range over a cluster (<= 8 CTAs) instead of stream-K with global fixups
   a.cluster_s = 0;
   static const int no_cluster = getenv("B200_GEMM_NO_CLUSTER") ? atoi(getenv("B200_GEMM_NO_CLUSTER")) : 0;
-  auto kern = marlin_gemm_kernel<T, MPAD, BITS, GM>;
+  auto kern = marlin_gemm_kernel<T, MPAD, BITS, GM, FUSE>;
   int dev = 0;
   cudaGetDevice(&dev);
   static bool attr_set[64] = {};
@@ -911,10 +1030,16 @@ int launch_gemm(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t s
 
 template <typename T, int BITS, int GM>
 int dispatch_mpad(const GemmArgs& a, const void* A, int64_t lda, cudaStream_t st) {
-  if (a.M <= 16) return launch_gemm<T, 16, BITS, GM>(a, A, lda, st);
-  if (a.M <= 32) return launch_gemm<T, 32, BITS, GM>(a, A, lda, st);
-  if (a.M <= 64) return launch_gemm<T, 64, BITS, GM>(a, A, lda, st);
-  return launch_gemm<T, 128, BITS, GM>(a, A, lda, st);
+  if (a.ar.world > 1) {   // row-parallel layer with the all-reduce fused into the epilogue (b200_ar_fuse_next_gemm)
+    if (a.M <= 16) return launch_gemm<T, 16, BITS, GM, true>(a, A, lda, st);
+    if (a.M <= 32) return launch_gemm<T, 32, BITS, GM, true>(a, A, lda, st);
+    if (a.M <= 64) return launch_gemm<T, 64, BITS, GM, true>(a, A, lda, st);
+    return launch_gemm<T, 128, BITS, GM, true>(a, A, lda, st);
+  }
+  if (a.M <= 16) return launch_gemm<T, 16, BITS, GM, false>(a, A, lda, st);
+  if (a.M <= 32) return launch_gemm<T, 32, BITS, GM, false>(a, A, lda, st);
+  if (a.M <= 64) return launch_gemm<T, 64, BITS, GM, false>(a, A, lda, st);
+  return launch_gemm<T, 128, BITS, GM, false>(a, A, lda, st);
 }
 
 // one translation unit per (T, BITS): marlin_gemm_inst_*.cu

@@ -90,6 +90,13 @@ class CustomAllreduce:
                                                   _DT[inp.dtype], ctypes.c_void_p(st)))
         return out
 
+    def fuse_next_gemm(self, m: int, n: int) -> bool:
+        """Ask the NEXT gptq_marlin_gemm issued by this thread ([m, n] output) to all-reduce its output inside its own
+        epilogue.  False when the shape does not qualify: the caller then runs GEMM + all_reduce as two kernels."""
+        if self.disabled:
+            return False
+        return capi.lib().b200_ar_fuse_next_gemm(ctypes.c_int64(self._ctx), ctypes.c_int64(m), ctypes.c_int64(n)) == 0
+
     def all_reduce_(self, inp: torch.Tensor) -> torch.Tensor:
         """In place (what the decode step uses: the GEMM output is overwritten by the sum)."""
         return self.all_reduce(inp, inp)

@@ -120,6 +120,8 @@ class SyntheticLlama:
         self.kv_cache_dtype, self.kv_scale, self.block_size, self.num_blocks = kv_cache_dtype, kv_scale, block_size, num_blocks
         self.group = group  # torch.distributed process group (None -> default) when tp > 1
         self.custom_ar = None  # CustomAllreduce once enable_custom_all_reduce() has been called
+        self.n_custom_ar_calls = 0  # stand-alone all-reduce kernel launches (bench.py counts them per step)
+        self.fuse_gemm_all_reduce = True  # row-parallel W4A16 GEMMs all-reduce in their epilogue when custom_ar is on
         s = shape
         self.nlayers = layers if layers is not None else s.layers
         assert s.heads % tp_size == 0
@@ -184,9 +186,19 @@ class SyntheticLlama:
             self.custom_ar = CustomAllreduce(self.group, torch.device(self.device), max_size)
         return self.custom_ar
 
+    def _row_parallel(self, lin, x):
+        """RowParallelLinear.forward (linear.py:779-803): local GEMM over this rank's K shard, then the sum over ranks.
+        With the custom all-reduce enabled the W4A16 GEMM exchanges its output tiles with the peers inside its own
+        epilogue (one kernel, csrc/marlin_gemm_kernel.cuh `FUSE`); otherwise GEMM followed by an all-reduce."""
+        if (self.tp > 1 and self.custom_ar is not None and self.fuse_gemm_all_reduce and lin.kind == "w4a16"
+                and self.custom_ar.fuse_next_gemm(x.shape[0], lin.N)):
+            return lin(x)
+        return self._all_reduce(lin(x))
+
     def _all_reduce(self, t):
         if self.tp > 1:
             if self.custom_ar is not None and self.custom_ar.should_custom_ar(t):
+                self.n_custom_ar_calls += 1
                 return self.custom_ar.all_reduce_(t)
             torch.distributed.all_reduce(t, group=self.group)
         return t
@@ -229,12 +241,12 @@ class SyntheticLlama:
             q, k, v = qkv.split([self.q_size, self.kv_size, self.kv_size], dim=-1)
             ops.rotary_embedding(positions, q, k, D, self.cos_sin, True)
             a = self._attention(li, q.view(-1, self.H, D), k.view(-1, self.Hkv, D), v.view(-1, self.Hkv, D), meta)
-            h = self._all_reduce(L["o"](a))
+            h = self._row_parallel(L["o"], a)
             ops.fused_add_rms_norm(h, residual, L["ln2"], s.eps)
             gu = L["gate_up"](h)
             act = torch.empty((gu.shape[0], gu.shape[1] // 2), dtype=gu.dtype, device=gu.device)
             ops.silu_and_mul(act, gu)
-            h = self._all_reduce(L["down"](act))
+            h = self._row_parallel(L["down"], act)
         ops.fused_add_rms_norm(h, residual, self.norm, s.eps)
         logits = self.lm_head(h)
         if self.tp > 1:  # vocab-parallel logits gathered once per step

@@ -102,10 +102,67 @@ for name, fn in (("custom", lambda t: ar.all_reduce_(t)), ("nccl", lambda t: dis
             e1.record(st)
             torch.cuda.synchronize()
         res["%s_%dx%d" % (name, *shape)] = e0.elapsed_time(e1) * 1e3 / 640
+
+# fused GEMM + all-reduce (marlin_gemm_kernel FUSE): must equal GEMM -> all_reduce bit for bit, eager and replayed
+from nm_vllm_b200 import _custom_ops as ops  # noqa: E402
+fused_res = {}
+e_i32 = torch.empty(0, dtype=torch.int32, device=dev)
+for dtype in (torch.bfloat16, torch.float16):
+    for (M, K, N) in ((1, 512, 4096), (16, 2048, 4096), (64, 7168, 4096), (64, 1792, 4096), (33, 4096, 8192),
+                      (128, 1024, 1024), (16, 1024, 12288), (5, 4096, 128)):
+        g = torch.Generator(device=dev).manual_seed(77 + rank)
+        w = torch.randint(-2**31, 2**31 - 1, (K // 16, N * 2), generator=g, dtype=torch.int32, device=dev)
+        sc = (torch.rand((K // 128, N), generator=g, device=dev) * 0.01 + 0.005).to(dtype)
+        x = torch.randn((M, K), generator=g, device=dev).to(dtype)
+        wk = torch.zeros((N // 64) * 16, dtype=torch.int32, device=dev)
+        ref = ar.all_reduce(ops.gptq_marlin_gemm(x, w, sc, e_i32, e_i32, wk, 4, M, N, K, True))
+        if not ar.fuse_next_gemm(M, N):
+            fused_res["%s_%dx%dx%d" % (str(dtype)[6:], M, K, N)] = "not fused"
+            continue
+        for rep in range(3):
+            if rep:
+                assert ar.fuse_next_gemm(M, N)
+            out = ops.gptq_marlin_gemm(x, w, sc, e_i32, e_i32, wk, 4, M, N, K, True)
+            if not torch.equal(out, ref):
+                fails.append(("fused", str(dtype), (M, K, N), rep, float((out.float() - ref.float()).abs().max())))
+                break
+        fused_res["%s_%dx%dx%d" % (str(dtype)[6:], M, K, N)] = "ok"
+# timing: graph of 32 x (GEMM + all-reduce) vs 32 fused GEMMs, down-proj shard shape of this world size
+Kd = max(128, (14336 // world) // 128 * 128)
+g = torch.Generator(device=dev).manual_seed(5 + rank)
+ws_ = [torch.randint(-2**31, 2**31 - 1, (Kd // 16, 4096 * 2), generator=g, dtype=torch.int32, device=dev) for _ in range(8)]
+sc = (torch.rand((Kd // 128, 4096), generator=g, device=dev) * 0.01 + 0.005).to(torch.bfloat16)
+wk = torch.zeros((4096 // 64) * 16, dtype=torch.int32, device=dev)
+for M in (1, 16, 64):
+    x = torch.randn((M, Kd), generator=g, device=dev).to(torch.bfloat16)
+    for name in ("gemm_then_ar", "fused"):
+        def one(i):
+            if name == "fused" and ar.fuse_next_gemm(M, 4096):
+                return ops.gptq_marlin_gemm(x, ws_[i % 8], sc, e_i32, e_i32, wk, 4, M, 4096, Kd, True)
+            return ar.all_reduce_(ops.gptq_marlin_gemm(x, ws_[i % 8], sc, e_i32, e_i32, wk, 4, M, 4096, Kd, True))
+        with torch.cuda.stream(st):
+            for i in range(3):
+                one(i)
+            torch.cuda.synchronize()
+            gg = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gg, stream=st):
+                for i in range(32):
+                    one(i)
+            for _ in range(3):
+                gg.replay()
+            dist.barrier()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(st)
+            for _ in range(10):
+                gg.replay()
+            e1.record(st)
+            torch.cuda.synchronize()
+        res["%s_M%d_K%d" % (name, M, Kd)] = e0.elapsed_time(e1) * 1e3 / 320
 nf = torch.tensor([len(fails)], device=dev)
 dist.all_reduce(nf)
 if rank == 0:
-    print(json.dumps({"world": world, "fails_total": int(nf), "fails_rank0": fails[:5], "us_per_call": res}), flush=True)
+    print(json.dumps({"world": world, "fails_total": int(nf), "fails_rank0": [str(f) for f in fails[:5]], "fused": fused_res, "us_per_call": res}), flush=True)
 dist.barrier()
 torch.cuda.synchronize()
 sys.stdout.flush()
