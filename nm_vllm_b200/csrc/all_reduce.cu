@@ -57,7 +57,8 @@ struct ArCtx {
   ArPtrs ptrs;
   bool live = false;
   size_t two_shot_bytes = 256 * 1024;   // W > 2: payload x (W-1) above this goes two-shot (B200_AR_TWO_SHOT_BYTES)
-  size_t fuse_max_bytes = 2u << 20;     // GEMM-fused one-shot exchange: payload x (W-1) limit (B200_AR_FUSE_MAX_BYTES)
+  size_t fuse_max_bytes = 2u << 20;     // GEMM-fused exchange: payload x (W-1) above this goes two-shot (B200_AR_FUSE_MAX_BYTES)
+  bool fuse_two_shot_always = false;    // B200_AR_FUSE_TWO_SHOT=1: two-shot exchange in the fused GEMM at any size (tests)
   bool no_ll = false;   // B200_AR_NO_LL=1: always the fence + flag kernel (bring-up / comparison)
 };
 
@@ -335,6 +336,7 @@ static cudaError_t ar_launch(const ArCtx& c, const void* in, void* out, int nvec
 
 
 static thread_local long long g_pending_ctx = 0, g_pending_m = 0, g_pending_n = 0;
+static thread_local bool g_pending_two_shot = false;
 
 // rows of 16-byte LL cells per output channel the fused GEMM epilogue may use (marlin_gemm_kernel.cuh: MPAD/4 groups,
 // plus up to one partly filled group per cluster rank)
@@ -353,6 +355,7 @@ bool ar_take_pending(ArFuse* out, long long* m_out, long long* n_out) {
   out->ll_off = ArLayout::ll_offset(c.world);
   out->ll_slot = ArLayout::ll_slot(c.slot_bytes);
   out->ctr_off = ArLayout::flags_bytes(c.world);
+  out->two_shot = g_pending_two_shot ? 1 : 0;
   *m_out = g_pending_m;
   *n_out = g_pending_n;
   g_pending_ctx = 0;
@@ -424,6 +427,7 @@ int b200_ar_init(int rank, int world, void* const* region_ptrs, int64_t max_byte
     if (!c.ptrs.region[i]) return set_error(B200_EINVAL, "ar_init: region pointer %d is null", i);
   c.live = true;
   { const char* e = getenv("B200_AR_NO_LL"); c.no_ll = e && atoi(e) != 0; }
+  { const char* e = getenv("B200_AR_FUSE_TWO_SHOT"); c.fuse_two_shot_always = e && atoi(e) != 0; }
   { const char* e = getenv("B200_AR_FUSE_MAX_BYTES"); if (e && atoll(e) >= 0) c.fuse_max_bytes = (size_t)atoll(e); }
   { const char* e = getenv("B200_AR_TWO_SHOT_BYTES"); if (e && atoll(e) >= 0) c.two_shot_bytes = (size_t)atoll(e); }
   std::lock_guard<std::mutex> g(g_ar_mu);
@@ -442,9 +446,9 @@ int b200_ar_fuse_next_gemm(int64_t ctx, int64_t m, int64_t n) {
   const size_t npad = (size_t)((n + 127) / 128) * 128;
   if (m < 1 || m > 128 || fused_cells(m) * npad * 16 > ArLayout::ll_slot(c.slot_bytes))
     return set_error(B200_ENOTSUP, "ar_fuse_next_gemm: [%lld, %lld] does not fit the exchange area", (long long)m, (long long)n);
-  // one-shot exchange: every rank sends its whole output to every peer; above this the two-shot kernel wins
-  if ((size_t)m * n * 2 * (c.world - 1) > c.fuse_max_bytes)
-    return set_error(B200_ENOTSUP, "ar_fuse_next_gemm: payload too large for the one-shot exchange at world %d", c.world);
+  // one-shot exchange (every rank sends its whole output to every peer) while payload x (W-1) stays small -- measured
+  // better at TP4 / 512 KiB --, two-shot (the owner rank of each 32 channels sums and broadcasts) above that
+  g_pending_two_shot = (c.world > 2 && (size_t)m * n * 2 * (c.world - 1) > c.fuse_max_bytes) || c.fuse_two_shot_always;
   g_pending_ctx = ctx; g_pending_m = m; g_pending_n = n;
   return B200_OK;
 }

@@ -15,6 +15,7 @@ struct ArFuse {
   unsigned long long ll_off;      // offset of the LL area inside a region
   unsigned long long ll_slot;     // bytes of one [parity][phase][rank] LL slot
   unsigned long long ctr_off;     // offset of {call counter, finished-CTA ticket}
+  int two_shot;                   // fused GEMM exchange: 0 = every rank sums everything, 1 = the cell's owner rank sums and broadcasts
 };
 
 __device__ __forceinline__ void st_ll(uint8_t* p, uint32_t d0, uint32_t d1, uint32_t e) {

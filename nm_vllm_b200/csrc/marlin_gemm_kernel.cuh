@@ -278,22 +278,36 @@ __device__ __forceinline__ float ar_unpack(uint32_t w, int hi) {
   const unsigned short b = (unsigned short)(hi ? (w >> 16) : (w & 0xffffu));
   return to_f32<T>(*reinterpret_cast<const T*>(&b));
 }
+// One-shot (owner < 0): every rank gets every rank's cell and sums.  Two-shot (owner = the rank that owns this thread's
+// channels, uniform per warp): the others push to the owner only (phase area 0), the owner sums and pushes the result to
+// everyone (phase area 1), the others pick it up -- (W-1)/W of the payload each way instead of (W-1) x.
 template <typename T>
-__device__ __forceinline__ void ar_push4(const ArFuse& ar, uint32_t epoch, size_t idx, const float (&v)[4]) {
+__device__ __forceinline__ void ar_push4(const ArFuse& ar, uint32_t epoch, size_t idx, const float (&v)[4], int owner) {
+  if (owner == ar.rank) return;   // the owner's own contribution stays in registers
   const uint32_t w0 = ar_pack2<T>(v[0], v[1]), w1 = ar_pack2<T>(v[2], v[3]);
   const size_t off = ar.ll_off + ((size_t)(epoch & 1u) * 2 * ar.world + ar.rank) * ar.ll_slot + idx * 16;
 #pragma unroll
   for (int q = 0; q < kArMaxWorld; ++q)
-    if (q < ar.world && q != ar.rank) st_ll(ar.region[q] + off, w0, w1, epoch);
+    if (q < ar.world && q != ar.rank && (owner < 0 || q == owner)) st_ll(ar.region[q] + off, w0, w1, epoch);
 }
 template <typename T>
-__device__ __forceinline__ void ar_sum4(const ArFuse& ar, uint32_t epoch, size_t idx, float (&v)[4]) {
-  const uint32_t w0 = ar_pack2<T>(v[0], v[1]), w1 = ar_pack2<T>(v[2], v[3]);
+__device__ __forceinline__ void ar_sum4(const ArFuse& ar, uint32_t epoch, size_t idx, float (&v)[4], int owner) {
   uint8_t* self = nullptr;
 #pragma unroll
   for (int q = 0; q < kArMaxWorld; ++q)
     if (q == ar.rank) self = ar.region[q];
-  const uint8_t* base = self + ar.ll_off + (size_t)(epoch & 1u) * 2 * ar.world * ar.ll_slot + idx * 16;
+  const size_t par_off = ar.ll_off + (size_t)(epoch & 1u) * 2 * ar.world * ar.ll_slot;
+  if (owner >= 0 && owner != ar.rank) {
+    // two-shot, not the owner: the finished sum arrives in the owner's slot of phase area 1
+    const uint8_t* src = self + par_off + (size_t)(ar.world + owner) * ar.ll_slot + idx * 16;
+    uint4 x;
+    do { x = ld_ll(src); } while (x.y != epoch || x.w != epoch);
+    v[0] = ar_unpack<T>(x.x, 0); v[1] = ar_unpack<T>(x.x, 1);
+    v[2] = ar_unpack<T>(x.z, 0); v[3] = ar_unpack<T>(x.z, 1);
+    return;
+  }
+  const uint32_t w0 = ar_pack2<T>(v[0], v[1]), w1 = ar_pack2<T>(v[2], v[3]);
+  const uint8_t* base = self + par_off + idx * 16;
   float s[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
   for (int q = 0; q < kArMaxWorld; ++q) {
@@ -310,6 +324,14 @@ __device__ __forceinline__ void ar_sum4(const ArFuse& ar, uint32_t epoch, size_t
   }
 #pragma unroll
   for (int i = 0; i < 4; ++i) v[i] = s[i];
+  if (owner >= 0) {
+    // two-shot owner: publish the rounded sums (what every rank will store) in my slot of phase area 1 of every peer
+    const uint32_t r0 = ar_pack2<T>(s[0], s[1]), r1 = ar_pack2<T>(s[2], s[3]);
+    const size_t off = par_off + (size_t)(ar.world + ar.rank) * ar.ll_slot + idx * 16;
+#pragma unroll
+    for (int q = 0; q < kArMaxWorld; ++q)
+      if (q < ar.world && q != ar.rank) st_ll(ar.region[q] + off, r0, r1, epoch);
+  }
 }
 
 // ---- the kernel --------------------------------------------------------------------------------------------------
@@ -677,6 +699,8 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       ar_epoch = *reinterpret_cast<volatile uint32_t*>(self + args.ar.ctr_off) + 1;
     }
     const size_t ar_npad = (size_t)args.n_tiles * kTileN;
+    // two-shot exchange: 32 consecutive channels (one epilogue warp) belong to one rank; -1 = one-shot
+    auto ar_owner = [&](int n) { return args.ar.two_shot ? (n >> 5) % args.ar.world : -1; };
     // stores this thread's ACCW final outputs (or, fused, exchanges them with the peers first): rows jb .. jb + ACCW - 1
     auto store_rows = [&](float (&acc)[ACCW], float ch_scale, T* cdst, int n, bool n_ok, int m_valid) {
       if (!n_ok) return;
@@ -684,12 +708,12 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
 #pragma unroll
         for (int g = 0; g < ACCW / 4; ++g) {
           const float v[4] = {acc[4 * g] * ch_scale, acc[4 * g + 1] * ch_scale, acc[4 * g + 2] * ch_scale, acc[4 * g + 3] * ch_scale};
-          ar_push4<T>(args.ar, ar_epoch, (size_t)(jb / 4 + g) * ar_npad + n, v);
+          ar_push4<T>(args.ar, ar_epoch, (size_t)(jb / 4 + g) * ar_npad + n, v, ar_owner(n));
         }
 #pragma unroll
         for (int g = 0; g < ACCW / 4; ++g) {
           float v[4] = {acc[4 * g] * ch_scale, acc[4 * g + 1] * ch_scale, acc[4 * g + 2] * ch_scale, acc[4 * g + 3] * ch_scale};
-          ar_sum4<T>(args.ar, ar_epoch, (size_t)(jb / 4 + g) * ar_npad + n, v);
+          ar_sum4<T>(args.ar, ar_epoch, (size_t)(jb / 4 + g) * ar_npad + n, v, ar_owner(n));
 #pragma unroll
           for (int i = 0; i < 4; ++i)
             if (jb + 4 * g + i < m_valid) cdst[(size_t)(jb + 4 * g + i) * args.N] = from_f32<T>(v[i]);
@@ -819,7 +843,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
             const int mb = c_rank + k * 4 * CS;
             if (mb < m_valid) {
               row_group(mb, keep[it]);
-              if (n_ok) ar_push4<T>(args.ar, ar_epoch, ((size_t)c_rank * G + k) * ar_npad + n, keep[it]);
+              if (n_ok) ar_push4<T>(args.ar, ar_epoch, ((size_t)c_rank * G + k) * ar_npad + n, keep[it], ar_owner(n));
             }
           }
 #pragma unroll
@@ -827,7 +851,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
             const int k = (et >> 7) + it * Cfg::NEG;
             const int mb = c_rank + k * 4 * CS;
             if (mb < m_valid && n_ok) {
-              ar_sum4<T>(args.ar, ar_epoch, ((size_t)c_rank * G + k) * ar_npad + n, keep[it]);
+              ar_sum4<T>(args.ar, ar_epoch, ((size_t)c_rank * G + k) * ar_npad + n, keep[it], ar_owner(n));
 #pragma unroll
               for (int i = 0; i < 4; ++i)
                 if (mb + i * CS < m_valid) cdst[(size_t)(mb + i * CS) * args.N] = from_f32<T>(keep[it][i]);
