@@ -186,7 +186,8 @@ int b200_ar_dispose(int64_t ctx);
 /* Fused GEMM + all-reduce: the NEXT b200_gptq_marlin_gemm issued by this host thread, whose output must be [m, n],
  * exchanges its output tiles with the peers inside its epilogue (flag-in-data cells in the peers' regions) and writes
  * the all-reduced result -- bit-identical to b200_gptq_marlin_gemm followed by b200_ar_all_reduce.  B200_ENOTSUP when
- * the shape does not qualify (m > 128, or the cells do not fit the exchange area): run the two calls separately then.  Replaces RowParallelLinear.forward's GEMM -> tensor_model_parallel_all_reduce pair
+ * the shape does not qualify (m > 128, the cells do not fit the exchange area, or payload x (world-1) is beyond the
+ * one-shot range where the stand-alone two-shot kernel is faster): run the two calls separately then.  Replaces RowParallelLinear.forward's GEMM -> tensor_model_parallel_all_reduce pair
  * (vllm/model_executor/layers/linear.py:779-803). */
 int b200_ar_fuse_next_gemm(int64_t ctx, int64_t m, int64_t n);
 

@@ -57,7 +57,7 @@ struct ArCtx {
   ArPtrs ptrs;
   bool live = false;
   size_t two_shot_bytes = 256 * 1024;   // W > 2: payload x (W-1) above this goes two-shot (B200_AR_TWO_SHOT_BYTES)
-  size_t fuse_max_bytes = 2u << 20;     // GEMM-fused exchange: payload x (W-1) above this goes two-shot (B200_AR_FUSE_MAX_BYTES)
+  size_t fuse_max_bytes = 2u << 20;     // GEMM-fused one-shot exchange: payload x (W-1) limit (B200_AR_FUSE_MAX_BYTES)
   bool fuse_two_shot_always = false;    // B200_AR_FUSE_TWO_SHOT=1: two-shot exchange in the fused GEMM at any size (tests)
   bool no_ll = false;   // B200_AR_NO_LL=1: always the fence + flag kernel (bring-up / comparison)
 };
@@ -446,9 +446,14 @@ int b200_ar_fuse_next_gemm(int64_t ctx, int64_t m, int64_t n) {
   const size_t npad = (size_t)((n + 127) / 128) * 128;
   if (m < 1 || m > 128 || fused_cells(m) * npad * 16 > ArLayout::ll_slot(c.slot_bytes))
     return set_error(B200_ENOTSUP, "ar_fuse_next_gemm: [%lld, %lld] does not fit the exchange area", (long long)m, (long long)n);
-  // one-shot exchange (every rank sends its whole output to every peer) while payload x (W-1) stays small -- measured
-  // better at TP4 / 512 KiB --, two-shot (the owner rank of each 32 channels sums and broadcasts) above that
-  g_pending_two_shot = (c.world > 2 && (size_t)m * n * 2 * (c.world - 1) > c.fuse_max_bytes) || c.fuse_two_shot_always;
+  // The fused exchange is one-shot (every rank sends its whole output to every peer) and only taken while
+  // payload x (W-1) stays small.  Measured on 8 x B200, Llama-3-8B batch 64 (profiles/r1_bench_tp8_*.json): above that
+  // GEMM + the stand-alone two-shot kernel (2.37 ms/step) beats both a one-shot (2.95) and a two-shot (2.59) exchange
+  // inside the epilogue -- the few epilogue warps of 32 tiles poll serially where the stand-alone kernel has 128 CTAs.
+  // B200_AR_FUSE_TWO_SHOT=1 forces the two-shot epilogue exchange (kept for tests and further tuning).
+  g_pending_two_shot = c.fuse_two_shot_always;
+  if (!g_pending_two_shot && (size_t)m * n * 2 * (c.world - 1) > c.fuse_max_bytes)
+    return set_error(B200_ENOTSUP, "ar_fuse_next_gemm: payload too large for the one-shot exchange at world %d", c.world);
   g_pending_ctx = ctx; g_pending_m = m; g_pending_n = n;
   return B200_OK;
 }
