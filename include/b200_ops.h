@@ -148,6 +148,12 @@ int b200_rotary_embedding(const int64_t* positions, void* query, void* key, int 
                           int num_heads, int num_kv_heads, int64_t query_stride, int64_t key_stride,
                           int dtype, void* stream);
 
+/* greedy sampling: out[t] = argmax_v logits[t, v] (lowest index on ties, like torch.argmax on CUDA); logits
+ * [num_tokens, vocab] with row pitch row_stride (elements).  Reference: vllm/model_executor/layers/sampler.py
+ * _greedy_sample (torch.argmax); here so that the whole decode step is graph-captured kernels of this library. */
+int b200_greedy_sample(int64_t* out, const void* logits, int64_t num_tokens, int64_t vocab,
+                       int64_t row_stride, int dtype, void* stream);
+
 /* ---- KV block maintenance: csrc/cache.h:8-32 ----------------------------
  * copy_blocks (cache_kernels.cu:64-148): key_cache_ptrs / value_cache_ptrs are DEVICE arrays of
  * num_layers device pointers, block_mapping a DEVICE int64 [num_pairs, 2] of (src, dst) block numbers;

@@ -47,6 +47,14 @@ def paged_attention_v2(out: torch.Tensor, exp_sum: torch.Tensor, max_logits: tor
 
 
 # ---- glue: vllm/_custom_ops.py:48-50 (silu_and_mul), :132-160 (rotary_embedding, rms_norm, fused_add_rms_norm) ----
+def greedy_sample(logits: torch.Tensor) -> torch.Tensor:
+    """argmax over the vocabulary (lowest index on ties) -- the temperature-0 branch of the reference's Sampler
+    (vllm/model_executor/layers/sampler.py _greedy_sample)."""
+    out = torch.empty((logits.shape[0],), dtype=torch.int64, device=logits.device)
+    _ops().greedy_sample(out, logits)
+    return out
+
+
 def silu_and_mul(out: torch.Tensor, x: torch.Tensor) -> None:
     _ops().silu_and_mul(out, x)
 

@@ -436,6 +436,16 @@ void fused_add_rms_norm(torch::Tensor& input, torch::Tensor& residual, torch::Te
                                    cur_stream(input)),
            "fused_add_rms_norm");
 }
+void greedy_sample(torch::Tensor& out, torch::Tensor& logits) {
+  TORCH_CHECK(logits.dim() == 2 && logits.stride(1) == 1, "greedy_sample: logits must be [tokens, vocab] with unit inner stride");
+  TORCH_CHECK(out.scalar_type() == at::ScalarType::Long && out.is_contiguous() && out.numel() == logits.size(0),
+              "greedy_sample: out must be contiguous int64 [tokens]");
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(logits));
+  raise_if(b200_greedy_sample(out.data_ptr<int64_t>(), logits.data_ptr(), logits.size(0), logits.size(1), logits.stride(0),
+                              dtype_enum(logits.scalar_type(), "greedy_sample"), cur_stream(logits)),
+           "greedy_sample");
+}
+
 void silu_and_mul(torch::Tensor& out, torch::Tensor& input) {
   TORCH_CHECK(input.is_contiguous() && out.is_contiguous());
   const int d = (int)input.size(-1) / 2;
@@ -502,6 +512,8 @@ TORCH_LIBRARY(_b200_C, ops) {
       "    int blocksparse_head_sliding_step) -> ()");
   ops.impl("paged_attention_v2", torch::kCUDA, &paged_attention_v2);
 
+  ops.def("greedy_sample(Tensor! out, Tensor logits) -> ()");
+  ops.impl("greedy_sample", torch::kCUDA, &greedy_sample);
   ops.def("silu_and_mul(Tensor! out, Tensor input) -> ()");
   ops.impl("silu_and_mul", torch::kCUDA, &silu_and_mul);
   ops.def("rms_norm(Tensor! out, Tensor input, Tensor weight, float epsilon) -> ()");

@@ -253,7 +253,7 @@ class SyntheticLlama:
             parts = [torch.empty_like(logits) for _ in range(self.tp)]
             torch.distributed.all_gather(parts, logits, group=self.group)
             logits = torch.cat(parts, dim=-1)
-        return torch.argmax(logits, dim=-1)
+        return ops.greedy_sample(logits)
 
 
 class DecodeEngine:

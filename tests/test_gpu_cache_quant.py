@@ -148,3 +148,53 @@ def test_glue_kernels(ops, dtype):
         wq, wk = ops_ref.rotary_embedding(pos, q, k, D, cache, neox)
         assert torch.allclose(qd.cpu().float(), wq.float(), **tol)
         assert torch.allclose(kd.cpu().float(), wk.float(), **tol)
+
+
+def _first_max(x):
+    """lowest index of the row maximum (the tie rule of torch.argmax's CUDA reduction), computed without argmax"""
+    xf = x.float()
+    eq = xf == xf.max(dim=-1, keepdim=True).values
+    idx = torch.arange(x.shape[1], device=x.device).expand_as(xf)
+    return torch.where(eq, idx, x.shape[1]).min(dim=-1).values
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+@pytest.mark.parametrize("shape", [(64, 128256), (1, 32000), (7, 1000), (3, 8), (5, 16032), (2, 50257)])
+def test_greedy_sample_matches_argmax(ops, dtype, shape):
+    g = torch.Generator(device=DEV).manual_seed(3)
+    x = torch.randn(shape, generator=g, device=DEV).to(dtype)
+    assert torch.equal(ops.greedy_sample(x), _first_max(x))
+    # ties: few distinct values -> the lowest index of the maximum must win
+    q = torch.randint(0, 4, shape, generator=g, device=DEV).to(dtype)
+    assert torch.equal(ops.greedy_sample(q), _first_max(q))
+    # strided rows (a slice of a wider logits buffer, 16-byte aligned or not)
+    wide = torch.randn((shape[0], shape[1] + 24), generator=g, device=DEV).to(dtype)
+    for off in (8, 3):
+        assert torch.equal(ops.greedy_sample(wide[:, off:off + shape[1]]), _first_max(wide[:, off:off + shape[1]]))
+
+
+def test_decode_step_tokens_are_first_max_of_logits(ops, monkeypatch):
+    """The engine's sampled ids are the lowest-index maxima of the logits it computed (eager step and graph replay)."""
+    from nm_vllm_b200 import decoder
+    seen = {}
+    orig = ops.greedy_sample
+
+    def capture(logits):
+        if not torch.cuda.is_current_stream_capturing():
+            seen["logits"] = logits.clone()
+        return orig(logits)
+
+    monkeypatch.setattr(decoder.ops, "greedy_sample", capture)
+    model = decoder.SyntheticLlama(decoder.TINY, device=DEV, num_blocks=64, max_pos=256)
+    eng = decoder.DecodeEngine(model, batch=4, max_ctx=96)
+    hi = eng.host_inputs(80, seed=0)
+    eng.load_inputs(hi)
+    eng._device_step(80)
+    torch.cuda.synchronize()
+    want = _first_max(seen["logits"])
+    assert torch.equal(eng.d_out, want)
+    assert torch.equal(eng.step(hi).to(DEV), want)   # CUDA-graph replay of the same step
+    # informational: where torch.argmax's tie choice differs, both point at equal logits
+    ta = torch.argmax(seen["logits"], dim=-1)
+    rows = torch.arange(4, device=DEV)
+    assert torch.equal(seen["logits"][rows, ta], seen["logits"][rows, want])
