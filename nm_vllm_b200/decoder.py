@@ -163,9 +163,9 @@ class SyntheticLlama:
             kc = torch.empty((num_blocks, self.Hkv, D // x, block_size, x), dtype=cache_t, device=device)
             vc = torch.empty((num_blocks, self.Hkv, D, block_size), dtype=cache_t, device=device)
             if cache_t == torch.uint8:
-                kc.random_(0, 120); vc.random_(0, 120)
+                kc.random_(0, 120, generator=gen); vc.random_(0, 120, generator=gen)
             else:
-                kc.uniform_(-D ** -0.5, D ** -0.5); vc.uniform_(-D ** -0.5, D ** -0.5)
+                kc.uniform_(-D ** -0.5, D ** -0.5, generator=gen); vc.uniform_(-D ** -0.5, D ** -0.5, generator=gen)
             self.kv.append((kc, vc))
         self.scale = float(D ** -0.5)
 
