@@ -270,7 +270,7 @@ class DecodeEngine:
         B = batch
         self.d_tok = torch.zeros(B, dtype=torch.long, device=dev)
         self.d_pos = torch.zeros(B, dtype=torch.long, device=dev)
-        self.d_slot = torch.zeros(B, dtype=torch.long, device=dev)
+        self.d_slot = torch.full((B,), -1, dtype=torch.long, device=dev)   # _PAD_SLOT_ID until inputs are loaded (model_runner.py:60)
         self.d_lens = torch.ones(B, dtype=torch.int32, device=dev)
         self.d_bt = torch.zeros((B, self.max_blocks), dtype=torch.int32, device=dev)
         self.d_out = torch.zeros(B, dtype=torch.long, device=dev)
@@ -339,11 +339,13 @@ class DecodeEngine:
 
     def step(self, hi):
         """Host in -> host out (synchronous)."""
+        # inputs first: the eager warm-up / graph capture inside prepare() then runs on real metadata (its cache writes
+        # are the ones the step makes anyway) instead of whatever the device buffers held
+        self.load_inputs(hi)
         if self.use_graph:
             self.prepare(hi["max_seq_len"])
         else:
             self.graph_max_len = hi["max_seq_len"]
-        self.load_inputs(hi)
         self.run_device()
         self.h_out.copy_(self.d_out, non_blocking=True)
         torch.cuda.current_stream().synchronize()
