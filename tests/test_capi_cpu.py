@@ -96,3 +96,24 @@ def test_product_path_never_imports_oracle():
                 if "import oracle" in txt or "from oracle" in txt or "oracle/" in txt:
                     bad.append(os.path.join(dp, fn))
     assert not bad, bad
+
+
+def test_all_reduce_host_checks_without_gpu():
+    """Argument validation of the NVLink all-reduce entry points happens before any CUDA call."""
+    import ctypes
+    from nm_vllm_b200 import capi
+    lib = capi.lib()
+    n = ctypes.c_int64()
+    assert lib.b200_ar_region_bytes(2, ctypes.c_int64(1 << 20), ctypes.byref(n)) == 0
+    two = n.value
+    assert lib.b200_ar_region_bytes(8, ctypes.c_int64(1 << 20), ctypes.byref(n)) == 0
+    assert n.value > two > 2 * 2 * (1 << 20)          # flags + LL cells + two parities of W slots
+    assert lib.b200_ar_region_bytes(9, ctypes.c_int64(1 << 20), ctypes.byref(n)) == -1   # B200_EINVAL
+    assert lib.b200_ar_region_bytes(2, ctypes.c_int64(0), ctypes.byref(n)) == -1
+    ctx = ctypes.c_int64()
+    regions = (ctypes.c_void_p * 3)(1, 2, 3)
+    assert lib.b200_ar_init(0, 3, regions, ctypes.c_int64(1 << 20), ctypes.byref(ctx)) == -1   # world must be 2/4/6/8
+    assert "world must be" in capi.last_error()
+    assert lib.b200_ar_all_reduce(ctypes.c_int64(12345), None, None, ctypes.c_int64(8), 1, None) == -1
+    assert lib.b200_ar_fuse_next_gemm(ctypes.c_int64(12345), ctypes.c_int64(4), ctypes.c_int64(128)) == -1
+    assert lib.b200_ar_dispose(ctypes.c_int64(0)) == -1
