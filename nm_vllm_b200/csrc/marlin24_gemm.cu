@@ -256,7 +256,7 @@ static int launch_m24(m24::Args a, cudaStream_t st) {
   int dev = 0;
   cudaGetDevice(&dev);
   GemmScratch sc;
-  if (int e = gemm_ensure_scratch(dev, (size_t)a.n_tiles * m_chunks * splits * MC * 64, a.n_tiles * m_chunks, st, &sc)) return e;
+  if (int e = gemm_ensure_scratch(dev, splits > 1 ? (size_t)a.n_tiles * m_chunks * splits * MC * 64 : 1, a.n_tiles * m_chunks, st, &sc)) return e;
   a.scratch = sc.partials;
   a.counters = sc.counters;
   const size_t smem = (size_t)(kWarps * 32 * MB * 32 + MC * 64) * 4;

@@ -1,6 +1,6 @@
 // C ABI of the Marlin-layout W4A16 / W8A16 GEMM (kernel: marlin_gemm_kernel.cuh; instantiations: marlin_gemm_inst_*.cu).
 // Reference: csrc/quantization/gptq_marlin/gptq_marlin.cu:1735-1868 (op), csrc/ops.h:75-77, :86-90.
-#include "marlin_gemm_kernel.cuh"
+#include "marlin_decode_kernel.cuh"
 
 namespace b200 {
 
@@ -25,6 +25,8 @@ struct DeviceScratch {
   size_t partial_floats = 0;
   size_t a_tmp_bytes = 0;
   int counter_ints = 0;
+  float* dec_partials = nullptr;
+  int* dec_counters = nullptr;
 };
 static DeviceScratch g_scratch[64];
 
@@ -34,24 +36,35 @@ static bool capturing(cudaStream_t st) {
   return cap != cudaStreamCaptureStatusNone;
 }
 
+// Scratch policy (CUDA-graph safety): a buffer that a captured graph may point to is NEVER freed.  The first call sizes
+// the scratch for the largest request any of the three GEMM kernels makes at decode / prefill shapes
+// (b200_gemm_scratch_reserve can raise that before capture); a later, larger request outside capture allocates a new
+// buffer and RETIRES the old one (kept alive until process exit), so graphs captured earlier keep replaying correctly;
+// during capture a too-small scratch is an error, never a reallocation.
 int gemm_ensure_scratch(int dev, size_t partial_floats, int counter_ints, cudaStream_t st, GemmScratch* out) {
   DeviceScratch& s = g_scratch[dev & 63];
   if (!(s.partials && s.partial_floats >= partial_floats && s.counter_ints >= counter_ints)) {
     if (capturing(st))
       return set_error(B200_EINVAL,
-                       "marlin gemm: split-K scratch must be reserved before CUDA-graph capture "
-                       "(run one eager call or b200_gemm_scratch_reserve first)");
-    // grow generously once: worst case MPAD = 128 on 256 CTAs
-    if (partial_floats < (size_t)256 * kTileN * 128) partial_floats = (size_t)256 * kTileN * 128;
+                       "gemm: split-K scratch must be reserved before CUDA-graph capture "
+                       "(run one eager call of the largest shape or b200_gemm_scratch_reserve first)");
+    // floor: scaled_mm at MT = 256 on a full grid (num_sms * 2 * 128 * 256 floats, 39 MB) covers every decode shape
+    const size_t floor_floats = (size_t)num_sms() * 2 * kTileN * 256;
+    if (partial_floats < floor_floats) partial_floats = floor_floats;
+    if (partial_floats < s.partial_floats) partial_floats = s.partial_floats;
     if (counter_ints < 1 << 16) counter_ints = 1 << 16;
-    cudaDeviceSynchronize();
-    if (s.partials) cudaFree(s.partials);
-    if (s.counters) cudaFree(s.counters);
-    if (cudaMalloc(&s.partials, partial_floats * sizeof(float)) != cudaSuccess ||
-        cudaMalloc(&s.counters, counter_ints * sizeof(int)) != cudaSuccess)
-      return set_error(B200_ECUDA, "marlin gemm: scratch allocation failed");
-    cudaMemset(s.counters, 0, counter_ints * sizeof(int));
-    cudaDeviceSynchronize();
+    if (counter_ints < s.counter_ints) counter_ints = s.counter_ints;
+    float* np = nullptr;
+    int* nc = nullptr;
+    if (cudaMalloc(&np, partial_floats * sizeof(float)) != cudaSuccess ||
+        cudaMalloc(&nc, (size_t)counter_ints * sizeof(int)) != cudaSuccess) {
+      cudaGetLastError();
+      return set_error(B200_ECUDA, "gemm: scratch allocation failed (%zu floats)", partial_floats);
+    }
+    cudaMemsetAsync(nc, 0, (size_t)counter_ints * sizeof(int), st);
+    // the retired buffers stay allocated on purpose (see above); counters of the old buffer are all zero between launches
+    s.partials = np;
+    s.counters = nc;
     s.partial_floats = partial_floats;
     s.counter_ints = counter_ints;
   }
@@ -62,14 +75,33 @@ int gemm_ensure_scratch(int dev, size_t partial_floats, int counter_ints, cudaSt
   return B200_OK;
 }
 
+// decode kernel: fixed-size partial slots (2 per CTA) and ticket counters, allocated once
+int dec_scratch(int dev, cudaStream_t st, float** partials, int** counters) {
+  DeviceScratch& s = g_scratch[dev & 63];
+  if (!s.dec_partials) {
+    if (capturing(st))
+      return set_error(B200_EINVAL, "marlin decode gemm: scratch must exist before CUDA-graph capture (run one eager call or "
+                                    "b200_gemm_scratch_reserve first)");
+    if (cudaMalloc(&s.dec_partials, (size_t)kDecMaxGrid * 2 * 64 * kTileN * sizeof(float)) != cudaSuccess ||
+        cudaMalloc(&s.dec_counters, (size_t)kDecMaxTiles * sizeof(int)) != cudaSuccess) {
+      cudaGetLastError();
+      s.dec_partials = nullptr;
+      return set_error(B200_ECUDA, "marlin decode gemm: scratch allocation failed");
+    }
+    cudaMemsetAsync(s.dec_counters, 0, (size_t)kDecMaxTiles * sizeof(int), st);
+  }
+  *partials = s.dec_partials;
+  *counters = s.dec_counters;
+  return B200_OK;
+}
+
 static int ensure_a_tmp(int dev, size_t bytes, cudaStream_t st) {
   DeviceScratch& s = g_scratch[dev & 63];
   if (s.a_tmp && s.a_tmp_bytes >= bytes) return B200_OK;
   if (capturing(st))
     return set_error(B200_EINVAL, "marlin gemm: act-order scratch must be reserved before CUDA-graph capture (run one eager call first)");
   if (bytes < ((size_t)8 << 20)) bytes = (size_t)8 << 20;
-  cudaDeviceSynchronize();
-  if (s.a_tmp) cudaFree(s.a_tmp);
+  // the old buffer (if any) is retired, not freed: a captured graph may still point to it
   if (cudaMalloc(&s.a_tmp, bytes) != cudaSuccess) return set_error(B200_ECUDA, "marlin gemm: act-order scratch allocation failed");
   s.a_tmp_bytes = bytes;
   return B200_OK;
@@ -78,10 +110,21 @@ static int ensure_a_tmp(int dev, size_t bytes, cudaStream_t st) {
 }  // namespace b200
 
 extern "C" int b200_gemm_scratch_reserve(int64_t max_m, int64_t max_n) {
-  (void)max_m; (void)max_n;
+  using namespace b200;
   int dev = 0;
   cudaGetDevice(&dev);
-  return b200::gemm_ensure_scratch(dev, 1, 1, 0, nullptr);
+  float* p;
+  int* c;
+  if (int e = dec_scratch(dev, 0, &p, &c)) return e;
+  // largest request of the three kernels for a [max_m, max_n] output: marlin (grid x 128 x MPAD), scaled_mm
+  // (grid x 2 x 128 x MT), marlin24 split-K (n_tiles x m_chunks x splits x 64 x 64)
+  const size_t m = (size_t)(max_m > 0 ? max_m : 1), n = (size_t)(max_n > 0 ? max_n : 1);
+  const size_t m_pad = (m + 63) / 64 * 64;
+  size_t want = (size_t)num_sms() * 2 * kTileN * 256;
+  const size_t m24 = ((n + 127) / 128) * m_pad * 64 * 8;
+  if (m24 > want) want = m24;
+  const size_t tiles = ((n + 63) / 64) * ((m + 15) / 16);
+  return gemm_ensure_scratch(dev, want, (int)(tiles < (1u << 20) ? tiles : (1u << 20)), 0, nullptr);
 }
 
 extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_weight, const void* b_scales,
@@ -149,6 +192,15 @@ extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_
     }
   }
   int rc;
+  static const int force_old = getenv("B200_GEMM_OLD") ? atoi(getenv("B200_GEMM_OLD")) : 0;
+  if (size_m <= 64 && ga.ar.world <= 1 && !force_old && ga.n_tiles <= kDecMaxTiles) {
+    // decode shapes: the small-CTA kernel (marlin_decode_kernel.cuh)
+    if (dtype == B200_F16) rc = (num_bits == 4) ? dispatch_decode_f16_4(ga, a, lda, st) : dispatch_decode_f16_8(ga, a, lda, st);
+    else rc = (num_bits == 4) ? dispatch_decode_bf16_4(ga, a, lda, st) : dispatch_decode_bf16_8(ga, a, lda, st);
+    if (rc) return rc;
+    B200_LAUNCH_CHECK("gptq_marlin_gemm");
+    return B200_OK;
+  }
   if (dtype == B200_F16) rc = (num_bits == 4) ? dispatch_gemm_f16_4(ga, a, lda, st) : dispatch_gemm_f16_8(ga, a, lda, st);
   else rc = (num_bits == 4) ? dispatch_gemm_bf16_4(ga, a, lda, st) : dispatch_gemm_bf16_8(ga, a, lda, st);
   if (rc) return rc;
