@@ -43,6 +43,7 @@ def load_extension():
 
     import torch
 
-    ctypes.CDLL(_LIB_OPS, mode=ctypes.RTLD_GLOBAL)
+    # B200_LIB_OPS: tuning builds of the same library (tools/build_variant.py), same soname
+    ctypes.CDLL(os.environ.get("B200_LIB_OPS", _LIB_OPS), mode=ctypes.RTLD_GLOBAL)
     torch.ops.load_library(_LIB_TORCH)
     _loaded = True

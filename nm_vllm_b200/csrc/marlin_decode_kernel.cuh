@@ -385,6 +385,434 @@ marlin_decode_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_co
   if (warp == 2) tmem_dealloc<Cfg::TMEM_COLS>(*tmem_slot_p);
 }
 
+// =====================================================================================================================
+// v2 (4-bit, group 128 or channelwise): zero point and group scale leave the dequant warps.
+//
+// The ALU pipe (LOP3 / SHF, one warp instruction per 2 clocks per scheduler) is what bounds the expansion: 7 ALU + 8 FMA
+// pipe instructions per packed word above.  Here a packed word costs 4 LOP3 (ALU) + 3 right shifts issued as IMAD.HI
+// (FMA pipe) and nothing else:
+//   * the weights go into TMEM WITH their bias, w' = 2^e + nibble (bf16: 128 + n, fp16: 1024 + n, both exact); the
+//     missing  -(2^e + 8) * sum_k a[m,k]  is added by ONE extra tcgen05.mma per 128-k stage whose A operand is a constant
+//     slab in TMEM and whose B operand holds the per-(row, group) activation sums (split hi + lo so that the 16-bit
+//     operand carries ~16 bits of the sum; spread over the 16 k positions so that fp16 cannot overflow).  The sums come
+//     from the kernel that produced the activations (or from act_group_sums_kernel): fp32 [K/128][stride];
+//   * at group 128 a stage is exactly one quantisation group: every stage gets a fresh accumulator (two, ping-pong) and
+//     the dequant warps -- which own the TMEM lane quarters -- read it back one stage later and apply the group scale
+//     in fp32: acc[m] += s[g, n] * D_g[n, m].  Channelwise keeps one accumulator per tile segment.
+// Everything else (rings, stream-K partition, last-arriver reduction) is the machine above.
+template <typename T> struct ZpcFmt;
+template <> struct ZpcFmt<__nv_bfloat16> { static constexpr uint32_t EX = 0x43004300u; static constexpr float BIAS = 136.f; };
+template <> struct ZpcFmt<__half> { static constexpr uint32_t EX = 0x64006400u; static constexpr float BIAS = 1032.f; };
+
+#ifndef B200_DEC_NSHF_FMA
+#define B200_DEC_NSHF_FMA 3      // how many of the three shifts go to the FMA pipe as IMAD.HI (rest: SHF on the ALU pipe)
+#endif
+
+template <typename T>
+__device__ __forceinline__ void dequant4_biased(uint32_t q, uint32_t* o, const uint32_t (&shmul)[3]) {
+  constexpr uint32_t MASK = 0x000f000f, EX = ZpcFmt<T>::EX;
+  const uint32_t q4 = B200_DEC_NSHF_FMA >= 1 ? __umulhi(q, shmul[0]) : (q >> 4);
+  const uint32_t q8 = B200_DEC_NSHF_FMA >= 2 ? __umulhi(q, shmul[1]) : (q >> 8);
+  const uint32_t q12 = B200_DEC_NSHF_FMA >= 3 ? __umulhi(q, shmul[2]) : (q >> 12);
+  asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(o[0]) : "r"(q), "n"(MASK), "n"(EX));     // p0,p4
+  asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(o[2]) : "r"(q4), "n"(MASK), "n"(EX));    // p1,p5
+  asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(o[1]) : "r"(q8), "n"(MASK), "n"(EX));    // p2,p6
+  asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(o[3]) : "r"(q12), "n"(MASK), "n"(EX));   // p3,p7
+}
+
+constexpr int kDecNC = 8;   // correction-slab ring: 8 stages = two 64-k boxes of four k16 slabs
+
+#ifndef B200_DEC2_DQW16
+#define B200_DEC2_DQW16 1
+#endif
+
+template <int MPAD, int GPS>
+struct Dec2Cfg {
+  static constexpr int DQW = MPAD <= 16 ? B200_DEC2_DQW16 : 2;
+  static constexpr int NDQ = 4 * DQW;
+  static constexpr int THREADS = 32 * (kDecCtrlWarps + NDQ);
+  static constexpr int EW = MPAD / DQW;
+  static constexpr int NACC = GPS == 1 ? 2 : 1;
+  static constexpr int TMEM_COLS = (MPAD <= 16 && DQW == 1) ? 128 : 256;
+  static constexpr int OCC = 512 / TMEM_COLS >= 3 ? 3 : 2;
+  // TMEM: [64-k operand slots][accumulators][constant slab of the correction MMA, 8 columns]
+  static constexpr int SLOT_COL0 = 0;
+  static constexpr int NSLOT = (TMEM_COLS - 8 - NACC * MPAD) / 32 > 4 ? 4 : (TMEM_COLS - 8 - NACC * MPAD) / 32;
+  static constexpr int ACC_COL0 = SLOT_COL0 + NSLOT * 32;
+  static constexpr int CONST_COL = ACC_COL0 + NACC * MPAD;
+  static constexpr int W_ROW_BYTES = kTileN * 16 * 4 / 8;
+  static constexpr int W_STAGE_BYTES = kDecSlabs * W_ROW_BYTES;              // 8 KB
+  static constexpr int A_BOX_BYTES = MPAD * 128;
+  static constexpr int A_STAGE_BYTES = 2 * A_BOX_BYTES;
+  static constexpr int S_STAGE_BYTES = 256;                                  // one 128-column scale row
+  static constexpr int C_BYTES = 2 * A_BOX_BYTES;                            // correction ring
+  static constexpr int NA = MPAD <= 32 ? 4 : 3;
+  static constexpr int BUDGET = (227 * 1024) / OCC - 1024 - 1024 - 512;
+  static constexpr int NW_RAW = (BUDGET - NA * (A_STAGE_BYTES + S_STAGE_BYTES) - C_BYTES) / W_STAGE_BYTES;
+  static constexpr int NW = NW_RAW > 8 ? 8 : NW_RAW;
+  static constexpr int NBARS = 2 * NW + 2 * NA + 2 * NSLOT + 4 + 2 * kDecNC;
+  static constexpr int SMEM_BYTES = 1024 + NA * (A_STAGE_BYTES + S_STAGE_BYTES) + C_BYTES + NW * W_STAGE_BYTES + NBARS * 8 + 16;
+  static_assert(NSLOT >= 2, "TMEM operand ring");
+  static_assert(NW >= 2, "weight ring");
+  static_assert(NBARS * 8 + 16 <= 512, "barrier area");
+  static_assert(EW % 16 == 0, "epilogue reads 16 columns at a time");
+};
+
+template <typename T, int MPAD, int GPS>   // GPS: 0 channelwise, 1 group 128
+__global__ void __launch_bounds__(Dec2Cfg<MPAD, GPS>::THREADS, Dec2Cfg<MPAD, GPS>::OCC)
+marlin_decode2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
+                      const __grid_constant__ CUtensorMap tmap_s, const GemmArgs args) {
+  using Cfg = Dec2Cfg<MPAD, GPS>;
+  constexpr int NW = Cfg::NW, NA = Cfg::NA, NSLOT = Cfg::NSLOT, DQW = Cfg::DQW, NACC = Cfg::NACC, NC = kDecNC;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  // layout: [activation stages] [correction boxes] (1024-aligned) [weight stages] [scale rows] [barriers]
+  const uint32_t act_base = smem_base;
+  const uint32_t corr_base = act_base + NA * Cfg::A_STAGE_BYTES;
+  const uint32_t w_base = corr_base + Cfg::C_BYTES;
+  const uint32_t sc_base = w_base + NW * Cfg::W_STAGE_BYTES;
+  const uint32_t bar_base = sc_base + NA * Cfg::S_STAGE_BYTES;
+  constexpr int B_WE = NW, B_AF = 2 * NW, B_AE = B_AF + NA, B_SF = B_AE + NA, B_SE = B_SF + NSLOT, B_CF = B_SE + NSLOT,
+                B_CE = B_CF + NC, B_ACF = B_CE + NC, B_ACE = B_ACF + 2;
+  auto bar = [&](int i) { return bar_base + 8u * i; };
+  const uint32_t tmem_slot = bar_base + 8u * Cfg::NBARS;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  volatile uint32_t* tmem_slot_p = reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
+  volatile int* ticket_p = reinterpret_cast<volatile int*>(smem_gen + (tmem_slot - smem_base) + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmap_w);
+    prefetch_tmap(&tmap_a);
+    if (GPS != 0) prefetch_tmap(&tmap_s);
+  }
+  if (threadIdx.x >= 32 && threadIdx.x < 32 + Cfg::NBARS) {
+    const int i = threadIdx.x - 32;
+    uint32_t cnt = 1;                                            // wfull, actfull, slotempty, corrfull/empty, accfull
+    if (i >= B_WE && i < B_AF) cnt = Cfg::NDQ;                   // wempty: every dequant warp
+    else if (i >= B_AE && i < B_SF) cnt = 1 + (GPS != 0 ? Cfg::NDQ : 0);   // actempty: issuer commit (+ scale readers)
+    else if (i >= B_SF && i < B_SE) cnt = 4;                     // slotfull: the four lane-quarter warps
+    else if (i >= B_ACE) cnt = Cfg::NDQ;                         // accempty: every epilogue warp
+    mbar_init(bar(i), cnt);
+    fence_barrier_init();
+  }
+  __syncthreads();
+  pdl_launch_dependents();
+
+  const int KS = args.KS;
+  const Partition part(args.total_units, (int)gridDim.x);
+  const int u_begin = part.start((int)blockIdx.x);
+  const int u_end = part.start((int)blockIdx.x + 1);
+  const int n_units = u_end - u_begin;
+
+  auto get_tmem_base = [&]() -> uint32_t {
+    tc_fence_before();
+    asm volatile("bar.sync 2, %0;" ::"n"(Cfg::THREADS - 64) : "memory");
+    tc_fence_after();
+    return *tmem_slot_p;
+  };
+
+  if (warp == 0) {
+    // ================= weight producer (no PDL wait: weights are static) ============================================
+    const uint64_t pol_w = policy_evict_first();
+    int tile = u_begin / KS, ks = u_begin - tile * KS;
+    int s = 0, ph = 1;
+    for (int it = 0; it < n_units; ++it) {
+      mbar_wait(bar(B_WE + s), ph);
+      if (elect_one()) {
+        mbar_arrive_expect_tx(bar(s), Cfg::W_STAGE_BYTES);
+        tma_2d_g2s_hint(w_base + s * Cfg::W_STAGE_BYTES, &tmap_w, tile * (Cfg::W_ROW_BYTES / 8), ks * kDecSlabs, bar(s), pol_w);
+      }
+      __syncwarp();
+      if (++s == NW) { s = 0; ph ^= 1; }
+      if (++ks == KS) { ks = 0; ++tile; }
+    }
+  } else if (warp == 1) {
+    // ================= activation (+ group scale row) producer =====================================================
+    const uint64_t pol_a = policy_evict_last();
+    constexpr uint32_t tx = Cfg::A_STAGE_BYTES + (GPS != 0 ? 256 : 0);
+    int tile = u_begin / KS, ks = u_begin - tile * KS;
+    int s = 0, ph = 1;
+    pdl_wait();
+    for (int it = 0; it < n_units; ++it) {
+      mbar_wait(bar(B_AE + s), ph);
+      if (elect_one()) {
+        mbar_arrive_expect_tx(bar(B_AF + s), tx);
+        tma_3d_g2s_hint(act_base + s * Cfg::A_STAGE_BYTES, &tmap_a, 0, 0, ks * 2, bar(B_AF + s), pol_a);
+        if (GPS != 0) tma_2d_g2s_hint(sc_base + s * Cfg::S_STAGE_BYTES, &tmap_s, tile * kTileN, ks, bar(B_AF + s), pol_a);
+      }
+      __syncwarp();
+      if (++s == NA) { s = 0; ph ^= 1; }
+      if (++ks == KS) { ks = 0; ++tile; }
+    }
+  } else if (warp == 2) {
+    // ================= TMEM allocator + MMA issuer ====================================================================
+    tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
+    const uint32_t tmem_base = get_tmem_base();
+    constexpr uint32_t idesc = make_idesc(1 /*F32*/, Pack2<T>::FMT, Pack2<T>::FMT, 128, MPAD);
+    int ks = u_begin % KS;
+    int sa = 0, pha = 0, slot = 0, phs = 0, ce = 0, phc = 0, seg = 0;
+    for (int it = 0; it < n_units; ++it) {
+      const bool first = (it == 0 || ks == 0);
+      const bool last = (it == n_units - 1 || ks == KS - 1);
+      const int ab = GPS == 1 ? (it & 1) : 0;
+      const uint32_t d_tmem = tmem_base + Cfg::ACC_COL0 + ab * MPAD;
+      mbar_wait(bar(B_AF + sa), pha);
+      mbar_wait(bar(B_CF + ce), phc);
+      if (GPS == 1) mbar_wait(bar(B_ACE + ab), ((it >> 1) & 1) ^ 1);      // the epilogue has read this buffer (2 stages ago)
+      else if (first && seg > 0) mbar_wait(bar(B_ACE), (seg - 1) & 1);
+      const uint32_t b_smem = act_base + sa * Cfg::A_STAGE_BYTES;
+#pragma unroll
+      for (int sub = 0; sub < 2; ++sub) {
+        mbar_wait(bar(B_SF + slot), phs);
+        tc_fence_after();
+        if (elect_one()) {
+#pragma unroll
+          for (int rr = 0; rr < 4; ++rr)
+            mma_f16_ts(d_tmem, tmem_base + Cfg::SLOT_COL0 + slot * 32 + rr * 8,
+                       make_kmajor_sw128_desc(b_smem + sub * Cfg::A_BOX_BYTES + rr * 32), idesc,
+                       ((GPS == 1 || first) && sub == 0 && rr == 0) ? 0u : 1u);
+          tc_commit(bar(B_SE + slot));
+          if (sub == 1) {
+            // zero-point correction of this stage: constant slab x activation-sum slab
+            mma_f16_ts(d_tmem, tmem_base + Cfg::CONST_COL,
+                       make_kmajor_sw128_desc(corr_base + (ce >> 2) * Cfg::A_BOX_BYTES + (ce & 3) * 32), idesc, 1u);
+            tc_commit(bar(B_AE + sa));
+            tc_commit(bar(B_CE + ce));
+            if (GPS == 1 || last) tc_commit(bar(B_ACF + ab));
+          }
+        }
+        __syncwarp();
+        if (++slot == NSLOT) { slot = 0; phs ^= 1; }
+      }
+      if (++sa == NA) { sa = 0; pha ^= 1; }
+      if (++ce == NC) { ce = 0; phc ^= 1; }
+      if (last) ++seg;
+      if (++ks == KS) ks = 0;
+    }
+  } else if (warp == 3) {
+    // ================= correction-slab builder: activation sums (global fp32) -> B operand slab ===================
+    (void)get_tmem_base();
+    int ks = u_begin % KS;
+    int ce = 0, phc = 1;
+    const int m_valid = args.M < MPAD ? args.M : MPAD;
+    pdl_wait();   // the sums are written by the kernel that produced the activations
+    for (int it = 0; it < n_units; ++it) {
+      float v[(MPAD + 31) / 32];
+#pragma unroll
+      for (int i = 0; i < (MPAD + 31) / 32; ++i) {
+        const int m = lane + 32 * i;
+        v[i] = (m < m_valid) ? __ldg(args.asum + (size_t)ks * args.asum_stride + m) * (1.f / 128.f) : 0.f;
+      }
+      mbar_wait(bar(B_CE + ce), phc);
+#pragma unroll
+      for (int i = 0; i < (MPAD + 31) / 32; ++i) {
+        const int m = lane + 32 * i;
+        if (m < MPAD) {
+          const T hi = from_f32<T>(v[i]);
+          const T lo = from_f32<T>(v[i] - to_f32<T>(hi));
+          const uint32_t h2 = (uint32_t)(*reinterpret_cast<const unsigned short*>(&hi)) * 0x00010001u;
+          const uint32_t l2 = (uint32_t)(*reinterpret_cast<const unsigned short*>(&lo)) * 0x00010001u;
+          uint8_t* rowp = smem_gen + (corr_base - smem_base) + (ce >> 2) * Cfg::A_BOX_BYTES + m * 128;
+          const int c0 = 2 * (ce & 3);
+          *reinterpret_cast<uint4*>(rowp + ((c0 ^ (m & 7)) << 4)) = make_uint4(h2, h2, h2, h2);          // k 0..7
+          *reinterpret_cast<uint4*>(rowp + (((c0 + 1) ^ (m & 7)) << 4)) = make_uint4(l2, l2, l2, l2);    // k 8..15
+        }
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(B_CF + ce));
+      if (++ce == NC) { ce = 0; phc ^= 1; }
+      if (++ks == KS) ks = 0;
+    }
+  } else {
+    // ================= dequant warps; they also scale / drain the accumulators =========================================
+    const uint32_t tmem_base = get_tmem_base();
+    const int qd = warp & 3;
+    const int p = (warp - kDecCtrlWarps) >> 2;
+    const int t64 = qd >> 1, jpair = qd & 1;
+    const uint32_t a_lane = tmem_base + ((uint32_t)(32 * qd) << 16);
+    const uint8_t* wsm = smem_gen + (w_base - smem_base) + t64 * (Cfg::W_ROW_BYTES / 2) + lane * 16 + jpair * 8;
+    const int row = 32 * qd + lane;
+    const int et = threadIdx.x - kDecCtrlWarps * 32;
+    constexpr int EW = Cfg::EW;
+    const int col0 = p * EW;
+    const int m_valid = args.M < MPAD ? args.M : MPAD;
+    const int sc_pos = 64 * (row >> 6) + 8 * (row & 7) + ((row & 63) >> 3);   // scale_perm: pos 8 c + b' <-> col c + 8 b'
+    const uint32_t shmul[3] = {args.shmul[0], args.shmul[1], args.shmul[2]};
+    bool waited = false;
+
+    if (p == 0) {
+      // constant A slab of the correction MMA: -(2^e + 8) * 16 at all 16 k positions of every lane
+      const T cv = from_f32<T>(-ZpcFmt<T>::BIAS * 16.f);
+      const uint32_t c2 = (uint32_t)(*reinterpret_cast<const unsigned short*>(&cv)) * 0x00010001u;
+      tmem_st_16x128b_x2(a_lane + Cfg::CONST_COL, c2, c2, c2, c2);
+      tmem_st_16x128b_x2(a_lane + ((uint32_t)16 << 16) + Cfg::CONST_COL, c2, c2, c2, c2);
+      // (made visible to the issuer by the wait::st / fence / arrive of this warp's first operand slot)
+    }
+
+    float facc[EW];
+#pragma unroll
+    for (int j = 0; j < EW; ++j) facc[j] = 0.f;
+
+    // group-128 epilogue of stage `jt` (its MMAs were committed a stage ago): facc += scale * D
+    auto epi_group = [&](int jt) {
+      const int ab = jt & 1, sj = jt % NA;
+      mbar_wait(bar(B_AF + sj), (jt / NA) & 1);      // (long complete: the scale row rode in with the activations)
+      mbar_wait(bar(B_ACF + ab), (jt >> 1) & 1);
+      tc_fence_after();
+      const float sc = to_f32<T>(*reinterpret_cast<const T*>(smem_gen + (sc_base - smem_base) + sj * Cfg::S_STAGE_BYTES + 2 * sc_pos));
+#pragma unroll
+      for (int c0 = 0; c0 < EW; c0 += 16) {
+        uint32_t t[16];
+        tmem_ld_32x32b_x16(a_lane + Cfg::ACC_COL0 + ab * MPAD + col0 + c0, t);
+        tc_wait_ld();
+        if (c0 + 16 == EW) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) { mbar_arrive(bar(B_ACE + ab)); mbar_arrive(bar(B_AE + sj)); }   // accumulator + scale row released
+        }
+#pragma unroll
+        for (int j = 0; j < 16; ++j) facc[c0 + j] = fmaf(sc, __uint_as_float(t[j]), facc[c0 + j]);
+      }
+    };
+
+    int tile = u_begin / KS, ks = u_begin - tile * KS;
+    int s = 0, phw = 0, seg = 0, it_seg0 = 0;
+    int slot = p % NSLOT, phs = 1;
+    for (int it = 0; it < n_units; ++it) {
+      const bool last = (it == n_units - 1 || ks == KS - 1);
+      mbar_wait(bar(s), phw);
+#pragma unroll
+      for (int sub = p; sub < 2; sub += DQW) {
+        uint32_t w[4][2];
+#pragma unroll
+        for (int rr = 0; rr < 4; ++rr) {
+          const uint2 v = *reinterpret_cast<const uint2*>(wsm + s * Cfg::W_STAGE_BYTES + (4 * sub + rr) * Cfg::W_ROW_BYTES);
+          w[rr][0] = v.x; w[rr][1] = v.y;
+        }
+        if (sub + DQW >= 2) {
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar(B_WE + s));
+        }
+        uint32_t ov[2][16];
+#pragma unroll
+        for (int rr = 0; rr < 4; ++rr) {
+          dequant4_biased<T>(w[rr][0], &ov[0][4 * rr], shmul);
+          dequant4_biased<T>(w[rr][1], &ov[1][4 * rr], shmul);
+        }
+        mbar_wait(bar(B_SE + slot), phs);
+        tc_fence_after();
+        tmem_st_16x128b_x8(a_lane + Cfg::SLOT_COL0 + slot * 32, ov[0]);
+        tmem_st_16x128b_x8(a_lane + ((uint32_t)16 << 16) + Cfg::SLOT_COL0 + slot * 32, ov[1]);
+        tc_wait_st();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(B_SF + slot));
+        slot += DQW;
+        if (slot >= NSLOT) { slot -= NSLOT; phs ^= 1; }
+      }
+      if (++s == NW) { s = 0; phw ^= 1; }
+      if (GPS == 1 && it > it_seg0) epi_group(it - 1);
+
+      if (last) {
+        // ---------- end of the segment [it_seg0, it] of `tile` ----------
+        const int len = it - it_seg0 + 1;
+        const bool full_k = (len == KS);
+        const int n = tile * kTileN + row;
+        const bool n_ok = n < args.N;
+        if (!waited) { pdl_wait(); waited = true; }
+        float ch_scale = 1.f;
+        if (GPS == 0) {
+          if (n_ok) ch_scale = to_f32<T>(reinterpret_cast<const T*>(args.scales)[(n & ~31) + scale_single_pos(n & 31)]);
+          mbar_wait(bar(B_ACF), seg & 1);
+          tc_fence_after();
+#pragma unroll
+          for (int c0 = 0; c0 < EW; c0 += 16) {
+            uint32_t t[16];
+            tmem_ld_32x32b_x16(a_lane + Cfg::ACC_COL0 + col0 + c0, t);
+            tc_wait_ld();
+            if (c0 + 16 == EW) {
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(bar(B_ACE));
+            }
+#pragma unroll
+            for (int j = 0; j < 16; ++j) facc[c0 + j] = __uint_as_float(t[j]);
+          }
+        } else {
+          epi_group(it);
+        }
+        T* cdst = reinterpret_cast<T*>(args.C) + n;
+        if (full_k) {
+          if (n_ok) {
+#pragma unroll
+            for (int j = 0; j < EW; ++j)
+              if (col0 + j < m_valid) cdst[(size_t)(col0 + j) * args.N] = from_f32<T>(facc[j] * ch_scale);
+          }
+        } else {
+          float* part_dst = args.scratch + ((size_t)(blockIdx.x * 2 + (it_seg0 == 0 ? 0 : 1)) * MPAD) * kTileN + row;
+#pragma unroll
+          for (int j = 0; j < EW; ++j)
+            if (col0 + j < m_valid) part_dst[(col0 + j) * kTileN] = facc[j];
+          const int u_t0 = tile * KS;
+          const int c_first = part.owner(u_t0), c_last = part.owner(u_t0 + KS - 1);
+          __threadfence();
+          asm volatile("bar.sync 1, %0;" ::"n"(Cfg::NDQ * 32) : "memory");
+          if (et == 0) *ticket_p = atomicAdd(&args.counters[tile], 1);
+          asm volatile("bar.sync 1, %0;" ::"n"(Cfg::NDQ * 32) : "memory");
+          if (*ticket_p == c_last - c_first) {
+            __threadfence();
+            const int first_bit = part.start(c_first) < u_t0 ? 1 : 0;
+#pragma unroll
+            for (int c0 = 0; c0 < EW; c0 += 16) {
+              float acc[16];
+#pragma unroll
+              for (int j = 0; j < 16; ++j) acc[j] = 0.f;
+              for (int cc = c_first; cc <= c_last; ++cc) {
+                const float* src = args.scratch + ((size_t)(cc * 2 + (cc == c_first ? first_bit : 0)) * MPAD) * kTileN + row;
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                  if (col0 + c0 + j < m_valid) acc[j] += __ldcg(src + (col0 + c0 + j) * kTileN);
+              }
+              if (n_ok) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                  if (col0 + c0 + j < m_valid) cdst[(size_t)(col0 + c0 + j) * args.N] = from_f32<T>(acc[j] * ch_scale);
+              }
+            }
+            if (et == 0) args.counters[tile] = 0;
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < EW; ++j) facc[j] = 0.f;
+        ++seg;
+        it_seg0 = it + 1;
+      }
+      if (++ks == KS) { ks = 0; ++tile; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<Cfg::TMEM_COLS>(*tmem_slot_p);
+}
+
+// per-(row, group of 128 k) sums of the activations, fp32 [K/128][stride]: one warp per (row, group)
+template <typename T>
+__global__ void act_group_sums_kernel(float* __restrict__ out, int stride, const T* __restrict__ a, int M, int G, int64_t lda) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (wid >= M * G) return;
+  const int m = wid / G, g = wid - m * G;
+  const uint2 v = *reinterpret_cast<const uint2*>(a + (size_t)m * lda + g * 128 + lane * 4);
+  const T* e = reinterpret_cast<const T*>(&v);
+  float s = (to_f32<T>(e[0]) + to_f32<T>(e[1])) + (to_f32<T>(e[2]) + to_f32<T>(e[3]));
+  s = warp_sum(s);
+  if (lane == 0) out[(size_t)g * stride + m] = s;
+}
+
 // ---- host side --------------------------------------------------------------------------------------------------
 template <typename T, int MPAD, int BITS, int GPS>
 int launch_decode(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t st) {
@@ -399,16 +827,20 @@ int launch_decode(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t
   static int occ[64] = {};
   if (occ[dev & 63] == 0) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     int n = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, Cfg::THREADS, Cfg::SMEM_BYTES) != cudaSuccess || n < 1)
       return set_error(B200_ECUDA, "marlin decode gemm: kernel does not fit on an SM (smem %d, threads %d)", Cfg::SMEM_BYTES, Cfg::THREADS);
     occ[dev & 63] = n < Cfg::OCC ? n : Cfg::OCC;
+    if (getenv("B200_DEC_VERBOSE"))
+      fprintf(stderr, "[dec1] MPAD=%d BITS=%d GPS=%d: occupancy %d (want %d), smem %d, threads %d\n", MPAD, BITS, GPS, n, Cfg::OCC,
+              Cfg::SMEM_BYTES, Cfg::THREADS);
   }
   // grid: below the number of resident slots, so that the next kernel of the stream finds a free slot on every SM while
   // this one is still running; at least `min_units` stages per CTA so that split-K partial traffic stays small
   static const int env_cps = getenv("B200_DEC_CTAS_PER_SM") ? atoi(getenv("B200_DEC_CTAS_PER_SM")) : 0;
   static const int env_minu = getenv("B200_DEC_MIN_UNITS") ? atoi(getenv("B200_DEC_MIN_UNITS")) : 0;
-  int cps = env_cps > 0 ? env_cps : (occ[dev & 63] > 1 ? occ[dev & 63] - 1 : 1);
+  int cps = env_cps > 0 ? env_cps : occ[dev & 63];
   const int min_units = env_minu > 0 ? env_minu : (MPAD >= 64 ? 4 : 2);
   int grid = num_sms() * cps;
   if (grid > kDecMaxGrid) grid = kDecMaxGrid;
@@ -449,10 +881,101 @@ int launch_decode(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t
   return B200_OK;
 }
 
+int dec_asum_scratch(int dev, cudaStream_t st, float** asum);   // marlin_gemm.cu: fp32 [kDecMaxGroups][64]
+constexpr int kDecMaxGroups = 8192;
+
+template <typename T, int MPAD, int GPS>
+int launch_decode2(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t st) {
+  using Cfg = Dec2Cfg<MPAD, GPS>;
+  GemmArgs a = a_in;
+  a.m_chunks = 1;
+  a.KS = a.K / kDecStageK;
+  a.total_units = a.n_tiles * a.KS;
+  auto kern = marlin_decode2_kernel<T, MPAD, GPS>;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  static int occ[64] = {};
+  if (occ[dev & 63] == 0) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    int n = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, Cfg::THREADS, Cfg::SMEM_BYTES) != cudaSuccess || n < 1)
+      return set_error(B200_ECUDA, "marlin decode gemm: kernel does not fit on an SM (smem %d, threads %d)", Cfg::SMEM_BYTES, Cfg::THREADS);
+    occ[dev & 63] = n < Cfg::OCC ? n : Cfg::OCC;
+    if (getenv("B200_DEC_VERBOSE"))
+      fprintf(stderr, "[dec2] MPAD=%d GPS=%d: occupancy %d (want %d), smem %d, threads %d, NW=%d NA=%d NSLOT=%d\n", MPAD, GPS, n,
+              Cfg::OCC, Cfg::SMEM_BYTES, Cfg::THREADS, Cfg::NW, Cfg::NA, Cfg::NSLOT);
+  }
+  static const int env_cps = getenv("B200_DEC_CTAS_PER_SM") ? atoi(getenv("B200_DEC_CTAS_PER_SM")) : 0;
+  static const int env_minu = getenv("B200_DEC_MIN_UNITS") ? atoi(getenv("B200_DEC_MIN_UNITS")) : 0;
+  const int cps = env_cps > 0 ? env_cps : occ[dev & 63];
+  const int min_units = env_minu > 0 ? env_minu : (MPAD >= 64 ? 4 : 2);
+  int grid = num_sms() * cps;
+  if (grid > kDecMaxGrid) grid = kDecMaxGrid;
+  if (grid > a.total_units / min_units) grid = a.total_units / min_units;
+  if (grid < 1) grid = 1;
+  if (int e = dec_scratch(dev, st, &a.scratch, &a.counters)) return e;
+  if (a.asum == nullptr) {
+    // the caller did not bring the activation group sums: one small kernel ahead of the GEMM computes them
+    float* asum = nullptr;
+    if (int e = dec_asum_scratch(dev, st, &asum)) return e;
+    const int G = a.K / 128;
+    const int warps = a.M * G;
+    cudaError_t e = launch_pdl(act_group_sums_kernel<T>, dim3((unsigned)((warps + 7) / 8)), dim3(256), 0, st, asum, 64,
+                               (const T*)A, a.M, G, lda);
+    if (e != cudaSuccess) return set_error(B200_ECUDA, "act_group_sums launch: %s", cudaGetErrorString(e));
+    a.asum = asum;
+    a.asum_stride = 64;
+  }
+  a.shmul[0] = 1u << 28; a.shmul[1] = 1u << 24; a.shmul[2] = 1u << 20;
+  CUtensorMap tmap_a, tmap_w, tmap_s;
+  const CUtensorMapDataType dt = std::is_same<T, __half>::value ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  bool ok = make_tmap_act3d(&tmap_a, A, dt, (uint64_t)a.M, (uint64_t)a.K, (uint64_t)lda * 2, MPAD, kDecStageK / 64);
+  const uint64_t wrow_bytes = (uint64_t)a.N * 8;
+  ok = ok && make_tmap_2d(&tmap_w, a.B, CU_TENSOR_MAP_DATA_TYPE_UINT64, 8, (uint64_t)a.K / 16, wrow_bytes / 8, wrow_bytes,
+                          kDecSlabs, Cfg::W_ROW_BYTES / 8, CU_TENSOR_MAP_SWIZZLE_NONE);
+  if (GPS != 0)
+    ok = ok && make_tmap_2d(&tmap_s, a.scales, dt, 2, (uint64_t)a.num_groups, (uint64_t)a.N, (uint64_t)a.N * 2, 1, kTileN,
+                            CU_TENSOR_MAP_SWIZZLE_NONE);
+  else
+    tmap_s = tmap_a;
+  if (!ok)
+    return set_error(B200_ECUDA, "marlin decode gemm: cuTensorMapEncodeTiled failed (A=%p M=%d K=%d N=%d lda=%lld)", A, a.M,
+                     a.K, a.N, (long long)lda);
+  a.prof = nullptr; a.trace = nullptr; a.trace_cta = 0; a.exp = 0; a.cluster_s = 0;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(Cfg::THREADS);
+  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  int na = 0;
+  if (pdl_enabled()) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = na;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmap_a, tmap_w, tmap_s, a);
+  if (e != cudaSuccess) return set_error(B200_ECUDA, "marlin decode gemm launch: %s", cudaGetErrorString(e));
+  return B200_OK;
+}
+
+template <typename T>
+int dispatch_decode2(const GemmArgs& a, const void* A, int64_t lda, cudaStream_t st) {
+  const bool g128 = a.num_groups > 1;
+  if (a.M <= 16) return g128 ? launch_decode2<T, 16, 1>(a, A, lda, st) : launch_decode2<T, 16, 0>(a, A, lda, st);
+  if (a.M <= 32) return g128 ? launch_decode2<T, 32, 1>(a, A, lda, st) : launch_decode2<T, 32, 0>(a, A, lda, st);
+  return g128 ? launch_decode2<T, 64, 1>(a, A, lda, st) : launch_decode2<T, 64, 0>(a, A, lda, st);
+}
+
 // M <= 64, no fused all-reduce.  gps_code: scale rows per 128-k stage (0 channelwise, 1, 2, 4)
 template <typename T, int BITS>
 int dispatch_decode(const GemmArgs& a, const void* A, int64_t lda, cudaStream_t st) {
   const int gps = a.num_groups > 1 ? kDecStageK / a.group_size : 0;
+  static const int force_v1 = getenv("B200_DEC_V1") ? atoi(getenv("B200_DEC_V1")) : 0;
+  if (BITS == 4 && gps <= 1 && !force_v1 && a.K / 128 <= kDecMaxGroups) return dispatch_decode2<T>(a, A, lda, st);
 #define B200_DEC_CASE(G)                                                        \
   if (gps == G) {                                                               \
     if (a.M <= 16) return launch_decode<T, 16, BITS, G>(a, A, lda, st);         \

@@ -27,6 +27,7 @@ struct DeviceScratch {
   int counter_ints = 0;
   float* dec_partials = nullptr;
   int* dec_counters = nullptr;
+  float* dec_asum = nullptr;
 };
 static DeviceScratch g_scratch[64];
 
@@ -107,6 +108,23 @@ static int ensure_a_tmp(int dev, size_t bytes, cudaStream_t st) {
   return B200_OK;
 }
 
+// decode kernel v2: activation group sums when the caller does not bring them
+int dec_asum_scratch(int dev, cudaStream_t st, float** asum) {
+  DeviceScratch& s = g_scratch[dev & 63];
+  if (!s.dec_asum) {
+    if (capturing(st))
+      return set_error(B200_EINVAL, "marlin decode gemm: scratch must exist before CUDA-graph capture (run one eager call or "
+                                    "b200_gemm_scratch_reserve first)");
+    if (cudaMalloc(&s.dec_asum, (size_t)kDecMaxGroups * 64 * sizeof(float)) != cudaSuccess) {
+      cudaGetLastError();
+      s.dec_asum = nullptr;
+      return set_error(B200_ECUDA, "marlin decode gemm: scratch allocation failed");
+    }
+  }
+  *asum = s.dec_asum;
+  return B200_OK;
+}
+
 }  // namespace b200
 
 extern "C" int b200_gemm_scratch_reserve(int64_t max_m, int64_t max_n) {
@@ -116,6 +134,7 @@ extern "C" int b200_gemm_scratch_reserve(int64_t max_m, int64_t max_n) {
   float* p;
   int* c;
   if (int e = dec_scratch(dev, 0, &p, &c)) return e;
+  if (int e = dec_asum_scratch(dev, 0, &p)) return e;
   // largest request of the three kernels for a [max_m, max_n] output: marlin (grid x 128 x MPAD), scaled_mm
   // (grid x 2 x 128 x MT), marlin24 split-K (n_tiles x m_chunks x splits x 64 x 64)
   const size_t m = (size_t)(max_m > 0 ? max_m : 1), n = (size_t)(max_n > 0 ? max_n : 1);
@@ -180,6 +199,7 @@ extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_
   ga.groups_per_stage = num_groups > 1 ? kStageK / gs : 0;
   ga.prof = nullptr; ga.trace = nullptr; ga.trace_cta = 0; ga.exp = 0;
   ga.cluster_s = 0;
+  ga.asum = nullptr; ga.asum_stride = 0;
   ga.ar.world = 0;
   {
     long long fm = 0, fn = 0;

@@ -113,6 +113,9 @@ struct GemmArgs {
   long long* trace;            // bring-up event trace of CTA trace_cta [11 roles][64][8]
   int trace_cta;
   ArFuse ar;                   // ar.world > 1: the epilogue all-reduces the output over the TP ranks (row-parallel layers)
+  const float* asum;           // decode kernel v2: per-(group of 128 k, row) activation sums, fp32 [K/128][asum_stride]
+  int asum_stride;
+  uint32_t shmul[3];           // decode kernel v2: 2^28, 2^24, 2^20 -- right shifts done as IMAD.HI on the FMA pipe
   int exp;                     // bring-up ablations (B200_GEMM_EXP, prof builds only): 1 no dequant ALU, 2 no MMAs, 3 no epilogue reads, 4 no TMEM stores
 };
 
