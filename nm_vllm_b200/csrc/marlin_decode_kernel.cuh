@@ -386,20 +386,22 @@ marlin_decode_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_co
 }
 
 // =====================================================================================================================
-// v2 (4-bit, group 128 or channelwise): zero point and group scale leave the dequant warps.
+// Fast path (4-bit, group 128 or channelwise): zero point and group scale leave the dequant warps.
 //
-// The ALU pipe (LOP3 / SHF, one warp instruction per 2 clocks per scheduler) is what bounds the expansion: 7 ALU + 8 FMA
-// pipe instructions per packed word above.  Here a packed word costs 4 LOP3 (ALU) + 3 right shifts issued as IMAD.HI
-// (FMA pipe) and nothing else:
-//   * the weights go into TMEM WITH their bias, w' = 2^e + nibble (bf16: 128 + n, fp16: 1024 + n, both exact); the
-//     missing  -(2^e + 8) * sum_k a[m,k]  is added by ONE extra tcgen05.mma per 128-k stage whose A operand is a constant
-//     slab in TMEM and whose B operand holds the per-(row, group) activation sums (split hi + lo so that the 16-bit
-//     operand carries ~16 bits of the sum; spread over the 16 k positions so that fp16 cannot overflow).  The sums come
-//     from the kernel that produced the activations (or from act_group_sums_kernel): fp32 [K/128][stride];
-//   * at group 128 a stage is exactly one quantisation group: every stage gets a fresh accumulator (two, ping-pong) and
-//     the dequant warps -- which own the TMEM lane quarters -- read it back one stage later and apply the group scale
-//     in fp32: acc[m] += s[g, n] * D_g[n, m].  Channelwise keeps one accumulator per tile segment.
-// Everything else (rings, stream-K partition, last-arriver reduction) is the machine above.
+// Measured on the machine above (tools/dec_trace.py, one CTA per SM): a dequant warp needs ~2100 clk per 128-k stage, of
+// which ~560 are mbarrier waits that were already satisfied (~90-190 clk each), ~220 the two tcgen05.st + wait::st round
+// trips, ~760 the expansion of 16 packed words (latency-bound: one warp per scheduler) -- per-warp latency, not any
+// pipe, is the limit, so the cure is fewer hand-offs per byte, fewer instructions per word and more warps in flight:
+//   * hand-offs are per 128-k STAGE (one 64-column TMEM slot), not per 64-k sub-slot, and there are two dequant warps
+//     per TMEM lane quarter that take alternate stages: 8 dequant warps per CTA, 2 CTAs per SM;
+//   * the weights go into TMEM WITH their bias, w' = 2^e + nibble (bf16: 128 + n, fp16: 1024 + n, both exact): a packed
+//     word costs 4 LOP3 + 3 shifts (issued as IMAD.HI on the FMA pipe) and nothing else.  The missing
+//     -(2^e + 8) * sum_k a[m,k] comes back in the epilogue from per-(row, group) activation sums, fp32
+//     [K/128][stride], written by the kernel that produced the activations (or by act_group_sums_kernel);
+//   * a stage is exactly one quantisation group at g128: every stage gets a fresh accumulator (two, ping-pong) and all
+//     dequant warps -- they own the TMEM lane quarters -- read it back one stage later, each its half of the
+//     columns, and apply scale and correction in fp32:  acc[m] += s[g,n] * (D_g[n,m] - bias * asum[g,m]).
+// Rings, stream-K partition and last-arriver reduction are the machine above.
 template <typename T> struct ZpcFmt;
 template <> struct ZpcFmt<__nv_bfloat16> { static constexpr uint32_t EX = 0x43004300u; static constexpr float BIAS = 136.f; };
 template <> struct ZpcFmt<__half> { static constexpr uint32_t EX = 0x64006400u; static constexpr float BIAS = 1032.f; };
@@ -420,60 +422,58 @@ __device__ __forceinline__ void dequant4_biased(uint32_t q, uint32_t* o, const u
   asm("lop3.b32 %0, %1, %2, %3, 0xea;" : "=r"(o[3]) : "r"(q12), "n"(MASK), "n"(EX));   // p3,p7
 }
 
-constexpr int kDecNC = 8;   // correction-slab ring: 8 stages = two 64-k boxes of four k16 slabs
+__device__ __forceinline__ void tmem_ld_32x32b_x8(uint32_t taddr, uint32_t (&r)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr)
+               : "memory");
+}
 
-#ifndef B200_DEC2_DQW16
-#define B200_DEC2_DQW16 1
+#ifdef B200_DEC_TRACE
+#define DTRACE(role, it, ev) if (args.trace && (int)blockIdx.x == args.trace_cta && lane == 0 && (it) < 32) { args.trace[((role) * 32 + (it)) * 16 + (ev)] = clock64(); }
+#else
+#define DTRACE(role, it, ev)
 #endif
 
-template <int MPAD, int GPS>
-struct Dec2Cfg {
-  static constexpr int DQW = MPAD <= 16 ? B200_DEC2_DQW16 : 2;
-  static constexpr int NDQ = 4 * DQW;
+template <int MPAD>
+struct Dec3Cfg {
+  static constexpr int NDQ = 8;                                              // dequant warps: 2 per TMEM lane quarter
   static constexpr int THREADS = 32 * (kDecCtrlWarps + NDQ);
-  static constexpr int EW = MPAD / DQW;
-  static constexpr int NACC = GPS == 1 ? 2 : 1;
-  static constexpr int TMEM_COLS = (MPAD <= 16 && DQW == 1) ? 128 : 256;
-  static constexpr int OCC = 512 / TMEM_COLS >= 3 ? 3 : 2;
-  // TMEM: [64-k operand slots][accumulators][constant slab of the correction MMA, 8 columns]
-  static constexpr int SLOT_COL0 = 0;
-  static constexpr int NSLOT = (TMEM_COLS - 8 - NACC * MPAD) / 32 > 4 ? 4 : (TMEM_COLS - 8 - NACC * MPAD) / 32;
-  static constexpr int ACC_COL0 = SLOT_COL0 + NSLOT * 32;
-  static constexpr int CONST_COL = ACC_COL0 + NACC * MPAD;
+  static constexpr int EW = MPAD / 2;                                        // accumulator columns per epilogue thread
+  static constexpr int EC = EW < 16 ? EW : 16;                               // columns per TMEM read
+  static constexpr int TMEM_COLS = 256;                                      // [2 x 64-column operand slots][2 x MPAD accumulators]
+  static constexpr int OCC = 2;
+  static constexpr int ACC_COL0 = 128;
   static constexpr int W_ROW_BYTES = kTileN * 16 * 4 / 8;
   static constexpr int W_STAGE_BYTES = kDecSlabs * W_ROW_BYTES;              // 8 KB
   static constexpr int A_BOX_BYTES = MPAD * 128;
   static constexpr int A_STAGE_BYTES = 2 * A_BOX_BYTES;
-  static constexpr int S_STAGE_BYTES = 256;                                  // one 128-column scale row
-  static constexpr int C_BYTES = 2 * A_BOX_BYTES;                            // correction ring
+  static constexpr int X_STAGE_BYTES = 512;                                  // [scale row 256 B][activation sums MPAD x 4 B]
   static constexpr int NA = MPAD <= 32 ? 4 : 3;
   static constexpr int BUDGET = (227 * 1024) / OCC - 1024 - 1024 - 512;
-  static constexpr int NW_RAW = (BUDGET - NA * (A_STAGE_BYTES + S_STAGE_BYTES) - C_BYTES) / W_STAGE_BYTES;
-  static constexpr int NW = NW_RAW > 8 ? 8 : NW_RAW;
-  static constexpr int NBARS = 2 * NW + 2 * NA + 2 * NSLOT + 4 + 2 * kDecNC;
-  static constexpr int SMEM_BYTES = 1024 + NA * (A_STAGE_BYTES + S_STAGE_BYTES) + C_BYTES + NW * W_STAGE_BYTES + NBARS * 8 + 16;
-  static_assert(NSLOT >= 2, "TMEM operand ring");
-  static_assert(NW >= 2, "weight ring");
+  static constexpr int NW_RAW = (BUDGET - NA * (A_STAGE_BYTES + X_STAGE_BYTES)) / W_STAGE_BYTES;
+  static constexpr int NW = NW_RAW > 10 ? 10 : NW_RAW;
+  static constexpr int NBARS = 2 * NW + 2 * NA + 8;
+  static constexpr int SMEM_BYTES = 1024 + NA * (A_STAGE_BYTES + X_STAGE_BYTES) + NW * W_STAGE_BYTES + NBARS * 8 + 16;
+  static_assert(NW >= 3, "weight ring");
   static_assert(NBARS * 8 + 16 <= 512, "barrier area");
-  static_assert(EW % 16 == 0, "epilogue reads 16 columns at a time");
+  static_assert(ACC_COL0 + 2 * MPAD <= TMEM_COLS, "TMEM budget");
 };
 
 template <typename T, int MPAD, int GPS>   // GPS: 0 channelwise, 1 group 128
-__global__ void __launch_bounds__(Dec2Cfg<MPAD, GPS>::THREADS, Dec2Cfg<MPAD, GPS>::OCC)
-marlin_decode2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
+__global__ void __launch_bounds__(Dec3Cfg<MPAD>::THREADS, Dec3Cfg<MPAD>::OCC)
+marlin_decode3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
                       const __grid_constant__ CUtensorMap tmap_s, const GemmArgs args) {
-  using Cfg = Dec2Cfg<MPAD, GPS>;
-  constexpr int NW = Cfg::NW, NA = Cfg::NA, NSLOT = Cfg::NSLOT, DQW = Cfg::DQW, NACC = Cfg::NACC, NC = kDecNC;
+  using Cfg = Dec3Cfg<MPAD>;
+  constexpr int NW = Cfg::NW, NA = Cfg::NA;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  // layout: [activation stages] [correction boxes] (1024-aligned) [weight stages] [scale rows] [barriers]
+  // layout: [activation stages (1024-aligned)] [weight stages] [scale row + activation sums per stage] [barriers]
   const uint32_t act_base = smem_base;
-  const uint32_t corr_base = act_base + NA * Cfg::A_STAGE_BYTES;
-  const uint32_t w_base = corr_base + Cfg::C_BYTES;
-  const uint32_t sc_base = w_base + NW * Cfg::W_STAGE_BYTES;
-  const uint32_t bar_base = sc_base + NA * Cfg::S_STAGE_BYTES;
-  constexpr int B_WE = NW, B_AF = 2 * NW, B_AE = B_AF + NA, B_SF = B_AE + NA, B_SE = B_SF + NSLOT, B_CF = B_SE + NSLOT,
-                B_CE = B_CF + NC, B_ACF = B_CE + NC, B_ACE = B_ACF + 2;
+  const uint32_t w_base = act_base + NA * Cfg::A_STAGE_BYTES;
+  const uint32_t x_base = w_base + NW * Cfg::W_STAGE_BYTES;
+  const uint32_t bar_base = x_base + NA * Cfg::X_STAGE_BYTES;
+  constexpr int B_WE = NW, B_AF = 2 * NW, B_AE = B_AF + NA, B_SF = B_AE + NA, B_SE = B_SF + 2, B_ACF = B_SE + 2, B_ACE = B_ACF + 2;
   auto bar = [&](int i) { return bar_base + 8u * i; };
   const uint32_t tmem_slot = bar_base + 8u * Cfg::NBARS;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
@@ -488,9 +488,9 @@ marlin_decode2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
   }
   if (threadIdx.x >= 32 && threadIdx.x < 32 + Cfg::NBARS) {
     const int i = threadIdx.x - 32;
-    uint32_t cnt = 1;                                            // wfull, actfull, slotempty, corrfull/empty, accfull
-    if (i >= B_WE && i < B_AF) cnt = Cfg::NDQ;                   // wempty: every dequant warp
-    else if (i >= B_AE && i < B_SF) cnt = 1 + (GPS != 0 ? Cfg::NDQ : 0);   // actempty: issuer commit (+ scale readers)
+    uint32_t cnt = 1;                                            // wfull, actfull, slotempty, accfull
+    if (i >= B_WE && i < B_AF) cnt = 4;                          // wempty: the four lane-quarter warps that own the stage
+    else if (i >= B_AE && i < B_SF) cnt = 1 + Cfg::NDQ;          // actempty: issuer commit + every epilogue warp (scale, sums)
     else if (i >= B_SF && i < B_SE) cnt = 4;                     // slotfull: the four lane-quarter warps
     else if (i >= B_ACE) cnt = Cfg::NDQ;                         // accempty: every epilogue warp
     mbar_init(bar(i), cnt);
@@ -528,221 +528,168 @@ marlin_decode2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
       if (++ks == KS) { ks = 0; ++tile; }
     }
   } else if (warp == 1) {
-    // ================= activation (+ group scale row) producer =====================================================
+    // ================= activations + group scale row + activation sums =============================================
     const uint64_t pol_a = policy_evict_last();
-    constexpr uint32_t tx = Cfg::A_STAGE_BYTES + (GPS != 0 ? 256 : 0);
+    constexpr uint32_t tx = Cfg::A_STAGE_BYTES + (GPS != 0 ? 256 : 0) + MPAD * 4;
     int tile = u_begin / KS, ks = u_begin - tile * KS;
     int s = 0, ph = 1;
-    pdl_wait();
+    pdl_wait();   // activations and their sums come from the previous kernels of the stream
     for (int it = 0; it < n_units; ++it) {
       mbar_wait(bar(B_AE + s), ph);
       if (elect_one()) {
         mbar_arrive_expect_tx(bar(B_AF + s), tx);
         tma_3d_g2s_hint(act_base + s * Cfg::A_STAGE_BYTES, &tmap_a, 0, 0, ks * 2, bar(B_AF + s), pol_a);
-        if (GPS != 0) tma_2d_g2s_hint(sc_base + s * Cfg::S_STAGE_BYTES, &tmap_s, tile * kTileN, ks, bar(B_AF + s), pol_a);
+        if (GPS != 0) tma_2d_g2s_hint(x_base + s * Cfg::X_STAGE_BYTES, &tmap_s, tile * kTileN, ks, bar(B_AF + s), pol_a);
+        bulk_g2s(x_base + s * Cfg::X_STAGE_BYTES + 256, args.asum + (size_t)ks * args.asum_stride, MPAD * 4, bar(B_AF + s));
       }
       __syncwarp();
       if (++s == NA) { s = 0; ph ^= 1; }
       if (++ks == KS) { ks = 0; ++tile; }
     }
   } else if (warp == 2) {
-    // ================= TMEM allocator + MMA issuer ====================================================================
+    // ================= TMEM allocator + MMA issuer: stage `it` -> operand slot it & 1 -> accumulator it & 1 ============
     tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
     const uint32_t tmem_base = get_tmem_base();
     constexpr uint32_t idesc = make_idesc(1 /*F32*/, Pack2<T>::FMT, Pack2<T>::FMT, 128, MPAD);
-    int ks = u_begin % KS;
-    int sa = 0, pha = 0, slot = 0, phs = 0, ce = 0, phc = 0, seg = 0;
+    int sa = 0, pha = 0;
     for (int it = 0; it < n_units; ++it) {
-      const bool first = (it == 0 || ks == 0);
-      const bool last = (it == n_units - 1 || ks == KS - 1);
-      const int ab = GPS == 1 ? (it & 1) : 0;
-      const uint32_t d_tmem = tmem_base + Cfg::ACC_COL0 + ab * MPAD;
+      const int b = it & 1, phb = (it >> 1) & 1;
+      const uint32_t d_tmem = tmem_base + Cfg::ACC_COL0 + b * MPAD;
+      DTRACE(1, it, 0);
       mbar_wait(bar(B_AF + sa), pha);
-      mbar_wait(bar(B_CF + ce), phc);
-      if (GPS == 1) mbar_wait(bar(B_ACE + ab), ((it >> 1) & 1) ^ 1);      // the epilogue has read this buffer (2 stages ago)
-      else if (first && seg > 0) mbar_wait(bar(B_ACE), (seg - 1) & 1);
-      const uint32_t b_smem = act_base + sa * Cfg::A_STAGE_BYTES;
+      DTRACE(1, it, 1);
+      mbar_wait(bar(B_ACE + b), phb ^ 1);      // the epilogue has read this accumulator (two stages ago)
+      DTRACE(1, it, 2);
+      mbar_wait(bar(B_SF + b), phb);
+      DTRACE(1, it, 3);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t b_smem = act_base + sa * Cfg::A_STAGE_BYTES;
 #pragma unroll
-      for (int sub = 0; sub < 2; ++sub) {
-        mbar_wait(bar(B_SF + slot), phs);
-        tc_fence_after();
-        if (elect_one()) {
-#pragma unroll
-          for (int rr = 0; rr < 4; ++rr)
-            mma_f16_ts(d_tmem, tmem_base + Cfg::SLOT_COL0 + slot * 32 + rr * 8,
-                       make_kmajor_sw128_desc(b_smem + sub * Cfg::A_BOX_BYTES + rr * 32), idesc,
-                       ((GPS == 1 || first) && sub == 0 && rr == 0) ? 0u : 1u);
-          tc_commit(bar(B_SE + slot));
-          if (sub == 1) {
-            // zero-point correction of this stage: constant slab x activation-sum slab
-            mma_f16_ts(d_tmem, tmem_base + Cfg::CONST_COL,
-                       make_kmajor_sw128_desc(corr_base + (ce >> 2) * Cfg::A_BOX_BYTES + (ce & 3) * 32), idesc, 1u);
-            tc_commit(bar(B_AE + sa));
-            tc_commit(bar(B_CE + ce));
-            if (GPS == 1 || last) tc_commit(bar(B_ACF + ab));
-          }
-        }
-        __syncwarp();
-        if (++slot == NSLOT) { slot = 0; phs ^= 1; }
+        for (int r = 0; r < 8; ++r)
+          mma_f16_ts(d_tmem, tmem_base + b * 64 + r * 8,
+                     make_kmajor_sw128_desc(b_smem + (r >> 2) * Cfg::A_BOX_BYTES + (r & 3) * 32), idesc, r == 0 ? 0u : 1u);
+        tc_commit(bar(B_SE + b));
+        tc_commit(bar(B_AE + sa));
+        tc_commit(bar(B_ACF + b));
       }
+      __syncwarp();
+      DTRACE(1, it, 4);
       if (++sa == NA) { sa = 0; pha ^= 1; }
-      if (++ce == NC) { ce = 0; phc ^= 1; }
-      if (last) ++seg;
-      if (++ks == KS) ks = 0;
     }
   } else if (warp == 3) {
-    // ================= correction-slab builder: activation sums (global fp32) -> B operand slab ===================
     (void)get_tmem_base();
-    int ks = u_begin % KS;
-    int ce = 0, phc = 1;
-    const int m_valid = args.M < MPAD ? args.M : MPAD;
-    pdl_wait();   // the sums are written by the kernel that produced the activations
-    for (int it = 0; it < n_units; ++it) {
-      float v[(MPAD + 31) / 32];
-#pragma unroll
-      for (int i = 0; i < (MPAD + 31) / 32; ++i) {
-        const int m = lane + 32 * i;
-        v[i] = (m < m_valid) ? __ldg(args.asum + (size_t)ks * args.asum_stride + m) * (1.f / 128.f) : 0.f;
-      }
-      mbar_wait(bar(B_CE + ce), phc);
-#pragma unroll
-      for (int i = 0; i < (MPAD + 31) / 32; ++i) {
-        const int m = lane + 32 * i;
-        if (m < MPAD) {
-          const T hi = from_f32<T>(v[i]);
-          const T lo = from_f32<T>(v[i] - to_f32<T>(hi));
-          const uint32_t h2 = (uint32_t)(*reinterpret_cast<const unsigned short*>(&hi)) * 0x00010001u;
-          const uint32_t l2 = (uint32_t)(*reinterpret_cast<const unsigned short*>(&lo)) * 0x00010001u;
-          uint8_t* rowp = smem_gen + (corr_base - smem_base) + (ce >> 2) * Cfg::A_BOX_BYTES + m * 128;
-          const int c0 = 2 * (ce & 3);
-          *reinterpret_cast<uint4*>(rowp + ((c0 ^ (m & 7)) << 4)) = make_uint4(h2, h2, h2, h2);          // k 0..7
-          *reinterpret_cast<uint4*>(rowp + (((c0 + 1) ^ (m & 7)) << 4)) = make_uint4(l2, l2, l2, l2);    // k 8..15
-        }
-      }
-      fence_proxy_async_smem();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar(B_CF + ce));
-      if (++ce == NC) { ce = 0; phc ^= 1; }
-      if (++ks == KS) ks = 0;
-    }
   } else {
-    // ================= dequant warps; they also scale / drain the accumulators =========================================
+    // ================= dequant warps; they also scale / correct / drain the accumulators ================================
     const uint32_t tmem_base = get_tmem_base();
-    const int qd = warp & 3;
-    const int p = (warp - kDecCtrlWarps) >> 2;
+    const int qd = warp & 3;                        // TMEM lane quarter: channels 32 qd .. 32 qd + 31 of the tile
+    const int p = (warp - kDecCtrlWarps) >> 2;      // dequantises the stages with (it & 1) == p; epilogue columns p * EW ..
     const int t64 = qd >> 1, jpair = qd & 1;
     const uint32_t a_lane = tmem_base + ((uint32_t)(32 * qd) << 16);
     const uint8_t* wsm = smem_gen + (w_base - smem_base) + t64 * (Cfg::W_ROW_BYTES / 2) + lane * 16 + jpair * 8;
+    const uint8_t* xsm = smem_gen + (x_base - smem_base);
     const int row = 32 * qd + lane;
     const int et = threadIdx.x - kDecCtrlWarps * 32;
-    constexpr int EW = Cfg::EW;
+    constexpr int EW = Cfg::EW, EC = Cfg::EC;
     const int col0 = p * EW;
     const int m_valid = args.M < MPAD ? args.M : MPAD;
     const int sc_pos = 64 * (row >> 6) + 8 * (row & 7) + ((row & 63) >> 3);   // scale_perm: pos 8 c + b' <-> col c + 8 b'
     const uint32_t shmul[3] = {args.shmul[0], args.shmul[1], args.shmul[2]};
     bool waited = false;
 
-    if (p == 0) {
-      // constant A slab of the correction MMA: -(2^e + 8) * 16 at all 16 k positions of every lane
-      const T cv = from_f32<T>(-ZpcFmt<T>::BIAS * 16.f);
-      const uint32_t c2 = (uint32_t)(*reinterpret_cast<const unsigned short*>(&cv)) * 0x00010001u;
-      tmem_st_16x128b_x2(a_lane + Cfg::CONST_COL, c2, c2, c2, c2);
-      tmem_st_16x128b_x2(a_lane + ((uint32_t)16 << 16) + Cfg::CONST_COL, c2, c2, c2, c2);
-      // (made visible to the issuer by the wait::st / fence / arrive of this warp's first operand slot)
-    }
-
     float facc[EW];
 #pragma unroll
     for (int j = 0; j < EW; ++j) facc[j] = 0.f;
 
-    // group-128 epilogue of stage `jt` (its MMAs were committed a stage ago): facc += scale * D
-    auto epi_group = [&](int jt) {
-      const int ab = jt & 1, sj = jt % NA;
-      mbar_wait(bar(B_AF + sj), (jt / NA) & 1);      // (long complete: the scale row rode in with the activations)
-      mbar_wait(bar(B_ACF + ab), (jt >> 1) & 1);
+    // epilogue of stage jt (one quantisation group): facc += scale * (D - bias * asum); releases accumulator and stage
+    auto epi = [&](int jt) {
+      const int b = jt & 1, sj = jt % NA;
+      if (p == 0 && qd == 0) DTRACE(0, jt, 8);
+      mbar_wait(bar(B_ACF + b), (jt >> 1) & 1);
+      if (p == 0 && qd == 0) DTRACE(0, jt, 9);
       tc_fence_after();
-      const float sc = to_f32<T>(*reinterpret_cast<const T*>(smem_gen + (sc_base - smem_base) + sj * Cfg::S_STAGE_BYTES + 2 * sc_pos));
+      const uint8_t* x = xsm + sj * Cfg::X_STAGE_BYTES;
+      float sc = 1.f;
+      if (GPS != 0) sc = to_f32<T>(*reinterpret_cast<const T*>(x + 2 * sc_pos));
 #pragma unroll
-      for (int c0 = 0; c0 < EW; c0 += 16) {
-        uint32_t t[16];
-        tmem_ld_32x32b_x16(a_lane + Cfg::ACC_COL0 + ab * MPAD + col0 + c0, t);
+      for (int c0 = 0; c0 < EW; c0 += EC) {
+        uint32_t t[EC];
+        if constexpr (EC == 16) tmem_ld_32x32b_x16(a_lane + Cfg::ACC_COL0 + b * MPAD + col0 + c0, t);
+        else tmem_ld_32x32b_x8(a_lane + Cfg::ACC_COL0 + b * MPAD + col0 + c0, t);
+        float as[EC];
+#pragma unroll
+        for (int j = 0; j < EC; j += 4) {
+          const float4 v = *reinterpret_cast<const float4*>(x + 256 + (col0 + c0 + j) * 4);
+          as[j] = v.x; as[j + 1] = v.y; as[j + 2] = v.z; as[j + 3] = v.w;
+        }
         tc_wait_ld();
-        if (c0 + 16 == EW) {
+        if (c0 + EC == EW) {
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) { mbar_arrive(bar(B_ACE + ab)); mbar_arrive(bar(B_AE + sj)); }   // accumulator + scale row released
+          if (lane == 0) { mbar_arrive(bar(B_ACE + b)); mbar_arrive(bar(B_AE + sj)); }   // accumulator, scale row and sums released
         }
 #pragma unroll
-        for (int j = 0; j < 16; ++j) facc[c0 + j] = fmaf(sc, __uint_as_float(t[j]), facc[c0 + j]);
+        for (int j = 0; j < EC; ++j)
+          facc[c0 + j] = fmaf(sc, fmaf(-ZpcFmt<T>::BIAS, as[j], __uint_as_float(t[j])), facc[c0 + j]);
       }
+      if (p == 0 && qd == 0) DTRACE(0, jt, 10);
     };
 
     int tile = u_begin / KS, ks = u_begin - tile * KS;
-    int s = 0, phw = 0, seg = 0, it_seg0 = 0;
-    int slot = p % NSLOT, phs = 1;
+    int s = 0, phw = 0, it_seg0 = 0;
     for (int it = 0; it < n_units; ++it) {
       const bool last = (it == n_units - 1 || ks == KS - 1);
-      mbar_wait(bar(s), phw);
+      if ((it & 1) == p) {
+        if (qd == 0) DTRACE(0, it, 0);
+        mbar_wait(bar(s), phw);
+        if (qd == 0) DTRACE(0, it, 1);
 #pragma unroll
-      for (int sub = p; sub < 2; sub += DQW) {
-        uint32_t w[4][2];
+        for (int half = 0; half < 2; ++half) {
+          uint32_t w[4][2];
 #pragma unroll
-        for (int rr = 0; rr < 4; ++rr) {
-          const uint2 v = *reinterpret_cast<const uint2*>(wsm + s * Cfg::W_STAGE_BYTES + (4 * sub + rr) * Cfg::W_ROW_BYTES);
-          w[rr][0] = v.x; w[rr][1] = v.y;
-        }
-        if (sub + DQW >= 2) {
-          __syncwarp();
-          if (lane == 0) mbar_arrive(bar(B_WE + s));
-        }
-        uint32_t ov[2][16];
+          for (int rr = 0; rr < 4; ++rr) {
+            const uint2 v = *reinterpret_cast<const uint2*>(wsm + s * Cfg::W_STAGE_BYTES + (4 * half + rr) * Cfg::W_ROW_BYTES);
+            w[rr][0] = v.x; w[rr][1] = v.y;
+          }
+          if (half == 1) {
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(B_WE + s));   // packed words are in registers: stage back to the producer
+          }
 #pragma unroll
-        for (int rr = 0; rr < 4; ++rr) {
-          dequant4_biased<T>(w[rr][0], &ov[0][4 * rr], shmul);
-          dequant4_biased<T>(w[rr][1], &ov[1][4 * rr], shmul);
+          for (int jj = 0; jj < 2; ++jj) {
+            uint32_t ov[16];
+#pragma unroll
+            for (int rr = 0; rr < 4; ++rr) dequant4_biased<T>(w[rr][jj], &ov[4 * rr], shmul);
+            if (half == 0 && jj == 0) {
+              if (qd == 0) DTRACE(0, it, 2);
+              mbar_wait(bar(B_SE + p), ((it >> 1) & 1) ^ 1);   // the MMAs of stage it - 2 have read this slot
+              if (qd == 0) DTRACE(0, it, 3);
+              tc_fence_after();
+            }
+            tmem_st_16x128b_x8(a_lane + ((uint32_t)(16 * jj) << 16) + p * 64 + half * 32, ov);
+          }
         }
-        mbar_wait(bar(B_SE + slot), phs);
-        tc_fence_after();
-        tmem_st_16x128b_x8(a_lane + Cfg::SLOT_COL0 + slot * 32, ov[0]);
-        tmem_st_16x128b_x8(a_lane + ((uint32_t)16 << 16) + Cfg::SLOT_COL0 + slot * 32, ov[1]);
+        if (qd == 0) DTRACE(0, it, 4);
         tc_wait_st();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(bar(B_SF + slot));
-        slot += DQW;
-        if (slot >= NSLOT) { slot -= NSLOT; phs ^= 1; }
+        if (lane == 0) mbar_arrive(bar(B_SF + p));
+        if (qd == 0) DTRACE(0, it, 5);
       }
       if (++s == NW) { s = 0; phw ^= 1; }
-      if (GPS == 1 && it > it_seg0) epi_group(it - 1);
+      if (it > it_seg0) epi(it - 1);
 
       if (last) {
         // ---------- end of the segment [it_seg0, it] of `tile` ----------
+        epi(it);
         const int len = it - it_seg0 + 1;
         const bool full_k = (len == KS);
         const int n = tile * kTileN + row;
         const bool n_ok = n < args.N;
-        if (!waited) { pdl_wait(); waited = true; }
+        if (!waited) { pdl_wait(); waited = true; }   // C, partial slots, counters may still be in use by the previous kernel
         float ch_scale = 1.f;
-        if (GPS == 0) {
-          if (n_ok) ch_scale = to_f32<T>(reinterpret_cast<const T*>(args.scales)[(n & ~31) + scale_single_pos(n & 31)]);
-          mbar_wait(bar(B_ACF), seg & 1);
-          tc_fence_after();
-#pragma unroll
-          for (int c0 = 0; c0 < EW; c0 += 16) {
-            uint32_t t[16];
-            tmem_ld_32x32b_x16(a_lane + Cfg::ACC_COL0 + col0 + c0, t);
-            tc_wait_ld();
-            if (c0 + 16 == EW) {
-              tc_fence_before();
-              __syncwarp();
-              if (lane == 0) mbar_arrive(bar(B_ACE));
-            }
-#pragma unroll
-            for (int j = 0; j < 16; ++j) facc[c0 + j] = __uint_as_float(t[j]);
-          }
-        } else {
-          epi_group(it);
-        }
+        if (GPS == 0 && n_ok)
+          ch_scale = to_f32<T>(reinterpret_cast<const T*>(args.scales)[(n & ~31) + scale_single_pos(n & 31)]);
         T* cdst = reinterpret_cast<T*>(args.C) + n;
         if (full_k) {
           if (n_ok) {
@@ -751,6 +698,8 @@ marlin_decode2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
               if (col0 + j < m_valid) cdst[(size_t)(col0 + j) * args.N] = from_f32<T>(facc[j] * ch_scale);
           }
         } else {
+          // last-arriver reduction: publish the partial, take a ticket; whoever holds the last one sums every piece of
+          // the tile in CTA order (its own included, re-read from the slot: same value, fixed order -> deterministic)
           float* part_dst = args.scratch + ((size_t)(blockIdx.x * 2 + (it_seg0 == 0 ? 0 : 1)) * MPAD) * kTileN + row;
 #pragma unroll
           for (int j = 0; j < EW; ++j)
@@ -763,30 +712,28 @@ marlin_decode2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_c
           asm volatile("bar.sync 1, %0;" ::"n"(Cfg::NDQ * 32) : "memory");
           if (*ticket_p == c_last - c_first) {
             __threadfence();
+            // slot of CTA cc's piece: its first segment (slot 0) unless cc is the CTA in which the tile begins and that
+            // CTA's range started in an earlier tile
             const int first_bit = part.start(c_first) < u_t0 ? 1 : 0;
+            float acc[EW];
 #pragma unroll
-            for (int c0 = 0; c0 < EW; c0 += 16) {
-              float acc[16];
+            for (int j = 0; j < EW; ++j) acc[j] = 0.f;
+            for (int cc = c_first; cc <= c_last; ++cc) {
+              const float* src = args.scratch + ((size_t)(cc * 2 + (cc == c_first ? first_bit : 0)) * MPAD) * kTileN + row;
 #pragma unroll
-              for (int j = 0; j < 16; ++j) acc[j] = 0.f;
-              for (int cc = c_first; cc <= c_last; ++cc) {
-                const float* src = args.scratch + ((size_t)(cc * 2 + (cc == c_first ? first_bit : 0)) * MPAD) * kTileN + row;
-#pragma unroll
-                for (int j = 0; j < 16; ++j)
-                  if (col0 + c0 + j < m_valid) acc[j] += __ldcg(src + (col0 + c0 + j) * kTileN);
-              }
-              if (n_ok) {
-#pragma unroll
-                for (int j = 0; j < 16; ++j)
-                  if (col0 + c0 + j < m_valid) cdst[(size_t)(col0 + c0 + j) * args.N] = from_f32<T>(acc[j] * ch_scale);
-              }
+              for (int j = 0; j < EW; ++j)
+                if (col0 + j < m_valid) acc[j] += __ldcg(src + (col0 + j) * kTileN);
             }
-            if (et == 0) args.counters[tile] = 0;
+            if (n_ok) {
+#pragma unroll
+              for (int j = 0; j < EW; ++j)
+                if (col0 + j < m_valid) cdst[(size_t)(col0 + j) * args.N] = from_f32<T>(acc[j] * ch_scale);
+            }
+            if (et == 0) args.counters[tile] = 0;   // self-reset for the next launch
           }
         }
 #pragma unroll
         for (int j = 0; j < EW; ++j) facc[j] = 0.f;
-        ++seg;
         it_seg0 = it + 1;
       }
       if (++ks == KS) { ks = 0; ++tile; }
@@ -840,7 +787,7 @@ int launch_decode(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t
   // this one is still running; at least `min_units` stages per CTA so that split-K partial traffic stays small
   static const int env_cps = getenv("B200_DEC_CTAS_PER_SM") ? atoi(getenv("B200_DEC_CTAS_PER_SM")) : 0;
   static const int env_minu = getenv("B200_DEC_MIN_UNITS") ? atoi(getenv("B200_DEC_MIN_UNITS")) : 0;
-  int cps = env_cps > 0 ? env_cps : occ[dev & 63];
+  int cps = env_cps > 0 ? env_cps : Cfg::OCC;
   const int min_units = env_minu > 0 ? env_minu : (MPAD >= 64 ? 4 : 2);
   int grid = num_sms() * cps;
   if (grid > kDecMaxGrid) grid = kDecMaxGrid;
@@ -885,30 +832,30 @@ int dec_asum_scratch(int dev, cudaStream_t st, float** asum);   // marlin_gemm.c
 constexpr int kDecMaxGroups = 8192;
 
 template <typename T, int MPAD, int GPS>
-int launch_decode2(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t st) {
-  using Cfg = Dec2Cfg<MPAD, GPS>;
+int launch_decode3(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t st) {
+  using Cfg = Dec3Cfg<MPAD>;
   GemmArgs a = a_in;
   a.m_chunks = 1;
   a.KS = a.K / kDecStageK;
   a.total_units = a.n_tiles * a.KS;
-  auto kern = marlin_decode2_kernel<T, MPAD, GPS>;
+  auto kern = marlin_decode3_kernel<T, MPAD, GPS>;
   int dev = 0;
   cudaGetDevice(&dev);
-  static int occ[64] = {};
-  if (occ[dev & 63] == 0) {
+  static bool attr_set[64] = {};
+  if (!attr_set[dev & 63]) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
     cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    int n = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, Cfg::THREADS, Cfg::SMEM_BYTES) != cudaSuccess || n < 1)
-      return set_error(B200_ECUDA, "marlin decode gemm: kernel does not fit on an SM (smem %d, threads %d)", Cfg::SMEM_BYTES, Cfg::THREADS);
-    occ[dev & 63] = n < Cfg::OCC ? n : Cfg::OCC;
-    if (getenv("B200_DEC_VERBOSE"))
-      fprintf(stderr, "[dec2] MPAD=%d GPS=%d: occupancy %d (want %d), smem %d, threads %d, NW=%d NA=%d NSLOT=%d\n", MPAD, GPS, n,
-              Cfg::OCC, Cfg::SMEM_BYTES, Cfg::THREADS, Cfg::NW, Cfg::NA, Cfg::NSLOT);
+    attr_set[dev & 63] = true;
+    if (getenv("B200_DEC_VERBOSE")) {
+      int n = 0;
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, Cfg::THREADS, Cfg::SMEM_BYTES);
+      fprintf(stderr, "[dec3] MPAD=%d GPS=%d: occupancy query %d (sized for %d), smem %d, threads %d, NW=%d NA=%d\n", MPAD, GPS, n,
+              Cfg::OCC, Cfg::SMEM_BYTES, Cfg::THREADS, Cfg::NW, Cfg::NA);
+    }
   }
   static const int env_cps = getenv("B200_DEC_CTAS_PER_SM") ? atoi(getenv("B200_DEC_CTAS_PER_SM")) : 0;
   static const int env_minu = getenv("B200_DEC_MIN_UNITS") ? atoi(getenv("B200_DEC_MIN_UNITS")) : 0;
-  const int cps = env_cps > 0 ? env_cps : occ[dev & 63];
+  const int cps = env_cps > 0 ? env_cps : Cfg::OCC;
   const int min_units = env_minu > 0 ? env_minu : (MPAD >= 64 ? 4 : 2);
   int grid = num_sms() * cps;
   if (grid > kDecMaxGrid) grid = kDecMaxGrid;
@@ -957,17 +904,41 @@ int launch_decode2(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_
   }
   cfg.attrs = attr;
   cfg.numAttrs = na;
+#ifdef B200_DEC_TRACE
+  if (getenv("B200_DEC_TRACE")) {
+    a.trace_cta = atoi(getenv("B200_DEC_TRACE"));
+    cudaMallocManaged(&a.trace, sizeof(long long) * 2 * 32 * 16);
+    cudaMemset(a.trace, 0, sizeof(long long) * 2 * 32 * 16);
+  }
+#endif
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmap_a, tmap_w, tmap_s, a);
   if (e != cudaSuccess) return set_error(B200_ECUDA, "marlin decode gemm launch: %s", cudaGetErrorString(e));
+#ifdef B200_DEC_TRACE
+  if (a.trace) {
+    cudaDeviceSynchronize();
+    long long t0 = 0;
+    for (int i = 0; i < 2 * 32 * 16; ++i) if (a.trace[i] && (t0 == 0 || a.trace[i] < t0)) t0 = a.trace[i];
+    for (int r = 0; r < 2; ++r)
+      for (int i = 0; i < 32; ++i) {
+        bool any = false;
+        for (int ev = 0; ev < 16; ++ev) any = any || a.trace[(r * 32 + i) * 16 + ev];
+        if (!any) continue;
+        fprintf(stderr, "[dec trace] %s it=%2d:", r ? "issuer " : "dequant", i);
+        for (int ev = 0; ev < 12; ++ev) fprintf(stderr, " %6lld", a.trace[(r * 32 + i) * 16 + ev] ? a.trace[(r * 32 + i) * 16 + ev] - t0 : -1);
+        fprintf(stderr, "\n");
+      }
+    cudaFree(a.trace);
+  }
+#endif
   return B200_OK;
 }
 
 template <typename T>
-int dispatch_decode2(const GemmArgs& a, const void* A, int64_t lda, cudaStream_t st) {
+int dispatch_decode3(const GemmArgs& a, const void* A, int64_t lda, cudaStream_t st) {
   const bool g128 = a.num_groups > 1;
-  if (a.M <= 16) return g128 ? launch_decode2<T, 16, 1>(a, A, lda, st) : launch_decode2<T, 16, 0>(a, A, lda, st);
-  if (a.M <= 32) return g128 ? launch_decode2<T, 32, 1>(a, A, lda, st) : launch_decode2<T, 32, 0>(a, A, lda, st);
-  return g128 ? launch_decode2<T, 64, 1>(a, A, lda, st) : launch_decode2<T, 64, 0>(a, A, lda, st);
+  if (a.M <= 16) return g128 ? launch_decode3<T, 16, 1>(a, A, lda, st) : launch_decode3<T, 16, 0>(a, A, lda, st);
+  if (a.M <= 32) return g128 ? launch_decode3<T, 32, 1>(a, A, lda, st) : launch_decode3<T, 32, 0>(a, A, lda, st);
+  return g128 ? launch_decode3<T, 64, 1>(a, A, lda, st) : launch_decode3<T, 64, 0>(a, A, lda, st);
 }
 
 // M <= 64, no fused all-reduce.  gps_code: scale rows per 128-k stage (0 channelwise, 1, 2, 4)
@@ -975,7 +946,7 @@ template <typename T, int BITS>
 int dispatch_decode(const GemmArgs& a, const void* A, int64_t lda, cudaStream_t st) {
   const int gps = a.num_groups > 1 ? kDecStageK / a.group_size : 0;
   static const int force_v1 = getenv("B200_DEC_V1") ? atoi(getenv("B200_DEC_V1")) : 0;
-  if (BITS == 4 && gps <= 1 && !force_v1 && a.K / 128 <= kDecMaxGroups) return dispatch_decode2<T>(a, A, lda, st);
+  if (BITS == 4 && gps <= 1 && !force_v1 && a.K / 128 <= kDecMaxGroups) return dispatch_decode3<T>(a, A, lda, st);
 #define B200_DEC_CASE(G)                                                        \
   if (gps == G) {                                                               \
     if (a.M <= 16) return launch_decode<T, 16, BITS, G>(a, A, lda, st);         \
