@@ -212,9 +212,10 @@ extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_
     }
   }
   int rc;
-  static const int force_old = getenv("B200_GEMM_OLD") ? atoi(getenv("B200_GEMM_OLD")) : 0;
-  if (size_m <= 64 && ga.ar.world <= 1 && !force_old && ga.n_tiles <= kDecMaxTiles) {
-    // decode shapes: the small-CTA kernel (marlin_decode_kernel.cuh)
+  // B200_GEMM_DECODE=1: the experimental small-CTA decode kernels (marlin_decode_kernel.cuh; parity-green, but measured
+  // slower than the kernel below on every Llama shape -- DESIGN.md section 6b has the numbers and the ncu evidence)
+  static const int use_decode = getenv("B200_GEMM_DECODE") ? atoi(getenv("B200_GEMM_DECODE")) : 0;
+  if (size_m <= 64 && ga.ar.world <= 1 && use_decode && ga.n_tiles <= kDecMaxTiles) {
     if (dtype == B200_F16) rc = (num_bits == 4) ? dispatch_decode_f16_4(ga, a, lda, st) : dispatch_decode_f16_8(ga, a, lda, st);
     else rc = (num_bits == 4) ? dispatch_decode_bf16_4(ga, a, lda, st) : dispatch_decode_bf16_8(ga, a, lda, st);
     if (rc) return rc;
