@@ -42,7 +42,10 @@ def parse():
                         "NCCL as the loud fallback when peer memory cannot be mapped (auto)")
     p.add_argument("--no-fuse", action="store_true", help="N>1: keep GEMM and all-reduce as two kernels")
     p.add_argument("--no-cpu-baseline", action="store_true")
-    p.add_argument("--sweep", action="store_true", help="also report tok/s at batch 1,2,4,8,16,32 (extra key)")
+    p.add_argument("--no-sweep", action="store_true",
+                   help="skip the batch sweep (tok/s at batch 1,2,4,8,16,32 + GEMM roofline fraction at batch 1 and 16)")
+    p.add_argument("--no-extra-models", action="store_true",
+                   help="N>1: skip the Llama-3-70B W4A16 / FP8 + fp8-KV ms-per-step lines at this TP degree")
     p.add_argument("--profile-step", action="store_true",
                    help="bracket ONE extra decode step with cudaProfilerStart/Stop (use with ncu --profile-from-start off)")
     return p.parse_args()
@@ -111,7 +114,7 @@ def run_reference(a):
     shape = shape_of(a.model)
     ts, last = [], None
     for i in range(a.warmup + a.steps):
-        last = cpu_decode.time_decode(shape, a.batch, a.ctx, layer_reps=1)
+        last = cpu_decode.time_decode(shape, a.batch, a.ctx, layer_reps=1, threads=os.cpu_count())
         if i >= a.warmup:
             ts.append(last["step_s"])
         if sum(ts) > 150:  # keep the whole run within minutes
@@ -122,8 +125,8 @@ def run_reference(a):
            "steps": len(ts), "warmup": a.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True,
            "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
            "config": {"workload": workload_name(a), "parallelism": "host cores"},
-           "cpu_baseline": {"value": v, "unit": "tok/s", "cores": last["cores"], "kind": last["kind"],
-                            "sample": last["sample"]},
+           "cpu_baseline": {"value": v, "unit": "tok/s", "cores": last["cores"], "host_cpu_count": os.cpu_count(),
+                            "kind": last["kind"], "sample": last["sample"]},
            "e2e": {"value": v, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(out), flush=True)
 
@@ -132,6 +135,7 @@ _OUR_KERNELS_PER_CALL = {  # CUDA launches of OUR kernels behind one operator ca
     "rms_norm": 1, "fused_add_rms_norm": 1, "silu_and_mul": 1, "rotary_embedding": 1, "reshape_and_cache": 1,
     "paged_attention_v1": 1, "paged_attention_v2": 2, "gptq_marlin_gemm": 1, "gptq_marlin_24_gemm": 1,
     "cutlass_scaled_mm": 1, "scaled_fp8_quant": 2, "scaled_int8_quant": 1, "greedy_sample": 1,
+    "rope_cache_paged_attention": 1,   # + the v2 merge kernel when exp_sums is given (counted in the wrapper)
 }
 
 
@@ -144,8 +148,13 @@ def count_launches(fn):
         saved[name] = orig
 
         def wrap(*args, __o=orig, __n=name, __p=per, **kw):
-            counts[__n] = counts.get(__n, 0) + __p
-            return __o(*args, **kw)
+            r = __o(*args, **kw)
+            if __n == "rope_cache_paged_attention":
+                if r:   # False = nothing launched (shape outside the fast path)
+                    counts[__n] = counts.get(__n, 0) + (2 if args[1] is not None else 1)
+            else:
+                counts[__n] = counts.get(__n, 0) + __p
+            return r
         setattr(ops, name, wrap)
     try:
         fn()
@@ -155,17 +164,7 @@ def count_launches(fn):
     return sum(counts.values()), counts
 
 
-def ncu_traffic():
-    """dram read+write bytes per launch of the dominant kernel from the committed `ncu --set full` capture
-    (profiles/r1_gemm_traffic.json, batch-64 decode step); None when the file is absent."""
-    try:
-        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_gemm_traffic.json")) as f:
-            return float(json.load(f)["traffic_bytes_per_launch"])
-    except Exception:
-        return None
-
-
-def gemm_roofline(model, batch, peaks):
+def gemm_roofline(model, batch, peaks, brief=False):
     """The dominant kernel timed ALONE: every Marlin GEMM of one step (4 per layer, distinct weights -> cold L2: the
     packed weights of one pass are 3.6 GB vs 126 MB of L2), CUDA events on the launching stream, 3 passes, median."""
     import torch
@@ -212,11 +211,102 @@ def gemm_roofline(model, batch, peaks):
     t = min(t, gt[len(gt) // 2])
     peak = peaks.get("hbm_gbs", 6650.0)
     ach = alg / t / 1e9
+    if brief:
+        return {"achieved": ach, "frac": ach / peak, "avg_launch_us": t / len(lin) * 1e6, "gemm_ms_per_step": t * 1e3}
     return {"bound": "hbm", "kernel": "marlin_gemm_kernel (gptq_marlin_gemm W4A16 g128)", "achieved": ach, "peak": peak,
-            "unit": "GB/s", "frac": ach / peak, "traffic": ncu_traffic(),
+            "unit": "GB/s", "frac": ach / peak,
+            # dram bytes per launch are NOT measured in this run (ncu only): see profiles/r1_gemm_traffic.json for the
+            # N=1 batch-64 capture (29.3 MB per launch vs 30.3 MB algorithmic)
+            "traffic": None,
             "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650",
             "launches": len(lin), "alg_bytes_per_launch": alg / len(lin), "avg_launch_us": t / len(lin) * 1e6,
             "gemm_ms_per_step": t * 1e3}
+
+
+def tp_parity_check(model, eng, batch, dev, rank, world):
+    """N > 1 self-check BEFORE timing (the driver's 1-GPU test box cannot run the multi-rank kernels): the NVLink
+    all-reduce kernel and the fused GEMM + all-reduce against an fp32 sum of the same per-rank inputs through NCCL
+    (tests/distributed/test_custom_all_reduce.py:29-131 does the same with known tensors), and the sampled ids of one
+    decode step identical on every rank.  Any mismatch makes the run exit non-zero."""
+    import torch
+    import torch.distributed as dist
+    res = {"allreduce_kernel": "not used", "fused_gemm_allreduce": "not used"}
+    ok = True
+    g = torch.Generator(device=dev).manual_seed(1000 + rank)
+
+    def close(y, ref32):
+        # both sides sum bf16 inputs in fp32 (different order) and round once: at most one ulp of the output dtype apart
+        tol = ref32.abs() * (2.0 ** -7 if y.dtype == torch.bfloat16 else 2.0 ** -10) + 1e-5
+        bad = ((y.float() - ref32).abs() > tol).sum()
+        return int(bad) == 0
+
+    hidden = model.shape.hidden
+    x = torch.randn((batch, hidden), generator=g, device=dev).to(model.dtype)
+    ref = x.float().clone()
+    dist.all_reduce(ref)
+    if model.custom_ar is not None and model.custom_ar.should_custom_ar(x):
+        y = model.custom_ar.all_reduce(x)
+        same = [torch.empty_like(y) for _ in range(world)]
+        dist.all_gather(same, y)
+        identical = all(torch.equal(same[0], t) for t in same)
+        good = close(y, ref) and identical
+        res["allreduce_kernel"] = "ok" if good else "MISMATCH"
+        ok = ok and good
+    lin = model.layers[0]["o"]
+    a = torch.randn((batch, lin.K), generator=g, device=dev).to(model.dtype)
+    part = lin(a)
+    ref2 = part.float().clone()
+    dist.all_reduce(ref2)
+    if (model.custom_ar is not None and model.fuse_gemm_all_reduce and lin.kind == "w4a16"
+            and model.custom_ar.fuse_next_gemm(batch, lin.N)):
+        y2 = lin(a)
+        good = close(y2, ref2)
+        res["fused_gemm_allreduce"] = "ok" if good else "MISMATCH"
+        ok = ok and good
+    eng.run_device()
+    torch.cuda.synchronize()
+    ids = [torch.empty_like(eng.d_out) for _ in range(world)]
+    dist.all_gather(ids, eng.d_out)
+    same_ids = all(torch.equal(ids[0], t) for t in ids)
+    res["sampled_ids_identical_on_all_ranks"] = bool(same_ids)
+    ok = ok and same_ids
+    flag = torch.tensor([1 if ok else 0], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    res["ok"] = bool(int(flag))
+    return res
+
+
+def time_extra_model(a, decoder, shape, quant, kv, dev, world, rank, use_custom_ar, steps):
+    """ms per decode step (device-timed CUDA-graph replays, max over ranks) of another model at this TP degree."""
+    import torch
+    import torch.distributed as dist
+    dtype = torch.float16 if quant == "w4a16_24" else torch.bfloat16
+    nb_seq = (a.ctx + 15) // 16
+    m = decoder.SyntheticLlama(shape, quant=quant, dtype=dtype, device=dev, tp_size=world, tp_rank=rank,
+                               kv_cache_dtype=kv, kv_scale=1.0 if kv == "auto" else 0.0376,
+                               num_blocks=max(a.batch * nb_seq * 2, 1024), max_pos=max(a.ctx + 1, 512))
+    if use_custom_ar is not None:
+        m.custom_ar = use_custom_ar
+    m.fuse_gemm_all_reduce = not a.no_fuse
+    eng = decoder.DecodeEngine(m, a.batch, a.ctx)
+    eng.load_inputs(eng.host_inputs(a.ctx, seed=1))
+    eng.prepare(a.ctx)
+    for _ in range(3):
+        eng.run_device()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        eng.run_device()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / steps], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    floor = (m.linear_weight_bytes() + m.lm_head.weight_bytes() + m.kv_read_bytes([a.ctx] * a.batch))
+    return {"ms_per_step": float(t), "tok_s": a.batch / float(t) * 1e3, "hbm_floor_bytes_per_rank": floor, "layers": m.nlayers}
 
 
 def run_b200(a):
@@ -275,6 +365,14 @@ def run_b200(a):
         if model.n_custom_ar_calls == 0:
             ar_kind = "fused into the row-parallel W4A16 GEMM epilogue (LL exchange over NVLink peer memory)"
     eng.prepare(a.ctx)
+    parity = None
+    if world > 1:
+        parity = tp_parity_check(model, eng, a.batch, dev, rank, world)
+        if not parity["ok"]:
+            if rank == 0:
+                print(json.dumps({"parity_check": parity, "error": "multi-GPU parity check failed; nothing timed"}), flush=True)
+            sys.stdout.flush()
+            os._exit(3)
 
     def barrier():
         if world > 1:
@@ -330,15 +428,33 @@ def run_b200(a):
                    "d2h_bytes_per_step": eng.h_out.numel() * eng.h_out.element_size(),
                    "ms_per_step": t_e2e / a.steps * 1e3},
            "gpu_launches": launches * a.steps, "gpu_launches_per_step": per_op, "clocks": clk}
+    if parity is not None:
+        out["parity_check"] = parity
     if a.layers is not None:
         out["config"]["INVALID"] = "truncated model (--layers)"
+    if world > 1 and not a.no_extra_models and a.model == "llama-3-8b" and a.quant == "w4a16" and a.layers is None:
+        # north_star asks for Llama-3-70B at TP 2/4/8: W4A16 g128 and W8A8 FP8 + fp8 KV, same batch / ctx, at this TP degree
+        extra = {}
+        del eng
+        for label, quant, kv in (("llama-3-70b w4a16 g128, kv auto", "w4a16", "auto"),
+                                 ("llama-3-70b w8a8 fp8 (cutlass_scaled_mm), kv fp8", "fp8", "fp8")):
+            try:
+                extra[label] = time_extra_model(a, decoder, decoder.LLAMA3_70B, quant, kv, dev, world, rank, model.custom_ar,
+                                                max(5, a.steps // 2))
+            except Exception as e:   # keep the headline line even if an extra model cannot run on this box
+                extra[label] = {"error": repr(e)[:200]}
+            torch.cuda.empty_cache()
+        out["extra_models_at_this_tp"] = extra
     if rank == 0 and a.quant in ("w4a16", "w4a16_24"):
         out["roofline"] = gemm_roofline(model, a.batch, peaks)
         step_alg = (model.linear_weight_bytes() + model.lm_head.weight_bytes() + model.kv_read_bytes([a.ctx] * a.batch))
         out["step_hbm_floor_ms"] = step_alg / (peaks.get("hbm_gbs", 6650.0) * 1e9) * 1e3
-    if a.sweep and world == 1:
-        sw = {}
+    if not a.no_sweep and world == 1:
+        # the metric is quoted over "bs 1-64" (benchmark_marlin.py:20-21 sweeps the same batches)
+        sw = {str(a.batch): tok / t_dev}
         for b in (1, 2, 4, 8, 16, 32):
+            if b == a.batch:
+                continue
             e = decoder.DecodeEngine(model, b, a.ctx)
             e.load_inputs(e.host_inputs(a.ctx, seed=3))
             e.prepare(a.ctx)
@@ -351,12 +467,18 @@ def run_b200(a):
             e1.record()
             torch.cuda.synchronize()
             sw[str(b)] = b * a.steps / (e0.elapsed_time(e1) * 1e-3)
-        out["tok_s_by_batch"] = sw
+            del e
+        out["tok_s_by_batch"] = dict(sorted(sw.items(), key=lambda kv: int(kv[0])))
+        if "roofline" in out:
+            out["roofline"]["by_batch"] = {str(a.batch): {"frac": out["roofline"]["frac"], "avg_launch_us": out["roofline"]["avg_launch_us"]}}
+            for b in (1, 16):
+                if b != a.batch:
+                    out["roofline"]["by_batch"][str(b)] = gemm_roofline(model, b, peaks, brief=True)
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
         from oracle import cpu_decode
-        r = cpu_decode.time_decode(shape, a.batch, a.ctx, layer_reps=3)
-        out["cpu_baseline"] = {"value": a.batch / r["step_s"], "unit": "tok/s", "cores": r["cores"], "kind": r["kind"],
-                               "sample": r["sample"]}
+        r = cpu_decode.time_decode(shape, a.batch, a.ctx, layer_reps=3, threads=os.cpu_count())
+        out["cpu_baseline"] = {"value": a.batch / r["step_s"], "unit": "tok/s", "cores": r["cores"],
+                               "host_cpu_count": os.cpu_count(), "kind": r["kind"], "sample": r["sample"]}
     if rank == 0:
         print(json.dumps(out), flush=True)
     if world > 1:

@@ -130,6 +130,21 @@ int b200_scaled_mm(void* out, const void* a, const void* b, const float* a_scale
 /* reference: scaled_mm_entry.cu:32-46 */
 int b200_scaled_mm_supports_fp8(int cuda_device_capability);
 
+/* ---- fused decode-step attention (new): rotary_embedding (csrc/pos_encoding_kernels.cu:71-203, neox,
+ * rot_dim == head_size == 128) + reshape_and_cache (csrc/cache_kernels.cu:153-204) + paged_attention_v1/v2
+ * (csrc/attention/attention_kernels.cu:805-990) in one launch (two with the v2 merge).  query is NOT modified (rotated in
+ * registers); the rotated key only exists in the cache.  slot_mapping[s] must be the slot of token seq_lens[s]-1.
+ * B200_ENOTSUP when the shape is outside the GQA fast path: call the three ops instead. */
+int b200_rope_cache_paged_attention(void* out, float* exp_sums, float* max_logits, void* tmp_out,
+                                    const void* query, const void* key, const void* value, void* key_cache,
+                                    void* value_cache, const int64_t* positions, const void* cos_sin_cache,
+                                    int rot_dim, const int64_t* slot_mapping, int num_seqs, int num_heads,
+                                    int num_kv_heads, int head_size, float scale, const int32_t* block_tables,
+                                    const int32_t* seq_lens, int max_blocks_per_seq, int block_size,
+                                    int max_seq_len, int64_t q_stride, int64_t k_stride, int64_t v_stride,
+                                    int64_t kv_block_stride, int64_t kv_head_stride, int dtype, int kv_dtype,
+                                    float kv_scale, int use_v2, void* stream);
+
 /* ---- scratch management (new; see DESIGN.md "split-K partials") -------------------------------------
  * Ensures the per-device split-K scratch is allocated for GEMMs up to max_m rows.  Called implicitly
  * by the first eager GEMM; call explicitly before CUDA-graph capture. */

@@ -55,6 +55,20 @@ def greedy_sample(logits: torch.Tensor) -> torch.Tensor:
     return out
 
 
+def rope_cache_paged_attention(out: torch.Tensor, exp_sums: Optional[torch.Tensor], max_logits: Optional[torch.Tensor],
+                               tmp_out: Optional[torch.Tensor], query: torch.Tensor, key: torch.Tensor,
+                               value: torch.Tensor, key_cache: torch.Tensor, value_cache: torch.Tensor,
+                               positions: torch.Tensor, cos_sin_cache: torch.Tensor, slot_mapping: torch.Tensor,
+                               num_kv_heads: int, scale: float, block_tables: torch.Tensor, seq_lens: torch.Tensor,
+                               block_size: int, max_seq_len: int, kv_cache_dtype: str, kv_scale: float) -> bool:
+    """Decode-step fusion of rotary_embedding (neox) + reshape_and_cache + paged_attention_v1 (exp_sums is None) / v2 in
+    one launch; `query` is left unrotated.  Returns False (nothing launched) when the shape is outside the fast path:
+    the caller then runs the three reference ops."""
+    return _ops().rope_cache_paged_attention(out, exp_sums, max_logits, tmp_out, query, key, value, key_cache,
+                                             value_cache, positions, cos_sin_cache, slot_mapping, num_kv_heads, scale,
+                                             block_tables, seq_lens, block_size, max_seq_len, kv_cache_dtype, kv_scale)
+
+
 def silu_and_mul(out: torch.Tensor, x: torch.Tensor) -> None:
     _ops().silu_and_mul(out, x)
 

@@ -56,10 +56,50 @@ __device__ __forceinline__ uint32_t movmatrix_trans(uint32_t x) {
   asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(y) : "r"(x));
   return y;
 }
+// NC: read-only path (the caches are not written by this kernel).  The fused kernel below writes the new token's K / V
+// itself and must read them back coherently.
+template <bool NC>
 __device__ __forceinline__ uint32_t ldg32(const void* p) {
   uint32_t v;
-  asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  if (NC) asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  else asm volatile("ld.global.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
+}
+
+// rotary embedding (neox) + cache write of the step's new token, folded into the attention kernel's prologue
+// (reference: csrc/pos_encoding_kernels.cu:10-93 and csrc/cache_kernels.cu:153-204; rounding points as in glue.cu:
+// T(T(x*cos) - T(y*sin))).  All pointers may be null when the kernel is not fused.
+struct RopeCacheArgs {
+  const int64_t* positions;     // [S]
+  const void* cos_sin;          // [max_pos, 128]: cos [0,64) | sin [64,128)
+  const void* key;              // [S, Hkv, 128], row stride key_stride
+  const void* value;
+  const int64_t* slot_mapping;  // [S], -1 = padding
+  int64_t key_stride, value_stride;
+  void* k_cache_w;
+  void* v_cache_w;
+};
+
+template <typename T>
+__device__ __forceinline__ T rope_x(T x, T y, T c, T s_) {   // x' = T(T(x c) - T(y s))
+  return from_f32<T>(to_f32<T>(from_f32<T>(to_f32<T>(x) * to_f32<T>(c))) - to_f32<T>(from_f32<T>(to_f32<T>(y) * to_f32<T>(s_))));
+}
+template <typename T>
+__device__ __forceinline__ T rope_y(T x, T y, T c, T s_) {   // y' = T(T(y c) + T(x s))
+  return from_f32<T>(to_f32<T>(from_f32<T>(to_f32<T>(y) * to_f32<T>(c))) + to_f32<T>(from_f32<T>(to_f32<T>(x) * to_f32<T>(s_))));
+}
+// packed pairs: (x2, y2) = elements (d, d+1) and (d+64, d+65); (c2, s2) = cos / sin of (d, d+1)
+template <typename T>
+__device__ __forceinline__ void rope_pair(uint32_t& x2, uint32_t& y2, uint32_t c2, uint32_t s2) {
+  const T* x = reinterpret_cast<const T*>(&x2);
+  const T* y = reinterpret_cast<const T*>(&y2);
+  const T* c = reinterpret_cast<const T*>(&c2);
+  const T* s_ = reinterpret_cast<const T*>(&s2);
+  T xo[2], yo[2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) { xo[i] = rope_x<T>(x[i], y[i], c[i], s_[i]); yo[i] = rope_y<T>(x[i], y[i], c[i], s_[i]); }
+  x2 = *reinterpret_cast<const uint32_t*>(xo);
+  y2 = *reinterpret_cast<const uint32_t*>(yo);
 }
 
 // four fp8 bytes (little endian v0..v3) -> {half2(v0,v1), half2(v2,v3)}: exact (every e4m3 / e5m2 value is an fp16 value).
@@ -85,15 +125,17 @@ __device__ __forceinline__ uint32_t repack(uint32_t v) {
 
 }  // namespace amma
 
-template <typename T, int KV>
+template <typename T, int KV, bool FUSED>
 __global__ void __launch_bounds__(amma::kThreads, 3)
 paged_attn_gqa_kernel(float* __restrict__ exp_sums, float* __restrict__ max_logits, T* __restrict__ out,
                       const T* __restrict__ q, const void* __restrict__ k_cache_v, const void* __restrict__ v_cache_v,
                       int num_heads, int num_kv_heads, float scale, const int* __restrict__ block_tables,
                       const int* __restrict__ seq_lens, int max_blocks_per_seq, const float* __restrict__ alibi_slopes,
-                      int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride, int partitioned, float kv_scale) {
+                      int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride, int partitioned, float kv_scale,
+                      const amma::RopeCacheArgs rc) {
   using namespace amma;
   constexpr bool FP8 = KV != B200_KV_AUTO;
+  constexpr bool NC = !FUSED;
   using MT = typename std::conditional<FP8, __half, T>::type;   // MMA operand type
   const float s_scale = FP8 ? scale * kv_scale : scale;
   const float o_scale = FP8 ? kv_scale : 1.f;
@@ -125,6 +167,48 @@ paged_attn_gqa_kernel(float* __restrict__ exp_sums, float* __restrict__ max_logi
       qf[c][1] = g < G ? repack<T, MT>(*reinterpret_cast<const uint32_t*>(qrow + 16 * c + (FP8 ? 2 : 8))) : 0u;
     }
   }
+  if constexpr (FUSED) {
+    const int64_t pos = rc.positions[seq];
+    const T* cs = reinterpret_cast<const T*>(rc.cos_sin) + pos * D;
+    // the new token's K (rotated) and V go into the cache: thread d of the CTA that owns the token's partition
+    const int64_t slot = rc.slot_mapping[seq];
+    const bool writer = slot >= 0 && (!partitioned || part == (seq_len - 1) / kPartition);
+    if (writer) {
+      const int d = threadIdx.x, dd = d & 63;
+      const T* krow = reinterpret_cast<const T*>(rc.key) + (int64_t)seq * rc.key_stride + (int64_t)kvh * D;
+      const T x = krow[dd], y = krow[dd + 64], c = cs[dd], sn = cs[64 + dd];
+      const T kr = d < 64 ? rope_x<T>(x, y, c, sn) : rope_y<T>(x, y, c, sn);
+      const T vv = reinterpret_cast<const T*>(rc.value)[(int64_t)seq * rc.value_stride + (int64_t)kvh * D + d];
+      const int64_t wbase = (slot / BS) * kv_block_stride + (int64_t)kvh * kv_head_stride;
+      const int off = (int)(slot % BS);
+      if constexpr (!FP8) {
+        reinterpret_cast<T*>(rc.k_cache_w)[wbase + (d >> 3) * (BS * 8) + off * 8 + (d & 7)] = kr;
+        reinterpret_cast<T*>(rc.v_cache_w)[wbase + d * BS + off] = vv;
+      } else {
+        reinterpret_cast<uint8_t*>(rc.k_cache_w)[wbase + (d >> 4) * (BS * 16) + off * 16 + (d & 15)] =
+            fp8_quant<FP8 ? KV : B200_KV_FP8_E4M3>(to_f32<T>(kr), kv_scale);
+        reinterpret_cast<uint8_t*>(rc.v_cache_w)[wbase + d * BS + off] = fp8_quant<FP8 ? KV : B200_KV_FP8_E4M3>(to_f32<T>(vv), kv_scale);
+      }
+    }
+    // the query heads are rotated in their fragments: element d (chunk c < 4) and its partner d + 64 (chunk c + 4) sit in
+    // the same lane
+    if (g < G) {
+      const T* qrow = q + (int64_t)seq * q_stride + (int64_t)(head0 + g) * D + (FP8 ? 4 : 2) * qd;
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const int doff = 16 * c + (i ? (FP8 ? 2 : 8) : 0);
+          const int d0 = doff + (FP8 ? 4 : 2) * qd;
+          uint32_t x2 = *reinterpret_cast<const uint32_t*>(qrow + doff);
+          uint32_t y2 = *reinterpret_cast<const uint32_t*>(qrow + doff + 64);
+          rope_pair<T>(x2, y2, *reinterpret_cast<const uint32_t*>(cs + d0), *reinterpret_cast<const uint32_t*>(cs + 64 + d0));
+          qf[c][i] = repack<T, MT>(x2);
+          qf[c + 4][i] = repack<T, MT>(y2);
+        }
+    }
+    __syncthreads();   // the token just written is read back below by the warp that walks its page
+  }
   float slope[2] = {0.f, 0.f};
   if (alibi_slopes) {
     if (2 * qd < G) slope[0] = alibi_slopes[head0 + 2 * qd];
@@ -151,17 +235,17 @@ paged_attn_gqa_kernel(float* __restrict__ exp_sums, float* __restrict__ max_logi
       const T* vp = reinterpret_cast<const T*>(v_cache_v) + base + g * BS + 2 * qd;          // V [D][16]
 #pragma unroll
       for (int c = 0; c < 8; ++c) {
-        kf[c][0] = ldg32(kp + (2 * c) * (BS * 8));
-        kf[c][1] = ldg32(kp + (2 * c) * (BS * 8) + 64);
-        kf[c][2] = ldg32(kp + (2 * c + 1) * (BS * 8));
-        kf[c][3] = ldg32(kp + (2 * c + 1) * (BS * 8) + 64);
+        kf[c][0] = ldg32<NC>(kp + (2 * c) * (BS * 8));
+        kf[c][1] = ldg32<NC>(kp + (2 * c) * (BS * 8) + 64);
+        kf[c][2] = ldg32<NC>(kp + (2 * c + 1) * (BS * 8));
+        kf[c][3] = ldg32<NC>(kp + (2 * c + 1) * (BS * 8) + 64);
       }
 #pragma unroll
       for (int dm = 0; dm < 8; ++dm) {
-        vf[dm][0] = ldg32(vp + (16 * dm) * BS);
-        vf[dm][1] = ldg32(vp + (16 * dm + 8) * BS);
-        vf[dm][2] = ldg32(vp + (16 * dm) * BS + 8);
-        vf[dm][3] = ldg32(vp + (16 * dm + 8) * BS + 8);
+        vf[dm][0] = ldg32<NC>(vp + (16 * dm) * BS);
+        vf[dm][1] = ldg32<NC>(vp + (16 * dm + 8) * BS);
+        vf[dm][2] = ldg32<NC>(vp + (16 * dm) * BS + 8);
+        vf[dm][3] = ldg32<NC>(vp + (16 * dm + 8) * BS + 8);
       }
     } else {
       const uint8_t* kp = reinterpret_cast<const uint8_t*>(k_cache_v) + base + 4 * qd;        // K [D/16][16][16]
@@ -169,13 +253,13 @@ paged_attn_gqa_kernel(float* __restrict__ exp_sums, float* __restrict__ max_logi
       uint32_t kr[8][2], vr[8][2];
 #pragma unroll
       for (int c = 0; c < 8; ++c) {
-        kr[c][0] = ldg32(kp + c * (BS * 16) + t_lo * 16);
-        kr[c][1] = ldg32(kp + c * (BS * 16) + t_hi * 16);
+        kr[c][0] = ldg32<NC>(kp + c * (BS * 16) + t_lo * 16);
+        kr[c][1] = ldg32<NC>(kp + c * (BS * 16) + t_hi * 16);
       }
 #pragma unroll
       for (int dm = 0; dm < 8; ++dm) {
-        vr[dm][0] = ldg32(vp + (16 * dm) * BS);
-        vr[dm][1] = ldg32(vp + (16 * dm + 8) * BS);
+        vr[dm][0] = ldg32<NC>(vp + (16 * dm) * BS);
+        vr[dm][1] = ldg32<NC>(vp + (16 * dm + 8) * BS);
       }
 #pragma unroll
       for (int c = 0; c < 8; ++c) {
@@ -284,13 +368,12 @@ paged_attn_gqa_kernel(float* __restrict__ exp_sums, float* __restrict__ max_logi
 }
 
 // returns 1 if handled, 0 if the shape is not covered by this path (the caller runs the generic kernel), < 0 on error
-int launch_mma(float* exp_sums, float* max_logits, void* out, void* tmp_out, const void* q, const void* kc,
-               const void* vc, int num_seqs, int num_heads, int num_kv_heads, int head_size, float scale,
-               const int* block_tables, const int* seq_lens, int max_blocks_per_seq, int block_size, int max_seq_len,
-               const float* alibi, int64_t q_stride, int64_t kvbs, int64_t kvhs, int partitioned, int num_parts,
-               int dtype, int kv_dtype, float kv_scale, cudaStream_t st) {
+static int launch_mma_impl(float* exp_sums, float* max_logits, void* out, void* tmp_out, const void* q, const void* kc,
+                           const void* vc, int num_seqs, int num_heads, int num_kv_heads, int head_size, float scale,
+                           const int* block_tables, const int* seq_lens, int max_blocks_per_seq, int block_size,
+                           const float* alibi, int64_t q_stride, int64_t kvbs, int64_t kvhs, int partitioned, int num_parts,
+                           int dtype, int kv_dtype, float kv_scale, const amma::RopeCacheArgs* rcp, cudaStream_t st) {
   using namespace amma;
-  (void)max_seq_len;
   static const bool disabled = getenv("B200_ATTN_GENERIC") != nullptr;
   if (disabled) return 0;
   const int G = num_heads / num_kv_heads;
@@ -305,10 +388,13 @@ int launch_mma(float* exp_sums, float* max_logits, void* out, void* tmp_out, con
   dim3 grid(num_kv_heads, num_seqs, partitioned ? num_parts : 1);
   void* dst = partitioned ? tmp_out : out;
   cudaError_t e = cudaSuccess;
-#define GQA_GO(TT, KVV)                                                                                                 \
-  e = launch_pdl(paged_attn_gqa_kernel<TT, KVV>, grid, dim3(kThreads), 0, st, exp_sums, max_logits, (TT*)dst,            \
+  RopeCacheArgs rc = {};
+  if (rcp) rc = *rcp;
+#define GQA_GO2(TT, KVV, FF)                                                                                            \
+  e = launch_pdl(paged_attn_gqa_kernel<TT, KVV, FF>, grid, dim3(kThreads), 0, st, exp_sums, max_logits, (TT*)dst,        \
                  (const TT*)q, kc, vc, num_heads, num_kv_heads, scale, block_tables, seq_lens, max_blocks_per_seq, alibi, \
-                 q_stride, kvbs, kvhs, partitioned, kv_scale)
+                 q_stride, kvbs, kvhs, partitioned, kv_scale, rc)
+#define GQA_GO(TT, KVV) do { if (rcp) GQA_GO2(TT, KVV, true); else GQA_GO2(TT, KVV, false); } while (0)
   if (dtype == B200_F16) {
     if (kv_dtype == B200_KV_AUTO) GQA_GO(__half, B200_KV_AUTO);
     else if (kv_dtype == B200_KV_FP8_E4M3) GQA_GO(__half, B200_KV_FP8_E4M3);
@@ -319,8 +405,65 @@ int launch_mma(float* exp_sums, float* max_logits, void* out, void* tmp_out, con
     else GQA_GO(__nv_bfloat16, B200_KV_FP8_E5M2);
   }
 #undef GQA_GO
+#undef GQA_GO2
   if (e != cudaSuccess) return set_error(B200_ECUDA, "paged_attention (gqa path) launch: %s", cudaGetErrorString(e));
   return 1;
 }
 
+int launch_mma(float* exp_sums, float* max_logits, void* out, void* tmp_out, const void* q, const void* kc,
+               const void* vc, int num_seqs, int num_heads, int num_kv_heads, int head_size, float scale,
+               const int* block_tables, const int* seq_lens, int max_blocks_per_seq, int block_size, int max_seq_len,
+               const float* alibi, int64_t q_stride, int64_t kvbs, int64_t kvhs, int partitioned, int num_parts,
+               int dtype, int kv_dtype, float kv_scale, cudaStream_t st) {
+  (void)max_seq_len;
+  return launch_mma_impl(exp_sums, max_logits, out, tmp_out, q, kc, vc, num_seqs, num_heads, num_kv_heads, head_size, scale,
+                         block_tables, seq_lens, max_blocks_per_seq, block_size, alibi, q_stride, kvbs, kvhs, partitioned,
+                         num_parts, dtype, kv_dtype, kv_scale, nullptr, st);
+}
+
+int launch_v2_reduce(void* out, const float* exp_sums, const float* max_logits, const void* tmp_out,
+                     const int* seq_lens, int num_seqs, int num_heads, int head_size, int max_parts, int dtype,
+                     cudaStream_t st);
+
 }  // namespace b200
+
+// Fused decode-step attention: rotary embedding (neox, rot_dim == head_size == 128) of q and k, the new token's K / V
+// written into the paged cache, and paged_attention_v1 / v2 over the cache -- ONE launch (two with the v2 merge) instead
+// of rotary_embedding + reshape_and_cache + paged_attention.  q is rotated in registers (the caller's query tensor is left
+// unrotated), the rotated k only exists in the cache.  Contract beyond the three separate ops: slot_mapping[s] is the
+// slot of token seq_lens[s] - 1 of sequence s (decode), and no two sequences of the batch write into / read from the
+// same physical block (what the reference's block manager guarantees for a block that is being appended to).
+// Returns B200_ENOTSUP when the shape is outside the GQA fast path (run the three ops instead).
+extern "C" int b200_rope_cache_paged_attention(void* out, float* exp_sums, float* max_logits, void* tmp_out,
+                                               const void* query, const void* key, const void* value, void* key_cache,
+                                               void* value_cache, const int64_t* positions, const void* cos_sin_cache,
+                                               int rot_dim, const int64_t* slot_mapping, int num_seqs, int num_heads,
+                                               int num_kv_heads, int head_size, float scale, const int32_t* block_tables,
+                                               const int32_t* seq_lens, int max_blocks_per_seq, int block_size,
+                                               int max_seq_len, int64_t q_stride, int64_t k_stride, int64_t v_stride,
+                                               int64_t kv_block_stride, int64_t kv_head_stride, int dtype, int kv_dtype,
+                                               float kv_scale, int use_v2, void* stream) {
+  using namespace b200;
+  if (num_seqs == 0) return B200_OK;
+  if (rot_dim != head_size || head_size != amma::D || block_size != amma::BS)
+    return set_error(B200_ENOTSUP, "rope_cache_paged_attention: only head_size = rot_dim = 128, block_size 16");
+  if (use_v2 && (exp_sums == nullptr || max_logits == nullptr || tmp_out == nullptr))
+    return set_error(B200_EINVAL, "rope_cache_paged_attention: v2 needs exp_sums / max_logits / tmp_out");
+  amma::RopeCacheArgs rc;
+  rc.positions = positions; rc.cos_sin = cos_sin_cache; rc.key = key; rc.value = value; rc.slot_mapping = slot_mapping;
+  rc.key_stride = k_stride; rc.value_stride = v_stride; rc.k_cache_w = key_cache; rc.v_cache_w = value_cache;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int num_parts = use_v2 ? (max_seq_len + 511) / 512 : 1;
+  int r = launch_mma_impl(exp_sums, max_logits, out, tmp_out, query, key_cache, value_cache, num_seqs, num_heads,
+                          num_kv_heads, head_size, scale, block_tables, seq_lens, max_blocks_per_seq, block_size, nullptr,
+                          q_stride, kv_block_stride, kv_head_stride, use_v2 ? 1 : 0, num_parts, dtype, kv_dtype, kv_scale,
+                          &rc, st);
+  if (r < 0) return r;
+  if (r == 0) return set_error(B200_ENOTSUP, "rope_cache_paged_attention: shape outside the GQA fast path");
+  if (use_v2) {
+    r = launch_v2_reduce(out, exp_sums, max_logits, tmp_out, seq_lens, num_seqs, num_heads, head_size, num_parts, dtype, st);
+    if (r < 0) return r;
+  }
+  B200_LAUNCH_CHECK("rope_cache_paged_attention");
+  return B200_OK;
+}

@@ -92,6 +92,40 @@ void paged_attention_v2(torch::Tensor& out, torch::Tensor& exp_sums, torch::Tens
            "paged_attention_v2");
 }
 
+// fused rotary_embedding + reshape_and_cache + paged_attention_v1/v2 (decode); returns false when the shape is outside the
+// fast path and NOTHING was launched (the caller then runs the three reference ops)
+bool rope_cache_paged_attention(torch::Tensor& out, const std::optional<torch::Tensor>& exp_sums,
+                                const std::optional<torch::Tensor>& max_logits, const std::optional<torch::Tensor>& tmp_out,
+                                torch::Tensor& query, torch::Tensor& key, torch::Tensor& value, torch::Tensor& key_cache,
+                                torch::Tensor& value_cache, torch::Tensor& positions, torch::Tensor& cos_sin_cache,
+                                torch::Tensor& slot_mapping, int64_t num_kv_heads, double scale,
+                                torch::Tensor& block_tables, torch::Tensor& seq_lens, int64_t block_size,
+                                int64_t max_seq_len, const std::string& kv_cache_dtype, double kv_scale) {
+  TORCH_CHECK(block_tables.scalar_type() == at::ScalarType::Int && seq_lens.scalar_type() == at::ScalarType::Int,
+              "block_tables and seq_lens must be int32");
+  TORCH_CHECK(slot_mapping.scalar_type() == at::ScalarType::Long && positions.scalar_type() == at::ScalarType::Long,
+              "slot_mapping and positions must be int64");
+  TORCH_CHECK(query.dim() == 3 && key.dim() == 3 && value.dim() == 3, "query/key/value must be [tokens, heads, head_size]");
+  TORCH_CHECK(query.stride(-1) == 1 && query.stride(1) == query.size(2), "query heads must be contiguous");
+  TORCH_CHECK(key.stride(-1) == 1 && key.stride(1) == key.size(2) && value.stride(-1) == 1 && value.stride(1) == value.size(2),
+              "key/value heads must be contiguous");
+  TORCH_CHECK(out.is_contiguous() && cos_sin_cache.is_contiguous());
+  const bool v2 = exp_sums.has_value();
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(query));
+  int rc = b200_rope_cache_paged_attention(
+      out.data_ptr(), v2 ? exp_sums->data_ptr<float>() : nullptr, v2 ? max_logits->data_ptr<float>() : nullptr,
+      v2 ? tmp_out->data_ptr() : nullptr, query.data_ptr(), key.data_ptr(), value.data_ptr(), key_cache.data_ptr(),
+      value_cache.data_ptr(), positions.data_ptr<int64_t>(), cos_sin_cache.data_ptr(), (int)cos_sin_cache.size(1),
+      slot_mapping.data_ptr<int64_t>(), (int)query.size(0), (int)query.size(1), (int)num_kv_heads, (int)query.size(2),
+      (float)scale, block_tables.data_ptr<int>(), seq_lens.data_ptr<int>(), (int)block_tables.size(1), (int)block_size,
+      (int)max_seq_len, query.stride(0), key.stride(0), value.stride(0), key_cache.stride(0), key_cache.stride(1),
+      dtype_enum(query.scalar_type(), "rope_cache_paged_attention"), kv_enum(kv_cache_dtype), (float)kv_scale, v2 ? 1 : 0,
+      cur_stream(query));
+  if (rc == B200_ENOTSUP) return false;
+  raise_if(rc, "rope_cache_paged_attention");
+  return true;
+}
+
 // ---------------------------------------------------------------- cache (cache_kernels.cu:253-278, 339-389)
 void reshape_and_cache(torch::Tensor& key, torch::Tensor& value, torch::Tensor& key_cache, torch::Tensor& value_cache,
                        torch::Tensor& slot_mapping, const std::string& kv_cache_dtype, const double kv_scale) {
@@ -512,6 +546,12 @@ TORCH_LIBRARY(_b200_C, ops) {
       "    int blocksparse_head_sliding_step) -> ()");
   ops.impl("paged_attention_v2", torch::kCUDA, &paged_attention_v2);
 
+  ops.def(
+      "rope_cache_paged_attention(Tensor! out, Tensor? exp_sums, Tensor? max_logits, Tensor? tmp_out, Tensor query,"
+      " Tensor key, Tensor value, Tensor! key_cache, Tensor! value_cache, Tensor positions, Tensor cos_sin_cache,"
+      " Tensor slot_mapping, int num_kv_heads, float scale, Tensor block_tables, Tensor seq_lens, int block_size,"
+      " int max_seq_len, str kv_cache_dtype, float kv_scale) -> bool");
+  ops.impl("rope_cache_paged_attention", torch::kCUDA, &rope_cache_paged_attention);
   ops.def("greedy_sample(Tensor! out, Tensor logits) -> ()");
   ops.impl("greedy_sample", torch::kCUDA, &greedy_sample);
   ops.def("silu_and_mul(Tensor! out, Tensor input) -> ()");

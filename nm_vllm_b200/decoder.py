@@ -122,6 +122,7 @@ class SyntheticLlama:
         self.custom_ar = None  # CustomAllreduce once enable_custom_all_reduce() has been called
         self.n_custom_ar_calls = 0  # stand-alone all-reduce kernel launches (bench.py counts them per step)
         self.fuse_gemm_all_reduce = True  # row-parallel W4A16 GEMMs all-reduce in their epilogue when custom_ar is on
+        self.fuse_attention = True  # rope + cache write + paged attention in one launch when the shape is on the fast path
         s = shape
         self.nlayers = layers if layers is not None else s.layers
         assert s.heads % tp_size == 0
@@ -203,22 +204,31 @@ class SyntheticLlama:
             torch.distributed.all_reduce(t, group=self.group)
         return t
 
-    def _attention(self, li, q, k, v, meta):
+    def _attention(self, li, q, k, v, positions, meta):
+        """rotary_embedding -> reshape_and_cache -> paged_attention_v1/v2 (llama.py LlamaAttention.forward +
+        PagedAttention.write_to_paged_cache / forward_decode), or the one-launch fusion of the three."""
         kc, vc = self.kv[li]
-        ops.reshape_and_cache(k, v, kc, vc, meta["slot_mapping"], self.kv_cache_dtype, self.kv_scale)
         B, D = q.shape[0], self.shape.head_dim
         out = torch.empty((B, self.H, D), dtype=q.dtype, device=q.device)
         max_len = meta["max_seq_len"]
         nparts = (max_len + PARTITION_SIZE - 1) // PARTITION_SIZE
         # v1/v2 heuristic of PagedAttention.forward_decode (paged_attn.py:120-121)
         use_v1 = max_len <= 8192 and (nparts == 1 or B * self.H > 512)
+        tmp = es = ml = None
+        if not use_v1:
+            tmp = torch.empty((B, self.H, nparts, D), dtype=q.dtype, device=q.device)
+            es = torch.empty((B, self.H, nparts), dtype=torch.float32, device=q.device)
+            ml = torch.empty_like(es)
+        if self.fuse_attention and D == 128 and self.block_size == 16 and ops.rope_cache_paged_attention(
+                out, es, ml, tmp, q, k, v, kc, vc, positions, self.cos_sin, meta["slot_mapping"], self.Hkv, self.scale,
+                meta["block_tables"], meta["seq_lens"], self.block_size, max_len, self.kv_cache_dtype, self.kv_scale):
+            return out.view(B, self.H * D)
+        ops.rotary_embedding(positions, q, k, D, self.cos_sin, True)
+        ops.reshape_and_cache(k, v, kc, vc, meta["slot_mapping"], self.kv_cache_dtype, self.kv_scale)
         if use_v1:
             ops.paged_attention_v1(out, q, kc, vc, self.Hkv, self.scale, meta["block_tables"], meta["seq_lens"],
                                    self.block_size, max_len, None, self.kv_cache_dtype, self.kv_scale)
         else:
-            tmp = torch.empty((B, self.H, nparts, D), dtype=q.dtype, device=q.device)
-            es = torch.empty((B, self.H, nparts), dtype=torch.float32, device=q.device)
-            ml = torch.empty_like(es)
             ops.paged_attention_v2(out, es, ml, tmp, q, kc, vc, self.Hkv, self.scale, meta["block_tables"],
                                    meta["seq_lens"], self.block_size, max_len, None, self.kv_cache_dtype,
                                    self.kv_scale)
@@ -239,8 +249,7 @@ class SyntheticLlama:
                 x = h
             qkv = L["qkv"](x)
             q, k, v = qkv.split([self.q_size, self.kv_size, self.kv_size], dim=-1)
-            ops.rotary_embedding(positions, q, k, D, self.cos_sin, True)
-            a = self._attention(li, q.view(-1, self.H, D), k.view(-1, self.Hkv, D), v.view(-1, self.Hkv, D), meta)
+            a = self._attention(li, q.view(-1, self.H, D), k.view(-1, self.Hkv, D), v.view(-1, self.Hkv, D), positions, meta)
             h = self._row_parallel(L["o"], a)
             ops.fused_add_rms_norm(h, residual, L["ln2"], s.eps)
             gu = L["gate_up"](h)
@@ -282,12 +291,15 @@ class DecodeEngine:
 
     def host_inputs(self, ctx_len: int, seed=0):
         """Pinned host tensors of one synthetic decode step: every sequence has `ctx_len` tokens in the cache (incl. the
-        one being written), random block tables (collisions allowed, benchmark_paged_attention.py:62-70)."""
+        one being written), random block tables WITHOUT collisions: like the reference's block manager, no two sequences
+        of a batch own the same physical block (benchmark_paged_attention.py:62-70 draws with collisions, which makes a
+        step's result depend on kernel order as soon as it writes the cache)."""
         m, B = self.m, self.B
         g = torch.Generator().manual_seed(seed)
         nb = (ctx_len + m.block_size - 1) // m.block_size
         bt = torch.zeros((B, self.max_blocks), dtype=torch.int32)
-        bt[:, :nb] = torch.randint(0, m.num_blocks, (B, nb), generator=g, dtype=torch.int32)
+        assert B * nb <= m.num_blocks, "KV cache too small for batch x context"
+        bt[:, :nb] = torch.randperm(m.num_blocks, generator=g)[:B * nb].to(torch.int32).view(B, nb)
         pos = torch.full((B,), ctx_len - 1, dtype=torch.long)
         slot = bt[:, (ctx_len - 1) // m.block_size].long() * m.block_size + (ctx_len - 1) % m.block_size
         tok = torch.randint(0, m.shape.vocab, (B,), generator=g, dtype=torch.long)

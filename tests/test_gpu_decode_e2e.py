@@ -42,3 +42,45 @@ def test_decode_step_matches_oracle_chain(built_extension, monkeypatch, ctx):
     rows = torch.arange(ref_logits.shape[0])
     gap = ref_logits.max(dim=-1).values - ref_logits[rows, gpu_tok]
     assert float(gap.max()) <= 4 * float((gpu_logits - ref_logits).abs().max()) + 1e-6
+
+
+def test_decode_step_llama8b_shaped_two_layers(built_extension, monkeypatch):
+    """Same check on a 2-layer model with Llama-3-8B's layer geometry (hidden 4096, 32 q / 8 kv heads of 128, inter 14336):
+    the chain then runs the kernels and plans the benchmark times -- paged_attn_gqa_kernel (fused rope + cache write), the
+    qkv / o / gate_up / down Marlin GEMM plans (stream-K and cluster split-K) -- not the small-shape fallbacks."""
+    from nm_vllm_b200 import decoder
+    ops = decoder.ops
+    seen = {}
+    orig = ops.greedy_sample
+
+    def capture(logits):
+        seen["logits"] = logits.float().cpu()
+        return orig(logits)
+
+    monkeypatch.setattr(ops, "greedy_sample", capture)
+    shape = decoder.LlamaShape("llama-3-8b-2l", 4096, 14336, 32, 8, 128, 2, 2048)
+    m = decoder.SyntheticLlama(shape, device=DEV, num_blocks=64, max_pos=256)
+    fused_calls = []
+    orig_f = ops.rope_cache_paged_attention
+
+    def spy(*a, **k):
+        r = orig_f(*a, **k)
+        fused_calls.append(r)
+        return r
+
+    monkeypatch.setattr(ops, "rope_cache_paged_attention", spy)
+    for batch, ctx in ((3, 70), (64, 9)):
+        eng = decoder.DecodeEngine(m, batch=batch, max_ctx=96)
+        hi = eng.host_inputs(ctx, seed=2)
+        kv0 = [(k.cpu().clone(), v.cpu().clone()) for k, v in m.kv]
+        eng.load_inputs(hi)
+        eng._device_step(ctx)
+        torch.cuda.synchronize()
+        gpu_logits = seen["logits"]
+        ref_logits = decode_ref.decode_step_logits(m, hi, kv0)
+        err = float((gpu_logits - ref_logits).abs().mean() / ref_logits.abs().mean())
+        assert err < 2e-2, "decode-step logits (batch %d): mean relative error %g" % (batch, err)
+        # element-wise bound beside the mean: no single logit is off by more than 6 % of the logit range
+        span = float(ref_logits.max() - ref_logits.min())
+        assert float((gpu_logits - ref_logits).abs().max()) < 0.06 * span
+    assert fused_calls and all(fused_calls), "the fused attention path must have run"
