@@ -21,6 +21,10 @@
 #include <stdlib.h>
 #include <type_traits>
 
+#ifndef B200_ATTN_OCC
+#define B200_ATTN_OCC 4   // CTAs per SM the register budget is sized for: 64 seqs x 8 kv heads = 512 CTAs fit in ONE wave of 148 x 4
+#endif
+
 namespace b200 {
 namespace amma {
 
@@ -126,7 +130,7 @@ __device__ __forceinline__ uint32_t repack(uint32_t v) {
 }  // namespace amma
 
 template <typename T, int KV, bool FUSED>
-__global__ void __launch_bounds__(amma::kThreads, 3)
+__global__ void __launch_bounds__(amma::kThreads, B200_ATTN_OCC)
 paged_attn_gqa_kernel(float* __restrict__ exp_sums, float* __restrict__ max_logits, T* __restrict__ out,
                       const T* __restrict__ q, const void* __restrict__ k_cache_v, const void* __restrict__ v_cache_v,
                       int num_heads, int num_kv_heads, float scale, const int* __restrict__ block_tables,

@@ -110,7 +110,8 @@ def test_fused_vs_oracle_chain(built_extension, dtype):
     ops_ref.reshape_and_cache(kr.reshape(S, Hkv, D), c["v"].reshape(S, Hkv, D), kc, vc, c["slot"])
     assert torch.equal(kc, cache1[0]) and torch.equal(vc, cache1[1]), "cache write differs from the oracle (bit-exact for kv auto)"
     ref = ops_ref.paged_attention(qr.reshape(S, H, D), kc, vc, c["bt"], c["lens"], D ** -0.5)
-    torch.testing.assert_close(out1.float(), ref.float(), atol=2e-3, rtol=1e-5)
+    # inputs are O(1) here (not the D^-0.5 scale of the reference's attention tests): allow two ulps of the output dtype
+    torch.testing.assert_close(out1.float(), ref.float(), atol=2e-3, rtol=2 * (2.0 ** -8 if dtype == torch.bfloat16 else 2.0 ** -11))
 
 
 def test_fused_padding_slot_skips_write(built_extension):

@@ -1,0 +1,5 @@
+#!/bin/bash
+export B200_LIB_OPS=build/variants/prof/libb200ops.so
+for cfg in "4096 4096 16" "4096 6144 16" "4096 28672 64"; do
+  echo "=== $cfg"; timeout 120 python tools/gemm_trace.py $cfg 5 > /tmp/tr.log 2>&1; python tools/trace_fmt.py /tmp/tr.log | head -70; grep "gemm prof" /tmp/tr.log | tail -1
+done
