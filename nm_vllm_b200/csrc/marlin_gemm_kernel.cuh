@@ -380,7 +380,38 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     prefetch_tmap(&tmap_a);
     if (GM != kChannelwise) prefetch_tmap(&tmap_s);
   }
-  // work decomposition first: the weight producer needs its unit range before the CTA-wide sync (see below)
+  if (threadIdx.x >= 32 && threadIdx.x < 32 + Cfg::NBARS) {
+    // one barrier per thread (a serial loop over ~60 barriers costs more than a microsecond of every launch)
+    const int i = threadIdx.x - 32;
+    uint32_t cnt;
+    if (i < NW) cnt = 1;                       // wfull: the producer's expect_tx arrive
+    else if (i < 2 * NW) cnt = 8;              // wempty: 2 halves x 4 dequant quarter warps
+    else if (i < 2 * NW + NA) cnt = 1;         // actfull
+    else if (i < NR) cnt = 2 + (GM == kGroupSmall ? 8 : 0);   // actempty: the two issuers' commits (+ the 8 dequant
+                                               // warps of the two halves, which read the staged small-group scales)
+    else {
+      const int k = i - NR;
+      if (k < 2 * NOWN) cnt = 4;                              // afull: 4 dequant quarter warps
+      else if (k < 4 * NOWN) cnt = 1;                         // aempty: issuer commit
+      else if (k < 4 * NOWN + NOWN * NBUF) cnt = 1;           // accfull: issuer commit
+      else if (k < 4 * NOWN + 2 * NOWN * NBUF) cnt = Cfg::NEPI;   // accempty: every epilogue warp
+      else if (k < 4 * NOWN + 2 * NOWN * NBUF + NSC) cnt = 1;     // scfull
+      else cnt = Cfg::NEPI;                                       // scempty: every epilogue warp
+    }
+    mbar_init(bar_base + 8u * i, cnt);
+    fence_barrier_init();
+  }
+  __syncthreads();            // barriers are live: the producers start streaming weights right away
+  pdl_launch_dependents();    // the next kernel of the stream may start its own prologue now
+  // register re-balance (warpgroup-aligned roles): producers / allocator / issuers need few registers, the epilogue
+  // warps hold MPAD fp32 accumulators per thread
+  // (setmaxnreg is the first instruction of each role branch below, so that ptxas sees which code it governs)
+
+  // two work decompositions:
+  //   stream-K (cluster_s <= 1): the (tile, k-stage) space is cut into one contiguous range per CTA; shared tiles are
+  //     reduced through global scratch by the CTA that owns the tile's first stage;
+  //   cluster split-K (cluster_s = S > 1, used when there are fewer tiles than SMs): tile = blockIdx / S, the S CTAs of
+  //     one cluster take consecutive K slices of it and reduce through distributed shared memory -- no global round trip.
   const int KS = args.KS;
   const int CS = args.cluster_s;
   const bool clustered = CS > 1;
@@ -391,73 +422,6 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
   const int u_end = u_base + part.start((clustered ? c_rank : (int)blockIdx.x) + 1);
   const int n_units = u_end - u_begin;
   const int gps = args.groups_per_stage;
-  // weight-side TMA requests of unit `it` (packed weights; at g128 also the stage's two scale rows): static data, no
-  // dependence on the previous kernel of the stream
-  auto issue_weights = [&](int it, uint64_t pol_w, uint64_t pol_s, bool wait_empty) {
-    const int u = u_begin + it;
-    const int tile = u / KS, ks = u - tile * KS, nt = tile % args.n_tiles;
-    const int s = it % NW;
-    if (wait_empty && it >= NW) mbar_wait(wempty_bar(s), ((it / NW) & 1) ^ 1);
-    TRACE(9, it, 0);
-    if (elect_one()) {
-      mbar_arrive_expect_tx(wfull_bar(s), Cfg::W_STAGE_BYTES);
-      tma_2d_g2s_hint(w_base + s * Cfg::W_STAGE_BYTES, &tmap_w, nt * (Cfg::W_ROW_BYTES / 8), ks * (kStageK / 16),
-                      wfull_bar(s), pol_w);
-    }
-    __syncwarp();
-    if (GM == kGroup128) {
-      const int q = it % NSC;
-      if (wait_empty && it >= NSC) mbar_wait(scempty_bar(q), ((it / NSC) & 1) ^ 1);
-      if (elect_one()) {
-        mbar_arrive_expect_tx(scfull_bar(q), Cfg::SCQ_STAGE_BYTES);
-        tma_2d_g2s_hint(scq_base + q * Cfg::SCQ_STAGE_BYTES, &tmap_s, nt * kTileN, ks * 2, scfull_bar(q), pol_s);
-      }
-      __syncwarp();
-    }
-  };
-  constexpr int SC_BAR0 = NR + 4 * NOWN + 2 * NOWN * NBUF;   // first barrier of the scale ring
-  const int n_early = n_units < NW ? n_units : NW;           // weight stages requested BEFORE the CTA-wide sync
-  if (warp == 0) {
-    // the weight producer initialises the barriers of ITS rings itself and requests the first ring of weights right away:
-    // HBM latency (~1 us) then runs under the rest of the prologue (the other barriers, the CTA sync, the TMEM allocation)
-    for (int i = lane; i < 2 * NW; i += 32) mbar_init(bar_base + 8u * i, i < NW ? 1u : 8u);
-    for (int i = lane; i < 2 * NSC; i += 32) mbar_init(bar_base + 8u * (SC_BAR0 + i), i < NSC ? 1u : (uint32_t)Cfg::NEPI);
-    fence_barrier_init();
-    __syncwarp();
-    const uint64_t pol = policy_evict_first();
-    for (int it = 0; it < n_early; ++it) issue_weights(it, pol, pol, false);
-  } else if (threadIdx.x < 32 + Cfg::NBARS) {
-    // one barrier per thread (a serial loop over ~60 barriers costs more than a microsecond of every launch)
-    const int i = threadIdx.x - 32;
-    uint32_t cnt = 0;
-    if (i < 2 * NW) cnt = 0;                   // weight ring: initialised by warp 0 above
-    else if (i < 2 * NW + NA) cnt = 1;         // actfull
-    else if (i < NR) cnt = 2 + (GM == kGroupSmall ? 8 : 0);   // actempty: the two issuers' commits (+ the 8 dequant
-                                               // warps of the two halves, which read the staged small-group scales)
-    else {
-      const int k = i - NR;
-      if (k < 2 * NOWN) cnt = 4;                              // afull: 4 dequant quarter warps
-      else if (k < 4 * NOWN) cnt = 1;                         // aempty: issuer commit
-      else if (k < 4 * NOWN + NOWN * NBUF) cnt = 1;           // accfull: issuer commit
-      else if (k < 4 * NOWN + 2 * NOWN * NBUF) cnt = Cfg::NEPI;   // accempty: every epilogue warp
-      else cnt = 0;                                               // scale ring: initialised by warp 0 above
-    }
-    if (cnt) {
-      mbar_init(bar_base + 8u * i, cnt);
-      fence_barrier_init();
-    }
-  }
-  __syncthreads();            // every barrier is live
-  pdl_launch_dependents();    // the next kernel of the stream may start its own prologue now
-  // register re-balance (warpgroup-aligned roles): producers / allocator / issuers need few registers, the epilogue
-  // warps hold MPAD fp32 accumulators per thread
-  // (setmaxnreg is the first instruction of each role branch below, so that ptxas sees which code it governs)
-
-  // two work decompositions (computed above):
-  //   stream-K (cluster_s <= 1): the (tile, k-stage) space is cut into one contiguous range per CTA; shared tiles are
-  //     reduced through global scratch by the CTA that owns the tile's first stage;
-  //   cluster split-K (cluster_s = S > 1, used when there are fewer tiles than SMs): tile = blockIdx / S, the S CTAs of
-  //     one cluster take consecutive K slices of it and reduce through distributed shared memory -- no global round trip.
 
   // everyone but the producers needs the TMEM base address: named barrier 2 after the allocator warp's tcgen05.alloc
   auto get_tmem_base = [&]() -> uint32_t {
@@ -479,10 +443,32 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       mc = tile / args.n_tiles;
     };
     if (warp == 0) {
-      // weights do not depend on the previous kernel of the stream: no PDL wait on this path at all (the first ring was
-      // requested before the CTA-wide sync)
+      // weights do not depend on the previous kernel of the stream: no PDL wait on this path at all
       const uint64_t pol_w = policy_evict_first();   // weights are streamed exactly once
-      for (int it = n_early; it < n_units; ++it) issue_weights(it, pol_w, pol_w, true);
+      const uint64_t pol_s = policy_evict_first();
+      for (int it = 0; it < n_units; ++it) {
+        const int s = it % NW;
+        if (it >= NW) mbar_wait(wempty_bar(s), ((it / NW) & 1) ^ 1);
+        TRACE(9, it, 0);
+        int nt, mc, ks;
+        coords(it, nt, mc, ks);
+        if (elect_one()) {
+          mbar_arrive_expect_tx(wfull_bar(s), Cfg::W_STAGE_BYTES);
+          tma_2d_g2s_hint(w_base + s * Cfg::W_STAGE_BYTES, &tmap_w, nt * (Cfg::W_ROW_BYTES / 8), ks * (kStageK / 16),
+                          wfull_bar(s), pol_w);
+        }
+        __syncwarp();
+        if (GM == kGroup128) {
+          // the stage's two group-scale rows (static data like the weights) -> the epilogue's scale ring
+          const int q = it % NSC;
+          if (it >= NSC) mbar_wait(scempty_bar(q), ((it / NSC) & 1) ^ 1);
+          if (elect_one()) {
+            mbar_arrive_expect_tx(scfull_bar(q), Cfg::SCQ_STAGE_BYTES);
+            tma_2d_g2s_hint(scq_base + q * Cfg::SCQ_STAGE_BYTES, &tmap_s, nt * kTileN, ks * 2, scfull_bar(q), pol_s);
+          }
+          __syncwarp();
+        }
+      }
     } else {
       const uint64_t pol_a = policy_evict_last();    // activations / scales are re-read by every CTA
       const uint32_t tx = Cfg::A_STAGE_BYTES + (GM == kGroupSmall ? (uint32_t)gps * 256u : 0u);

@@ -223,7 +223,8 @@ class SyntheticLlama:
                 out, es, ml, tmp, q, k, v, kc, vc, positions, self.cos_sin, meta["slot_mapping"], self.Hkv, self.scale,
                 meta["block_tables"], meta["seq_lens"], self.block_size, max_len, self.kv_cache_dtype, self.kv_scale):
             return out.view(B, self.H * D)
-        ops.rotary_embedding(positions, q, k, D, self.cos_sin, True)
+        # rotary_embedding takes [tokens, heads * head_size] (pos_encoding_kernels.cu:130-141): the 2-D views of the same memory
+        ops.rotary_embedding(positions, q.view(B, self.H * D), k.view(B, self.Hkv * D), D, self.cos_sin, True)
         ops.reshape_and_cache(k, v, kc, vc, meta["slot_mapping"], self.kv_cache_dtype, self.kv_scale)
         if use_v1:
             ops.paged_attention_v1(out, q, kc, vc, self.Hkv, self.scale, meta["block_tables"], meta["seq_lens"],
