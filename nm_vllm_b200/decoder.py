@@ -55,11 +55,18 @@ class QuantLinear:
         self.kind, self.K, self.N, self.dtype = kind, K, N, dtype
         dev = device
         if kind == "w4a16":
-            self.qweight = _rand_i32((K // 16, N * 2), gen, dev)
+            # a GPTQ checkpoint as the reference loads it (qweight [K/8, N] int32 row-packed, scales [K/g, N], sequential
+            # g_idx): GPTQMarlinLinearMethod then repacks it into the Marlin layout on its first apply() -- our
+            # gptq_marlin_repack kernel + marlin_permute_scales run on the product path, nothing is fabricated in kernel layout
+            from .quantization import GPTQMarlinConfig, GPTQMarlinLinearMethod
+            self.method = GPTQMarlinLinearMethod(GPTQMarlinConfig(4, group, False, True, False))
+            self.layer = torch.nn.Module()
+            with torch.device(dev):
+                self.method.create_weights(self.layer, K, [N], K, N, dtype)
+            self.layer.qweight.data.copy_(_rand_i32((K // 8, N), gen, dev))
             ng = K // group if group > 0 else 1
-            self.scales = (torch.rand((ng, N), generator=gen, device=dev) * 0.002 + 0.003).to(dtype)
-            self.workspace = torch.zeros((N // 64) * 16, dtype=torch.int32, device=dev)
-            self.empty = torch.empty(0, dtype=torch.int32, device=dev)
+            self.layer.scales.data.copy_((torch.rand((ng, N), generator=gen, device=dev) * 0.002 + 0.003).to(dtype))
+            self.layer.g_idx.data.copy_((torch.arange(K, device=dev) // (group if group > 0 else K)).to(torch.int32))
         elif kind == "w4a16_24":
             self.qweight = _rand_i32((K // 32, N * 2), gen, dev)
             # each 4-bit quad of the metadata must be one of the six legal 2:4 codes (format_24.py:96-102)
@@ -82,10 +89,16 @@ class QuantLinear:
         else:
             raise ValueError(kind)
 
+    def __getattr__(self, name):
+        # Marlin-layout tensors of the w4a16 kind live on the LinearMethod's layer (valid after the first call)
+        if name in ("qweight", "scales") and "layer" in self.__dict__:
+            return getattr(self.__dict__["layer"], name)
+        raise AttributeError(name)
+
     def weight_bytes(self):
         K, N = self.K, self.N
         if self.kind == "w4a16":
-            return K * N // 2 + self.scales.numel() * 2
+            return K * N // 2 + self.layer.scales.numel() * 2
         if self.kind == "w4a16_24":
             return K * N // 4 + K * N // 8 + self.scales.numel() * 2
         if self.kind in ("fp8", "int8"):
@@ -95,8 +108,7 @@ class QuantLinear:
     def __call__(self, x):
         M = x.shape[0]
         if self.kind == "w4a16":
-            return ops.gptq_marlin_gemm(x, self.qweight, self.scales, self.empty, self.empty, self.workspace, 4, M,
-                                        self.N, self.K, True)
+            return self.method.apply(self.layer, x)
         if self.kind == "w4a16_24":
             return ops.gptq_marlin_24_gemm(x, self.qweight, self.meta, self.scales, self.workspace, 4, M, self.N,
                                            self.K)
