@@ -17,6 +17,79 @@ __global__ void permute_cols_kernel(T* __restrict__ out, const T* __restrict__ a
     out[m * K + k] = a[m * lda + perm[k]];
 }
 
+// ---- act-order with a partial K range (row-parallel shard of a desc_act checkpoint, is_k_full = false) ------------------
+// The shard's rows are sorted by group (gptq_marlin.py:398-407) but a group's rows are spread over the ranks, so the runs of
+// equal g_idx have arbitrary lengths and the [num_groups_of_the_FULL_K, N] scale table is indexed per ROW -- the reference
+// does this with cache_scales_chunk (gptq_marlin.cu:1416-1417).  It only arises for desc_act checkpoints under tensor
+// parallelism; this is a plain CUDA-core kernel (correct for every M, not tuned): one CTA = 64 output channels x 32 rows,
+// walks the 16-row slabs of the Marlin layout, expands a slab into shared memory with the per-row scale, FMAs in fp32.
+template <typename T, int BITS>
+__global__ void __launch_bounds__(128) marlin_actorder_partial_kernel(T* __restrict__ C, const T* __restrict__ A,
+                                                                      const uint32_t* __restrict__ B,
+                                                                      const T* __restrict__ scales,
+                                                                      const int* __restrict__ g_idx, int M, int N, int K) {
+  pdl_wait();
+  pdl_launch_dependents();
+  __shared__ float Wd[16][64 + 1];
+  __shared__ float As[32][16 + 1];
+  const int t64 = blockIdx.x, m0 = blockIdx.y * 32, tid = threadIdx.x;
+  const int n_own = tid & 63, mh = tid >> 6;
+  float acc[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) acc[i] = 0.f;
+  constexpr int WPS = 64 * 16 * BITS / 32;            // packed words of one 16 x 64 tile: 128 (4-bit) / 256 (8-bit)
+  const int words_per_row = N * 16 * BITS / 32;
+  for (int slab = 0; slab < K / 16; ++slab) {
+    const uint32_t* brow = B + (size_t)slab * words_per_row + (size_t)t64 * WPS;
+    if (BITS == 4) {
+      const uint32_t w = brow[tid];
+      const int l = tid >> 2, j = tid & 3, c = l >> 2, q = l & 3;
+#pragma unroll
+      for (int p = 0; p < 8; ++p) {
+        // nibble p: k = 2q + (p >> 2) + 8 (p & 1), n = 16 j + c + 8 ((p >> 1) & 1)   (marlin_perms.py:9-43)
+        const int k = 2 * q + (p >> 2) + 8 * (p & 1), n = 16 * j + c + 8 * ((p >> 1) & 1);
+        const int ng = t64 * 64 + n;
+        const float sc = to_f32<T>(scales[(size_t)g_idx[slab * 16 + k] * N + (ng & ~63) + 8 * (ng & 7) + ((ng & 63) >> 3)]);
+        Wd[k][n] = (float)((int)((w >> (4 * p)) & 15u) - 8) * sc;
+      }
+    } else {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int wi = tid * 2 + h;                   // [lane (8 words)][n16-tile j (2 words)][b]
+        const uint32_t w = brow[wi];
+        const int l = wi >> 3, j = (wi >> 1) & 3, b = wi & 1, c = l >> 2, q = l & 3;
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          // byte p: k = 2q + (p >> 1) + 8 (p & 1), n = 16 j + c + 8 b
+          const int k = 2 * q + (p >> 1) + 8 * (p & 1), n = 16 * j + c + 8 * b;
+          const int ng = t64 * 64 + n;
+          const float sc = to_f32<T>(scales[(size_t)g_idx[slab * 16 + k] * N + (ng & ~63) + 8 * (ng & 7) + ((ng & 63) >> 3)]);
+          Wd[k][n] = (float)((int)((w >> (8 * p)) & 255u) - 128) * sc;
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int e = tid + 128 * i, mm = e >> 4, kk = e & 15;
+      As[mm][kk] = (m0 + mm < M) ? to_f32<T>(A[(size_t)(m0 + mm) * K + slab * 16 + kk]) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < 16; ++kk) {
+      const float wv = Wd[kk][n_own];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) acc[i] = fmaf(As[mh * 16 + i][kk], wv, acc[i]);
+    }
+    __syncthreads();
+  }
+  const int n = t64 * 64 + n_own;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const int m = m0 + mh * 16 + i;
+    if (m < M && n < N) C[(size_t)m * N + n] = from_f32<T>(acc[i]);
+  }
+}
+
 // ---- per-device scratch: split-K partial slots, tile counters, act-order activation copy ---------------------------
 struct DeviceScratch {
   float* partials = nullptr;
@@ -164,9 +237,6 @@ extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_
   B200_CHECK((reinterpret_cast<uintptr_t>(a) & 15) == 0 && (lda * 2) % 16 == 0, "A must be 16-byte aligned with a 16-byte multiple row pitch");
   const bool act_order = (g_idx != nullptr && perm != nullptr);
   B200_CHECK((g_idx == nullptr) == (perm == nullptr), "g_idx and perm must both be given (act-order) or both be empty");
-  if (act_order && !is_k_full)
-    return set_error(B200_ENOTSUP, "gptq_marlin_gemm: act-order with is_k_full=False (row-parallel shard of an act-order "
-                                   "checkpoint) is not covered by the sm_100a kernel");
   if (size_m == 0 || size_n == 0) return B200_OK;
   const int gs = (int)(size_k / num_groups);
   if (num_groups > 1) B200_CHECK(gs == 32 || gs == 64 || gs == 128, "Unexpected group_size = %d", gs);
@@ -183,6 +253,22 @@ extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_
       launch_pdl(permute_cols_kernel<__nv_bfloat16>, grid, dim3(256), 0, st, (__nv_bfloat16*)tmp, (const __nv_bfloat16*)a, perm, (int)size_k, lda);
     a = tmp;
     lda = size_k;
+    if (!is_k_full) {
+      // partial K: per-row scale lookup through g_idx (see marlin_actorder_partial_kernel)
+      long long fm = 0, fn = 0;
+      ArFuse f;
+      if (ar_take_pending(&f, &fm, &fn))
+        return set_error(B200_ENOTSUP, "gptq_marlin_gemm: the fused all-reduce is not available for act-order with is_k_full=False");
+      dim3 g2((unsigned)(size_n / 64), (unsigned)((size_m + 31) / 32));
+#define AOP_GO(TT, BB)                                                                                              \
+  launch_pdl(marlin_actorder_partial_kernel<TT, BB>, g2, dim3(128), 0, st, (TT*)c, (const TT*)a, (const uint32_t*)b_q_weight, \
+             (const TT*)b_scales, g_idx, (int)size_m, (int)size_n, (int)size_k)
+      if (dtype == B200_F16) { if (num_bits == 4) AOP_GO(__half, 4); else AOP_GO(__half, 8); }
+      else { if (num_bits == 4) AOP_GO(__nv_bfloat16, 4); else AOP_GO(__nv_bfloat16, 8); }
+#undef AOP_GO
+      B200_LAUNCH_CHECK("gptq_marlin_gemm (act-order, partial K)");
+      return B200_OK;
+    }
   }
   GemmArgs ga;
   ga.B = reinterpret_cast<const uint8_t*>(b_q_weight);

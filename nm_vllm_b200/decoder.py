@@ -38,6 +38,7 @@ class LlamaShape:
 LLAMA3_8B = LlamaShape("llama-3-8b", 4096, 14336, 32, 8, 128, 32, 128256)
 LLAMA3_70B = LlamaShape("llama-3-70b", 8192, 28672, 64, 8, 128, 80, 128256)
 TINY = LlamaShape("tiny-llama", 512, 1024, 8, 2, 64, 2, 1024)
+MINI = LlamaShape("mini-llama-d128", 1024, 2048, 8, 2, 128, 2, 1024)   # head 128 + GQA: the fused attention fast path
 
 
 def _rand_i32(shape, gen, device):

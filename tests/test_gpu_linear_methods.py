@@ -39,13 +39,45 @@ def test_gptq_marlin_linear_method(built_extension, bits, group, act_order, dtyp
     out = method.apply(layer, x.to(DEV), bias.to(DEV))
     assert layer.marlin_state == GPTQMarlinState.READY and out.shape == (2, M // 2, N)
     # the repacked tensors are exactly what the oracle's own packer produces from the (group-sorted) integer weights
-    qs = ql.sort_weights(q, g_idx)[0] if act_order else q
+    # (rows of one group may come in any order: use the order the layer chose)
+    qs = q[layer.g_idx_sort_indices.cpu().long(), :].contiguous() if act_order else q
+    if act_order:
+        assert bool((layer.g_idx.cpu()[1:] >= layer.g_idx.cpu()[:-1]).all()), "g_idx must be sorted after the repack"
     assert torch.equal(layer.qweight.cpu(), ql.marlin_pack(qs, bits, ql.marlin_perm_tables(bits)[0]))
     ref = ops_ref.marlin_gemm_ref(x.reshape(-1, K), w_ref.to(dtype)).float() + bias.float()
     o = out.reshape(-1, N).cpu()
     assert ops_ref.rel_mean_err(o, ref) < 1e-2 and _elementwise_ok(o, ref)
     out2 = method.apply(layer, x.to(DEV), bias.to(DEV))     # READY state: no second repack
     assert torch.equal(out2, out)
+
+
+@pytest.mark.parametrize("bits,dtype,M", [(4, torch.float16, 5), (4, torch.bfloat16, 70), (8, torch.float16, 33)])
+def test_gptq_marlin_act_order_row_parallel_shards(built_extension, bits, dtype, M):
+    """desc_act checkpoint under tensor parallelism (gptq_marlin.py:256-263): each rank holds a K shard whose rows belong to
+    arbitrary groups, keeps ALL scale rows and runs with is_k_full=False; the sum of the two shards' outputs is the full
+    GEMM."""
+    from nm_vllm_b200.quantization import GPTQMarlinConfig, GPTQMarlinLinearMethod
+    K, N, group, tp = 1024, 256, 128, 2
+    g = torch.Generator().manual_seed(77 + bits)
+    w = (torch.randn((K, N), generator=g) * 0.05).to(dtype)
+    w_ref, q, s, g_idx, _ = ql.quantize_weights(w, bits, group, True, seed=5)
+    x = torch.randn((M, K), generator=g).to(dtype)
+    packed = ql.gptq_pack(q, bits)
+    pf = 32 // bits
+    total = torch.zeros((M, N), dtype=torch.float32)
+    for r in range(tp):
+        k0, k1 = r * K // tp, (r + 1) * K // tp
+        method = GPTQMarlinLinearMethod(GPTQMarlinConfig(bits, group, True, True, False))
+        layer = torch.nn.Module()
+        with torch.device(DEV):
+            method.create_weights(layer, K // tp, [N], K, N, dtype)
+        assert layer.is_k_full is False and layer.scales.shape[0] == K // group
+        layer.qweight.data.copy_(packed[k0 // pf:k1 // pf])
+        layer.scales.data.copy_(s.to(dtype))
+        layer.g_idx.data.copy_(g_idx[k0:k1])
+        total += method.apply(layer, x[:, k0:k1].contiguous().to(DEV)).float().cpu()
+    ref = ops_ref.marlin_gemm_ref(x, w_ref.to(dtype)).float()
+    assert ops_ref.rel_mean_err(total, ref) < 1e-2 and _elementwise_ok(total, ref)
 
 
 @pytest.mark.parametrize("bits,group", [(4, 128), (8, None)])
