@@ -59,6 +59,6 @@ for name, (K, N) in SHAPES.items():
         alg = K * N / 2 + (K / 128) * N * 2 + 2 * M * (K + N)
         gbs = alg / (med * 1e-3) / 1e9
         res[f"{name}_M{M}"] = dict(us=med * 1e3, gbs=gbs, frac=gbs / peak)
-        print(f"{name:8s} M={M:3d} K={K} N={N}: {med*1e3:8.2f} us  {gbs:7.1f} GB/s  {gbs/peak*100:5.1f}% of measured {peak:.0f}", flush=True)
+        print(f"{name:8s} M={M:3d} K={K} N={N}: {med*1e3:8.2f} us  {gbs:7.1f} GB/s  {gbs/peak*100:5.1f}% of measured {peak:.0f}" + (f"  {2*M*N*K/(med*1e-3)/1e12:7.1f} TFLOP/s" if M >= 256 else ""), flush=True)
     del ws_, ss_
 json.dump(res, open("gpurun_out/gemm_perf%s.json" % ("_hot" if HOT else ""), "w"), indent=1)

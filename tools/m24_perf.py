@@ -57,6 +57,6 @@ for name, (K, N) in SHAPES.items():
         alg = K * N / 4 + K * N / 8 + (K / 128) * N * 2 + 2 * M * (K + N)
         gbs = alg / med / 1e9
         res[f"{name}_M{M}"] = dict(us=med * 1e6, gbs=gbs, frac=gbs / peak)
-        print(f"2:4 {name:8s} M={M:3d} K={K} N={N}: {med*1e6:8.2f} us  {gbs:7.1f} GB/s  {gbs/peak*100:5.1f}% of measured {peak:.0f}", flush=True)
+        print(f"2:4 {name:8s} M={M:3d} K={K} N={N}: {med*1e6:8.2f} us  {gbs:7.1f} GB/s  {gbs/peak*100:5.1f}% of measured {peak:.0f}" + (f"  {2*M*N*K/med/1e12:7.1f} TFLOP/s" if M >= 256 else ""), flush=True)
     del qs, ms
 json.dump(res, open("gpurun_out/m24_perf.json", "w"), indent=1)
