@@ -21,15 +21,13 @@
 #include <stdlib.h>
 #include <type_traits>
 
-#ifndef B200_ATTN_OCC
-#define B200_ATTN_OCC 3   // CTAs per SM the register budget is sized for (4 measured slower: 2.91 -> 3.00 ms per step)
-#endif
 
 namespace b200 {
 namespace amma {
 
-constexpr int kWarps = 4;
-constexpr int kThreads = kWarps * 32;
+// warps per CTA is a template parameter (2, 3 or 4): at ~148 registers per thread an SM holds 3 CTAs of 4 warps, 4 of 3 or 6 of
+// 2, so the launcher picks the widest CTA whose grid still fits in ONE wave (64 sequences x 8 kv heads = 512 CTAs do not fit
+// the 444 slots of 4-warp CTAs: the 68 left-over CTAs cost a second, latency-bound wave)
 constexpr int D = 128, BS = 16, GMAX = 8;
 constexpr int kPartition = 512;
 
@@ -129,8 +127,8 @@ __device__ __forceinline__ uint32_t repack(uint32_t v) {
 
 }  // namespace amma
 
-template <typename T, int KV, bool FUSED>
-__global__ void __launch_bounds__(amma::kThreads, B200_ATTN_OCC)
+template <typename T, int KV, bool FUSED, int kWarps>
+__global__ void __launch_bounds__(kWarps * 32, kWarps == 4 ? 3 : (kWarps == 3 ? 4 : 6))
 paged_attn_gqa_kernel(float* __restrict__ exp_sums, float* __restrict__ max_logits, T* __restrict__ out,
                       const T* __restrict__ q, const void* __restrict__ k_cache_v, const void* __restrict__ v_cache_v,
                       int num_heads, int num_kv_heads, float scale, const int* __restrict__ block_tables,
@@ -138,6 +136,7 @@ paged_attn_gqa_kernel(float* __restrict__ exp_sums, float* __restrict__ max_logi
                       int64_t q_stride, int64_t kv_block_stride, int64_t kv_head_stride, int partitioned, float kv_scale,
                       const amma::RopeCacheArgs rc) {
   using namespace amma;
+  constexpr int kThreads = kWarps * 32;
   constexpr bool FP8 = KV != B200_KV_AUTO;
   constexpr bool NC = !FUSED;
   using MT = typename std::conditional<FP8, __half, T>::type;   // MMA operand type
@@ -177,8 +176,9 @@ paged_attn_gqa_kernel(float* __restrict__ exp_sums, float* __restrict__ max_logi
     // the new token's K (rotated) and V go into the cache: thread d of the CTA that owns the token's partition
     const int64_t slot = rc.slot_mapping[seq];
     const bool writer = slot >= 0 && (!partitioned || part == (seq_len - 1) / kPartition);
-    if (writer) {
-      const int d = threadIdx.x, dd = d & 63;
+    if (writer)
+    for (int d = threadIdx.x; d < D; d += kThreads) {
+      const int dd = d & 63;
       const T* krow = reinterpret_cast<const T*>(rc.key) + (int64_t)seq * rc.key_stride + (int64_t)kvh * D;
       const T x = krow[dd], y = krow[dd + 64], c = cs[dd], sn = cs[64 + dd];
       const T kr = d < 64 ? rope_x<T>(x, y, c, sn) : rope_y<T>(x, y, c, sn);
@@ -349,7 +349,7 @@ paged_attn_gqa_kernel(float* __restrict__ exp_sums, float* __restrict__ max_logi
     sm_o[warp][2 * qd + 1][16 * dm + g + 8] = o[dm][3];
   }
   __syncthreads();
-  const int d = threadIdx.x;   // kThreads == D
+  for (int d = threadIdx.x; d < D; d += kThreads)
   for (int h = 0; h < G; ++h) {
     float M = NEG;
 #pragma unroll
@@ -375,7 +375,7 @@ paged_attn_gqa_kernel(float* __restrict__ exp_sums, float* __restrict__ max_logi
 static int launch_mma_impl(float* exp_sums, float* max_logits, void* out, void* tmp_out, const void* q, const void* kc,
                            const void* vc, int num_seqs, int num_heads, int num_kv_heads, int head_size, float scale,
                            const int* block_tables, const int* seq_lens, int max_blocks_per_seq, int block_size,
-                           const float* alibi, int64_t q_stride, int64_t kvbs, int64_t kvhs, int partitioned, int num_parts,
+                           int max_seq_len, const float* alibi, int64_t q_stride, int64_t kvbs, int64_t kvhs, int partitioned, int num_parts,
                            int dtype, int kv_dtype, float kv_scale, const amma::RopeCacheArgs* rcp, cudaStream_t st) {
   using namespace amma;
   static const bool disabled = getenv("B200_ATTN_GENERIC") != nullptr;
@@ -394,10 +394,22 @@ static int launch_mma_impl(float* exp_sums, float* max_logits, void* out, void* 
   cudaError_t e = cudaSuccess;
   RopeCacheArgs rc = {};
   if (rcp) rc = *rcp;
-#define GQA_GO2(TT, KVV, FF)                                                                                            \
-  e = launch_pdl(paged_attn_gqa_kernel<TT, KVV, FF>, grid, dim3(kThreads), 0, st, exp_sums, max_logits, (TT*)dst,        \
+  // widest CTA whose grid fits in one wave (see the note at the top); beyond 6 CTAs of 2 warps per SM it is multi-wave anyway
+  const long long ctas = (long long)grid.x * grid.y * grid.z;
+  static const int force_w = getenv("B200_ATTN_WARPS") ? atoi(getenv("B200_ATTN_WARPS")) : 0;
+  // ... but only when a CTA has enough pages for bandwidth, not latency, to be the limit (>= 16 per warp of the narrow CTA):
+  // at 16 pages per CTA (ctx 256) the step measured slower with 3 warps (3.03 vs 2.91 ms), at 128 pages (ctx 2048) the
+  // kernel goes from 78 % to 91 % of the HBM rate (profiles/r2_attn_perf_warps.txt)
+  const int pages_per_cta = partitioned ? kPartition / BS : (max_seq_len + BS - 1) / BS;
+  int nw = 4;
+  if (ctas > (long long)num_sms() * 3 && pages_per_cta >= 64)
+    nw = ctas <= (long long)num_sms() * 4 ? 3 : (ctas <= (long long)num_sms() * 6 ? 2 : 4);
+  if (force_w >= 2 && force_w <= 4) nw = force_w;
+#define GQA_GO3(TT, KVV, FF, WW)                                                                                        \
+  e = launch_pdl(paged_attn_gqa_kernel<TT, KVV, FF, WW>, grid, dim3(WW * 32), 0, st, exp_sums, max_logits, (TT*)dst,     \
                  (const TT*)q, kc, vc, num_heads, num_kv_heads, scale, block_tables, seq_lens, max_blocks_per_seq, alibi, \
                  q_stride, kvbs, kvhs, partitioned, kv_scale, rc)
+#define GQA_GO2(TT, KVV, FF) do { if (nw == 4) GQA_GO3(TT, KVV, FF, 4); else if (nw == 3) GQA_GO3(TT, KVV, FF, 3); else GQA_GO3(TT, KVV, FF, 2); } while (0)
 #define GQA_GO(TT, KVV) do { if (rcp) GQA_GO2(TT, KVV, true); else GQA_GO2(TT, KVV, false); } while (0)
   if (dtype == B200_F16) {
     if (kv_dtype == B200_KV_AUTO) GQA_GO(__half, B200_KV_AUTO);
@@ -410,6 +422,7 @@ static int launch_mma_impl(float* exp_sums, float* max_logits, void* out, void* 
   }
 #undef GQA_GO
 #undef GQA_GO2
+#undef GQA_GO3
   if (e != cudaSuccess) return set_error(B200_ECUDA, "paged_attention (gqa path) launch: %s", cudaGetErrorString(e));
   return 1;
 }
@@ -419,9 +432,8 @@ int launch_mma(float* exp_sums, float* max_logits, void* out, void* tmp_out, con
                const int* block_tables, const int* seq_lens, int max_blocks_per_seq, int block_size, int max_seq_len,
                const float* alibi, int64_t q_stride, int64_t kvbs, int64_t kvhs, int partitioned, int num_parts,
                int dtype, int kv_dtype, float kv_scale, cudaStream_t st) {
-  (void)max_seq_len;
   return launch_mma_impl(exp_sums, max_logits, out, tmp_out, q, kc, vc, num_seqs, num_heads, num_kv_heads, head_size, scale,
-                         block_tables, seq_lens, max_blocks_per_seq, block_size, alibi, q_stride, kvbs, kvhs, partitioned,
+                         block_tables, seq_lens, max_blocks_per_seq, block_size, max_seq_len, alibi, q_stride, kvbs, kvhs, partitioned,
                          num_parts, dtype, kv_dtype, kv_scale, nullptr, st);
 }
 
@@ -459,8 +471,8 @@ extern "C" int b200_rope_cache_paged_attention(void* out, float* exp_sums, float
   cudaStream_t st = (cudaStream_t)stream;
   const int num_parts = use_v2 ? (max_seq_len + 511) / 512 : 1;
   int r = launch_mma_impl(exp_sums, max_logits, out, tmp_out, query, key_cache, value_cache, num_seqs, num_heads,
-                          num_kv_heads, head_size, scale, block_tables, seq_lens, max_blocks_per_seq, block_size, nullptr,
-                          q_stride, kv_block_stride, kv_head_stride, use_v2 ? 1 : 0, num_parts, dtype, kv_dtype, kv_scale,
+                          num_kv_heads, head_size, scale, block_tables, seq_lens, max_blocks_per_seq, block_size, max_seq_len,
+                          nullptr, q_stride, kv_block_stride, kv_head_stride, use_v2 ? 1 : 0, num_parts, dtype, kv_dtype, kv_scale,
                           &rc, st);
   if (r < 0) return r;
   if (r == 0) return set_error(B200_ENOTSUP, "rope_cache_paged_attention: shape outside the GQA fast path");
