@@ -186,12 +186,56 @@ def get_max_shared_memory_per_block_device_attribute(device: int) -> int:
     return torch.ops._b200_C_cuda_utils.get_max_shared_memory_per_block_device_attribute(device)
 
 
+# ---- custom all-reduce: vllm/_custom_ops.py:353-398 ---------------------------------------------------------------
+def _ar_ops():
+    load_extension()
+    return torch.ops._b200_C_custom_ar
+
+
+def init_custom_ar(meta: torch.Tensor, rank_data: torch.Tensor, handles, offsets, rank: int, full_nvlink: bool) -> int:
+    return _ar_ops().init_custom_ar(meta, rank_data, handles, offsets, rank, full_nvlink)
+
+
+def should_custom_ar(inp: torch.Tensor, max_size: int, world_size: int, full_nvlink: bool) -> bool:
+    return _ar_ops().should_custom_ar(inp, max_size, world_size, full_nvlink)
+
+
+def all_reduce_reg(fa: int, inp: torch.Tensor, out: torch.Tensor) -> None:
+    _ar_ops().all_reduce_reg(fa, inp, out)
+
+
+def all_reduce_unreg(fa: int, inp: torch.Tensor, reg_buffer: torch.Tensor, out: torch.Tensor) -> None:
+    _ar_ops().all_reduce_unreg(fa, inp, reg_buffer, out)
+
+
+def dispose(fa: int) -> None:
+    _ar_ops().dispose(fa)
+
+
+def meta_size() -> int:
+    return _ar_ops().meta_size()
+
+
+def register_buffer(fa: int, t: torch.Tensor, handles, offsets) -> None:
+    return _ar_ops().register_buffer(fa, t, handles, offsets)
+
+
+def get_graph_buffer_ipc_meta(fa: int):
+    return _ar_ops().get_graph_buffer_ipc_meta(fa)
+
+
+def register_graph_buffers(fa: int, handles, offsets) -> None:
+    _ar_ops().register_graph_buffers(fa, handles, offsets)
+
+
 _HOT_PATH_OPS = [
     "paged_attention_v1", "paged_attention_v2", "silu_and_mul", "rotary_embedding", "rms_norm", "fused_add_rms_norm",
     "marlin_gemm", "gptq_marlin_24_gemm", "cutlass_scaled_mm_supports_fp8", "cutlass_scaled_mm", "gptq_marlin_repack",
     "gptq_marlin_gemm", "scaled_fp8_quant", "scaled_int8_quant", "reshape_and_cache", "convert_fp8",
     "reshape_and_cache_flash", "copy_blocks", "swap_blocks",
     "get_device_attribute", "get_max_shared_memory_per_block_device_attribute",
+    "init_custom_ar", "should_custom_ar", "all_reduce_reg", "all_reduce_unreg", "dispose", "meta_size", "register_buffer",
+    "get_graph_buffer_ipc_meta", "register_graph_buffers",
 ]
 
 

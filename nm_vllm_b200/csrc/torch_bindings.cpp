@@ -620,8 +620,124 @@ TORCH_LIBRARY(_b200_C_cache_ops, cache_ops) {
   cache_ops.impl("convert_fp8", torch::kCUDA, &convert_fp8);
 }
 
+// ---------------------------------------------------------------- custom all-reduce (csrc/custom_all_reduce.cu:12-155)
+// The reference's op surface over this build's kernels.  Differences that follow from the design: the
+// peer-visible memory is ONE region per rank -- the `meta` tensor, which must be zero-initialised and hold
+// meta_size() + max_size bytes exactly as the reference's Python allocates it -- and inputs are pushed into the peers'
+// regions by the kernel itself, so nothing has to be registered: register_buffer / register_graph_buffers are accepted and
+// ignored, get_graph_buffer_ipc_meta returns empty lists, all_reduce_unreg does not need its staging buffer.
+using fptr_t = int64_t;
+struct ArHandle {
+  int64_t ctx;
+  std::vector<void*> opened;
+};
+
+int64_t meta_size() {
+  int64_t b = 0;
+  raise_if(b200_ar_region_bytes(8, 8192 * 1024, &b), "meta_size");
+  return b;   // covers every world <= 8 at the reference's default max_size of 8 MiB
+}
+
+fptr_t init_custom_ar(torch::Tensor& meta, torch::Tensor& rank_data, const std::vector<std::string>& handles,
+                      const std::vector<int64_t>& offsets, int64_t rank, bool full_nvlink) {
+  (void)rank_data; (void)full_nvlink;
+  const int world = (int)offsets.size();
+  if (world > 8) throw std::invalid_argument("world size > 8 is not supported");
+  if (world % 2 != 0) throw std::invalid_argument("Odd num gpus is not supported for now");
+  if (world != (int)handles.size()) throw std::invalid_argument("handles length should equal to offsets length");
+  if (rank < 0 || rank >= world) throw std::invalid_argument("invalid rank passed in");
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(meta));
+  // largest payload whose region fits into `meta`
+  const int64_t have = meta.numel() * meta.element_size();
+  int64_t lo = 4096, hi = have, need = 0;
+  raise_if(b200_ar_region_bytes(world, lo, &need), "init_custom_ar");
+  TORCH_CHECK(need <= have, "init_custom_ar: meta holds ", have, " bytes, the smallest region needs ", need);
+  while (hi - lo > 4096) {
+    const int64_t mid = (lo + hi) / 2 / 4096 * 4096;
+    raise_if(b200_ar_region_bytes(world, mid, &need), "init_custom_ar");
+    if (need <= have) lo = mid; else hi = mid;
+  }
+  auto* h = new ArHandle();
+  std::vector<void*> regions(world);
+  for (int r = 0; r < world; ++r) {
+    if (r == rank) {
+      regions[r] = meta.data_ptr();
+    } else {
+      TORCH_CHECK(handles[r].size() >= 64, "init_custom_ar: IPC handle of rank ", r, " is shorter than 64 bytes");
+      void* base = nullptr;
+      raise_if(b200_ar_open(handles[r].data(), &base), "init_custom_ar");
+      h->opened.push_back(base);
+      regions[r] = static_cast<char*>(base) + offsets[r];
+    }
+  }
+  raise_if(b200_ar_init((int)rank, world, regions.data(), lo, &h->ctx), "init_custom_ar");
+  return reinterpret_cast<fptr_t>(h);
+}
+
+bool should_custom_ar(torch::Tensor& inp, int64_t max_size, int64_t world_size, bool full_nvlink) {
+  const int64_t bytes = inp.numel() * inp.element_size();
+  if (bytes % 16 != 0) return false;
+  const bool weak_contig = inp.is_contiguous() ||
+      (int64_t)(inp.storage().nbytes() - inp.storage_offset() * inp.element_size()) == bytes;
+  if (!weak_contig) return false;
+  if (world_size == 2 || full_nvlink) return bytes <= max_size;
+  return false;
+}
+
+void all_reduce_reg(fptr_t fa, torch::Tensor& inp, torch::Tensor& out) {
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(inp));
+  TORCH_CHECK(inp.scalar_type() == out.scalar_type() && inp.numel() == out.numel());
+  auto* h = reinterpret_cast<ArHandle*>(fa);
+  raise_if(b200_ar_all_reduce(h->ctx, inp.data_ptr(), out.data_ptr(), inp.numel(), dtype_enum(inp.scalar_type(), "all_reduce_reg"),
+                              cur_stream(inp)),
+           "all_reduce_reg");
+}
+
+void all_reduce_unreg(fptr_t fa, torch::Tensor& inp, torch::Tensor& reg_buffer, torch::Tensor& out) {
+  (void)reg_buffer;   // the kernel reads `inp` locally and pushes it to the peers: no staging copy
+  all_reduce_reg(fa, inp, out);
+}
+
+void dispose(fptr_t fa) {
+  auto* h = reinterpret_cast<ArHandle*>(fa);
+  b200_ar_dispose(h->ctx);
+  for (void* p : h->opened) b200_ar_close(p);
+  delete h;
+}
+
+void register_buffer(fptr_t fa, torch::Tensor& t, const std::vector<std::string>& handles, const std::vector<int64_t>& offsets) {
+  (void)fa; (void)t; (void)handles; (void)offsets;
+}
+
+std::tuple<torch::Tensor, std::vector<int64_t>> get_graph_buffer_ipc_meta(fptr_t fa) {
+  (void)fa;
+  return {torch::empty({0}, torch::TensorOptions().dtype(torch::kUInt8).device(torch::kCPU)), std::vector<int64_t>()};
+}
+
+void register_graph_buffers(fptr_t fa, const std::vector<std::string>& handles, const std::vector<std::vector<int64_t>>& offsets) {
+  (void)fa; (void)handles; (void)offsets;
+}
+
 TORCH_LIBRARY(_b200_C_cuda_utils, cuda_utils) {
   // no tensor arguments -> no backend key to dispatch on: the def() catch-all kernel is the implementation
   cuda_utils.def("get_device_attribute", &get_device_attribute);
   cuda_utils.def("get_max_shared_memory_per_block_device_attribute", &get_max_shared_memory_per_block_device_attribute);
+}
+
+TORCH_LIBRARY(_b200_C_custom_ar, custom_ar) {
+  // same names / schema strings as csrc/torch_bindings.cpp:262-294
+  custom_ar.def("init_custom_ar", &init_custom_ar);
+  custom_ar.impl("init_custom_ar", torch::kCUDA, &init_custom_ar);
+  custom_ar.def("should_custom_ar", &should_custom_ar);
+  custom_ar.impl("should_custom_ar", torch::kCUDA, &should_custom_ar);
+  custom_ar.def("all_reduce_reg(int fa, Tensor inp, Tensor! out) -> ()");
+  custom_ar.impl("all_reduce_reg", torch::kCUDA, &all_reduce_reg);
+  custom_ar.def("all_reduce_unreg(int fa, Tensor inp, Tensor reg_buffer, Tensor! out) -> ()");
+  custom_ar.impl("all_reduce_unreg", torch::kCUDA, &all_reduce_unreg);
+  custom_ar.def("dispose", &dispose);
+  custom_ar.def("meta_size", &meta_size);
+  custom_ar.def("register_buffer", &register_buffer);
+  custom_ar.impl("register_buffer", torch::kCUDA, &register_buffer);
+  custom_ar.def("get_graph_buffer_ipc_meta", &get_graph_buffer_ipc_meta);
+  custom_ar.def("register_graph_buffers", &register_graph_buffers);
 }

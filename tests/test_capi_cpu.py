@@ -38,6 +38,45 @@ def test_torch_schemas_match_reference(built_extension):
         assert hasattr(torch.ops._b200_C, name)
 
 
+def _reference_schema_strings():
+    """every op the reference registers with an explicit schema string (ops.def("name(args) -> ret")), by library"""
+    import os
+    import re
+    path = os.path.join(os.environ.get("B200_REFERENCE_ROOT", "/root/reference"), "csrc", "torch_bindings.cpp")
+    if not os.path.exists(path):
+        return None
+    txt = open(path).read()
+    out = {}
+    for m in re.finditer(r"(\w+)\.def\(\s*((?:\"(?:[^\"\\\\]|\\\\.)*\"\s*)+)\)", txt):
+        lib, lit = m.group(1), "".join(re.findall(r"\"((?:[^\"\\\\]|\\\\.)*)\"", m.group(2)))
+        lit = " ".join(lit.split())
+        if "(" in lit:
+            out.setdefault(lib, {})[lit.split("(")[0].strip()] = lit
+    return out
+
+
+def test_torch_schemas_equal_reference_strings(built_extension):
+    """Every schema string this repo registers for a hot-path op parses to EXACTLY the schema the reference's
+    csrc/torch_bindings.cpp declares (argument names, types, mutability annotations, order, return)."""
+    ref = _reference_schema_strings()
+    if ref is None:
+        pytest.skip("reference tree not present")
+    libs = {"ops": torch.ops._b200_C, "cache_ops": torch.ops._b200_C_cache_ops, "custom_ar": torch.ops._b200_C_custom_ar}
+    checked = 0
+    for lib, mine in libs.items():
+        for name, lit in ref.get(lib, {}).items():
+            if not hasattr(mine, name):
+                continue
+            want = torch._C.parse_schema("x::" + lit)
+            got = getattr(mine, name).default._schema
+            assert str(got).split("::", 1)[1] == str(want).split("::", 1)[1], (name, str(got), str(want))
+            checked += 1
+    assert checked >= 12, checked
+    for name in ["init_custom_ar", "should_custom_ar", "all_reduce_reg", "all_reduce_unreg", "dispose", "meta_size",
+                 "register_buffer", "get_graph_buffer_ipc_meta", "register_graph_buffers"]:
+        assert hasattr(torch.ops._b200_C_custom_ar, name), name
+
+
 def test_custom_ops_mirror_signatures(built_extension):
     import inspect
 
