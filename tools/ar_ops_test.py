@@ -17,9 +17,16 @@ dev = torch.device("cuda", torch.cuda.current_device())
 dist.init_process_group("nccl", device_id=dev)
 max_size = 1024 * 1024
 meta = torch.zeros(ops.meta_size() + max_size, dtype=torch.uint8, device=dev)
-# IPC handle + offset of the tensor's allocation (what the reference's _get_ipc_meta does)
-share = meta.untyped_storage()._share_cuda_()
-handle, offset = share[1], share[3]
+# IPC handle + offset of the tensor's allocation (what the reference's _get_ipc_meta obtains through torch's storage
+# sharing; taken from the CUDA runtime / driver directly here so that the test does not depend on torch's handle format)
+import ctypes
+rt = ctypes.CDLL("libcudart.so.12") if os.path.exists("/usr/local/cuda/lib64/libcudart.so.12") else ctypes.CDLL("libcudart.so")
+drv = ctypes.CDLL("libcuda.so.1")
+base, size = ctypes.c_uint64(), ctypes.c_size_t()
+assert drv.cuMemGetAddressRange_v2(ctypes.byref(base), ctypes.byref(size), ctypes.c_uint64(meta.data_ptr())) == 0
+hbuf = ctypes.create_string_buffer(64)
+assert rt.cudaIpcGetMemHandle(hbuf, ctypes.c_void_p(base.value)) == 0
+handle, offset = hbuf.raw, meta.data_ptr() - base.value
 gathered = [None] * world
 dist.all_gather_object(gathered, (bytes(handle), int(offset)))
 handles, offsets = [g[0] for g in gathered], [g[1] for g in gathered]
