@@ -101,9 +101,35 @@ class PagedAttention:
         return output if ok else None
 
     @staticmethod
-    def forward_prefix(*args, **kwargs) -> torch.Tensor:
-        raise NotImplementedError("prefill attention over a cached prefix (vllm/attention/ops/prefix_prefill.py) is outside the "
-                                  "decode hot path of this build (SURVEY 8f rank 4)")
+    def forward_prefix(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, key_cache: torch.Tensor,
+                       value_cache: torch.Tensor, block_tables: torch.Tensor, query_start_loc: torch.Tensor,
+                       seq_lens_tensor: torch.Tensor, context_lens: torch.Tensor, max_query_len: int,
+                       alibi_slopes: Optional[torch.Tensor], sliding_window: Optional[int], kv_cache_dtype: str = "auto",
+                       kv_scale: float = 1.0, scale: Optional[float] = None) -> torch.Tensor:
+        """Prefill over a cached prefix (paged_attn.py:185-211 -> context_attention_fwd, prefix_prefill.py:674): query token i of
+        a sequence attends to the sequence's first context_len + i + 1 tokens.  The reference has already written the new
+        tokens' K / V into the paged cache at this point (write_to_paged_cache runs first, xformers.py:262-270), so causal
+        prefill IS paged decode attention with one row per QUERY TOKEN: same block-table row, seq_len = context_len + i + 1.
+        That is what this does, through paged_attention_v1 / v2 -- exact, but every query token re-reads its KV prefix
+        (served by L2 for neighbouring tokens): a functional path, not a tuned prefill kernel.  `key` / `value` are unused
+        (already in the cache); the reference's trailing arguments are extended with the cache dtype / scale it leaves implicit."""
+        del key, value, max_query_len
+        if sliding_window is not None:
+            raise NotImplementedError("sliding-window prefix attention")
+        num_tokens, num_heads, head_size = query.shape
+        num_kv_heads = value_cache.shape[1]
+        if scale is None:
+            scale = float(head_size) ** -0.5
+        starts = query_start_loc.to(torch.int64)
+        q_lens = (seq_lens_tensor - context_lens).to(torch.int64)
+        seq_of_tok = torch.repeat_interleave(torch.arange(q_lens.numel(), device=query.device), q_lens, output_size=num_tokens)
+        pos_in_q = torch.arange(num_tokens, device=query.device) - starts[:-1][seq_of_tok] if starts.numel() == q_lens.numel() + 1 \
+            else torch.arange(num_tokens, device=query.device) - starts[seq_of_tok]
+        tok_lens = (context_lens.to(torch.int64)[seq_of_tok] + pos_in_q + 1).to(torch.int32)
+        tok_tables = block_tables.index_select(0, seq_of_tok).contiguous()
+        max_len = int(seq_lens_tensor.max().item())
+        return PagedAttention.forward_decode(query, key_cache, value_cache, tok_tables, tok_lens, max_len, kv_cache_dtype,
+                                             num_kv_heads, scale, alibi_slopes, kv_scale)
 
     @staticmethod
     def swap_blocks(src_kv_cache: torch.Tensor, dst_kv_cache: torch.Tensor, src_to_dst: torch.Tensor) -> None:

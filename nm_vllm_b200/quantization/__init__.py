@@ -5,6 +5,7 @@ from .compressed_tensors import (CompressedTensorsConfig, CompressedTensorsLinea
 from .fp8 import Fp8Config, Fp8KVCacheMethod, Fp8LinearMethod
 from .gptq_marlin import GPTQMarlinConfig, GPTQMarlinLinearMethod, GPTQMarlinState
 from .layouts import get_scale_perms, marlin_permute_scales
+from . import sparse24
 from .marlin import GPTQMarlin24Config, GPTQMarlin24LinearMethod, MarlinConfig, MarlinLinearMethod
 
 QUANTIZATION_METHODS = {

@@ -232,3 +232,36 @@ def test_paged_decode_backend_forward(built_extension, kv_dtype):
     with pytest.raises(NotImplementedError):
         md.num_prefill_tokens = 1
         impl.forward(q.to(DEV), k.to(DEV), v.to(DEV), kv_d, md, kv_scale)
+
+
+def test_forward_prefix_matches_causal_reference(built_extension):
+    """PagedAttention.forward_prefix: new tokens (already written to the cache) attend causally to the cached prefix + themselves."""
+    from nm_vllm_b200.attention import PagedAttention
+    H, Hkv, D, BS, NB, dtype = 8, 2, 128, 16, 64, torch.float16
+    ctx, qlen = [20, 0, 33], [5, 17, 1]
+    S = len(ctx)
+    g = torch.Generator().manual_seed(8)
+    tot = [c + q for c, q in zip(ctx, qlen)]
+    kc = (torch.randn((NB, Hkv, D // 8, BS, 8), generator=g) * 0.3).to(dtype)
+    vc = (torch.randn((NB, Hkv, D, BS), generator=g) * 0.3).to(dtype)
+    maxb = (max(tot) + BS - 1) // BS
+    perm = torch.randperm(NB, generator=g)
+    bt = torch.zeros((S, maxb), dtype=torch.int32)
+    o = 0
+    for s_ in range(S):
+        nb = (tot[s_] + BS - 1) // BS
+        bt[s_, :nb] = perm[o:o + nb].to(torch.int32)
+        o += nb
+    T = sum(qlen)
+    q = (torch.randn((T, H, D), generator=g) * 0.3).to(dtype)
+    start = torch.tensor([0] + list(torch.tensor(qlen).cumsum(0)), dtype=torch.int32)
+    out = PagedAttention.forward_prefix(q.to(DEV), None, None, kc.to(DEV), vc.to(DEV), bt.to(DEV), start.to(DEV),
+                                        torch.tensor(tot, dtype=torch.int32, device=DEV), torch.tensor(ctx, dtype=torch.int32, device=DEV),
+                                        max(qlen), None, None).cpu()
+    # oracle: one paged-attention row per query token with its causal length
+    rows_bt, rows_len = [], []
+    for s_ in range(S):
+        for i in range(qlen[s_]):
+            rows_bt.append(bt[s_]); rows_len.append(ctx[s_] + i + 1)
+    ref = ops_ref.paged_attention(q, kc, vc, torch.stack(rows_bt), torch.tensor(rows_len, dtype=torch.int32), D ** -0.5)
+    torch.testing.assert_close(out.float(), ref.float(), atol=2e-3, rtol=2e-3)

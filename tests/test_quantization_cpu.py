@@ -298,3 +298,36 @@ def test_install_rebinds_vllm_custom_ops(monkeypatch):
     for n in ("gptq_marlin_gemm", "paged_attention_v1", "reshape_and_cache", "cutlass_scaled_mm", "scaled_fp8_quant"):
         assert getattr(fake_ops, n) is getattr(ours, n)
         assert n in done
+
+
+def test_sparse24_helpers_bit_exact_against_reference_golden():
+    """product-side 2:4 compression / metadata reorder / Marlin-24 packing against vectors the REFERENCE's own utilities
+    produced (oracle/make_golden.py)"""
+    from nm_vllm_b200.quantization import sparse24
+    from tests.util import as_torch, golden, golden_files
+    files = golden_files("marlin24_")
+    assert files
+    for f in files:
+        g = golden(f)
+        K, N, bits, group = int(g["K"]), int(g["N"]), int(g["bits"]), int(g["group"])
+        q24 = as_torch(g["q_w_24"])
+        comp, meta = sparse24.compress_quantized_24_weight(q24, K, N, bits)
+        assert torch.equal(comp, as_torch(g["comp_plain"]).to(torch.int32)), f
+        assert torch.equal(meta, as_torch(g["meta"])), f
+        assert torch.equal(sparse24.marlin_24_pack(comp, bits), as_torch(g["q_comp"])), f
+    tabs = golden("perm_tables.npz")
+    for bits in (4, 8):
+        perm, sp, sps = sparse24.get_perms_24(bits)
+        assert perm.tolist() == as_torch(tabs["perm24_%d" % bits]).tolist()
+        assert sp == as_torch(tabs["scale_perm24_%d" % bits]).tolist() and sps == as_torch(tabs["scale_perm_single24_%d" % bits]).tolist()
+
+
+def test_sparse24_quantize_matches_oracle():
+    from nm_vllm_b200.quantization import sparse24
+    w = (torch.randn((256, 128), generator=torch.Generator().manual_seed(4)) * 0.05).to(torch.float16)
+    a = sparse24.marlin_24_quantize(w, 4, 128)
+    b = ql.marlin_24_quantize(w, 4, 128)
+    for x, y in zip(a, b):
+        assert torch.equal(x, y.to(x.dtype))
+    mask = sparse24.mask_2_of_4(w.t().contiguous())
+    assert bool((mask.reshape(-1, 4).sum(1) == 2).all())
