@@ -34,7 +34,7 @@ def parse():
     p.add_argument("--batch", type=int, default=64)
     p.add_argument("--ctx", type=int, default=256)
     p.add_argument("--model", default="llama-3-8b", choices=["llama-3-8b", "llama-3-70b", "tiny"])
-    p.add_argument("--quant", default="w4a16", choices=["w4a16", "w4a16_24", "fp8", "int8"])
+    p.add_argument("--quant", default="w4a16", choices=["w4a16", "w4a16_24", "fp8", "fp8_static", "int8"])
     p.add_argument("--kv", default="auto", choices=["auto", "fp8", "fp8_e5m2"])
     p.add_argument("--layers", type=int, default=None, help="debug: truncate the model (makes the number INVALID)")
     p.add_argument("--allreduce", default="auto", choices=["auto", "custom", "nccl"],
@@ -136,6 +136,7 @@ _OUR_KERNELS_PER_CALL = {  # CUDA launches of OUR kernels behind one operator ca
     "paged_attention_v1": 1, "paged_attention_v2": 2, "gptq_marlin_gemm": 1, "gptq_marlin_24_gemm": 1,
     "cutlass_scaled_mm": 1, "scaled_fp8_quant": 2, "scaled_int8_quant": 1, "greedy_sample": 1,
     "rope_cache_paged_attention": 1,   # + the v2 merge kernel when exp_sums is given (counted in the wrapper)
+    "rms_norm_quant": 1, "silu_and_mul_quant": 1,
 }
 
 
@@ -152,6 +153,9 @@ def count_launches(fn):
             if __n == "rope_cache_paged_attention":
                 if r:   # False = nothing launched (shape outside the fast path)
                     counts[__n] = counts.get(__n, 0) + (2 if args[1] is not None else 1)
+            elif __n == "scaled_fp8_quant":   # dynamic: absmax + convert; static scale given: one kernel
+                static = (len(args) > 1 and args[1] is not None) or kw.get("scale") is not None
+                counts[__n] = counts.get(__n, 0) + (1 if static else 2)
             else:
                 counts[__n] = counts.get(__n, 0) + __p
             return r
@@ -437,7 +441,9 @@ def run_b200(a):
         extra = {}
         del eng
         for label, quant, kv in (("llama-3-70b w4a16 g128, kv auto", "w4a16", "auto"),
-                                 ("llama-3-70b w8a8 fp8 (cutlass_scaled_mm), kv fp8", "fp8", "fp8")):
+                                 ("llama-3-70b w8a8 fp8 (cutlass_scaled_mm), dynamic per-tensor activation scale, kv fp8", "fp8", "fp8"),
+                                 ("llama-3-70b w8a8 fp8 (cutlass_scaled_mm), static activation scales fused into norm/silu, kv fp8",
+                                  "fp8_static", "fp8")):
             try:
                 extra[label] = time_extra_model(a, decoder, decoder.LLAMA3_70B, quant, kv, dev, world, rank, model.custom_ar,
                                                 max(5, a.steps // 2))

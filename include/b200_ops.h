@@ -157,6 +157,16 @@ int b200_fused_add_rms_norm(void* input, void* residual, const void* weight, int
                             int hidden_size, float epsilon, int dtype, void* stream);
 int b200_silu_and_mul(void* out, const void* input, int64_t num_tokens, int d, int dtype,
                       void* stream);
+/* ---- glue fused with the activation quantiser of the following W8A8 linear (new): the 16-bit result of
+ * rms_norm / fused_add_rms_norm (csrc/layernorm_kernels.cu:22-352) or silu_and_mul (csrc/activation_kernels.cu:14-162) is
+ * quantised in the same kernel exactly like static_scaled_fp8_quant (csrc/quantization/fp8/common.cu:74-125) or
+ * static / dynamic_scaled_int8_quant (compressed_tensors/int8_quant_kernels.cu:30-71) would -- bit-identical to the two-op
+ * chain.  qkind 1: fp8 e4m3, static per-tensor scale *scales; 2: int8, static per-tensor scale *scales; 3: int8, dynamic
+ * per-token scales WRITTEN to scales[num_tokens].  residual != NULL: fused_add_rms_norm (residual updated in place). */
+int b200_rms_norm_quant(void* out_q, float* scales, const void* input, void* residual, const void* weight,
+                        int64_t num_tokens, int hidden_size, float epsilon, int dtype, int qkind, void* stream);
+int b200_silu_and_mul_quant(void* out_q, float* scales, const void* input, int64_t num_tokens, int d, int dtype,
+                            int qkind, void* stream);
 /* positions int64 [T]; query [T, Hq*D] / key [T, Hkv*D] rotated in place; cos_sin_cache [max_pos, rot_dim] */
 int b200_rotary_embedding(const int64_t* positions, void* query, void* key, int head_size,
                           const void* cos_sin_cache, int rot_dim, int is_neox, int64_t num_tokens,

@@ -69,6 +69,31 @@ def rope_cache_paged_attention(out: torch.Tensor, exp_sums: Optional[torch.Tenso
                                              block_tables, seq_lens, block_size, max_seq_len, kv_cache_dtype, kv_scale)
 
 
+_Q_DTYPE = {"fp8": torch.float8_e4m3fn, "int8": torch.int8, "int8_token": torch.int8}
+
+
+def rms_norm_quant(input: torch.Tensor, weight: torch.Tensor, epsilon: float, kind: str, scale: Optional[torch.Tensor] = None,
+                   residual: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """rms_norm (residual is None) or fused_add_rms_norm (residual updated in place) fused with the activation quantiser of the
+    W8A8 linear that consumes it; returns (quantised activations, scales) like scaled_fp8_quant / scaled_int8_quant.
+    kind "fp8" / "int8": `scale` is the static per-tensor scale; "int8_token": dynamic per-token scales are produced."""
+    out = torch.empty(input.shape, dtype=_Q_DTYPE[kind], device=input.device)
+    if kind == "int8_token":
+        scale = torch.empty((input.numel() // input.shape[-1], 1), dtype=torch.float32, device=input.device)
+    _ops().rms_norm_quant(out, scale, input, residual, weight, epsilon, kind)
+    return out, scale
+
+
+def silu_and_mul_quant(x: torch.Tensor, kind: str, scale: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """silu_and_mul fused with the activation quantiser of the following W8A8 linear (see rms_norm_quant)."""
+    d = x.shape[-1] // 2
+    out = torch.empty(x.shape[:-1] + (d,), dtype=_Q_DTYPE[kind], device=x.device)
+    if kind == "int8_token":
+        scale = torch.empty((x.numel() // x.shape[-1], 1), dtype=torch.float32, device=x.device)
+    _ops().silu_and_mul_quant(out, scale, x, kind)
+    return out, scale
+
+
 def silu_and_mul(out: torch.Tensor, x: torch.Tensor) -> None:
     _ops().silu_and_mul(out, x)
 

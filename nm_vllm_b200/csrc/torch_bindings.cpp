@@ -92,6 +92,40 @@ void paged_attention_v2(torch::Tensor& out, torch::Tensor& exp_sums, torch::Tens
            "paged_attention_v2");
 }
 
+// norm / activation fused with the activation quantiser of the following W8A8 linear.  kind: "fp8" (static per-tensor scale),
+// "int8" (static per-tensor scale), "int8_token" (dynamic per-token scales, written to `scales` [tokens, 1])
+static int qkind_enum(const std::string& kind) {
+  if (kind == "fp8") return 1;
+  if (kind == "int8") return 2;
+  if (kind == "int8_token") return 3;
+  TORCH_CHECK(false, "unknown quantisation kind: ", kind);
+  return 0;
+}
+void rms_norm_quant(torch::Tensor& out_q, torch::Tensor& scales, torch::Tensor& input, const std::optional<torch::Tensor>& residual,
+                    torch::Tensor& weight, double epsilon, const std::string& kind) {
+  TORCH_CHECK(input.is_contiguous() && out_q.is_contiguous() && scales.scalar_type() == at::ScalarType::Float);
+  TORCH_CHECK(out_q.element_size() == 1 && out_q.numel() == input.numel(), "out_q must be a 1-byte tensor of input's shape");
+  const int qk = qkind_enum(kind);
+  const int64_t hidden = input.size(-1), tokens = input.numel() / hidden;
+  TORCH_CHECK(qk != 3 || scales.numel() >= tokens, "int8_token: scales must hold one float per token");
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(input));
+  raise_if(b200_rms_norm_quant(out_q.data_ptr(), scales.data_ptr<float>(), input.data_ptr(),
+                               residual ? residual->data_ptr() : nullptr, weight.data_ptr(), tokens, (int)hidden, (float)epsilon,
+                               dtype_enum(input.scalar_type(), "rms_norm_quant"), qk, cur_stream(input)),
+           "rms_norm_quant");
+}
+void silu_and_mul_quant(torch::Tensor& out_q, torch::Tensor& scales, torch::Tensor& input, const std::string& kind) {
+  TORCH_CHECK(input.is_contiguous() && out_q.is_contiguous() && scales.scalar_type() == at::ScalarType::Float);
+  const int qk = qkind_enum(kind);
+  const int64_t d = input.size(-1) / 2, tokens = input.numel() / input.size(-1);
+  TORCH_CHECK(out_q.element_size() == 1 && out_q.numel() == tokens * d, "out_q must be a 1-byte tensor [tokens, d]");
+  TORCH_CHECK(qk != 3 || scales.numel() >= tokens, "int8_token: scales must hold one float per token");
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(input));
+  raise_if(b200_silu_and_mul_quant(out_q.data_ptr(), scales.data_ptr<float>(), input.data_ptr(), tokens, (int)d,
+                                   dtype_enum(input.scalar_type(), "silu_and_mul_quant"), qk, cur_stream(input)),
+           "silu_and_mul_quant");
+}
+
 // fused rotary_embedding + reshape_and_cache + paged_attention_v1/v2 (decode); returns false when the shape is outside the
 // fast path and NOTHING was launched (the caller then runs the three reference ops)
 bool rope_cache_paged_attention(torch::Tensor& out, const std::optional<torch::Tensor>& exp_sums,
@@ -552,6 +586,10 @@ TORCH_LIBRARY(_b200_C, ops) {
       " Tensor slot_mapping, int num_kv_heads, float scale, Tensor block_tables, Tensor seq_lens, int block_size,"
       " int max_seq_len, str kv_cache_dtype, float kv_scale) -> bool");
   ops.impl("rope_cache_paged_attention", torch::kCUDA, &rope_cache_paged_attention);
+  ops.def("rms_norm_quant(Tensor! out_q, Tensor! scales, Tensor input, Tensor!? residual, Tensor weight, float epsilon, str kind) -> ()");
+  ops.impl("rms_norm_quant", torch::kCUDA, &rms_norm_quant);
+  ops.def("silu_and_mul_quant(Tensor! out_q, Tensor! scales, Tensor input, str kind) -> ()");
+  ops.impl("silu_and_mul_quant", torch::kCUDA, &silu_and_mul_quant);
   ops.def("greedy_sample(Tensor! out, Tensor logits) -> ()");
   ops.impl("greedy_sample", torch::kCUDA, &greedy_sample);
   ops.def("silu_and_mul(Tensor! out, Tensor input) -> ()");

@@ -78,8 +78,12 @@ class QuantLinear:
             ng = K // group if group > 0 else 1
             self.scales = (torch.rand((ng, N), generator=gen, device=dev) * 0.002 + 0.003).to(torch.float16)
             self.workspace = torch.zeros((N // 128) * 64, dtype=torch.int32, device=dev)
-        elif kind in ("fp8", "int8"):
-            if kind == "fp8":
+        elif kind in ("fp8", "fp8_static", "int8"):
+            # fp8: dynamic per-tensor activation scale (Fp8Config activation_scheme "dynamic", two-kernel quantiser);
+            # fp8_static: activation_scheme "static" (input_scale from the checkpoint) -> the quantiser fuses into the
+            # producing norm / activation kernel; int8: compressed-tensors W8A8 dynamic per-token, fuses as well
+            self.input_scale = torch.full((1,), 0.05, dtype=torch.float32, device=dev) if kind == "fp8_static" else None
+            if kind in ("fp8", "fp8_static"):
                 w = (torch.randn((N, K), generator=gen, device=dev) * 0.02 / 0.0005).clamp(-448, 448)
                 self.weight = w.to(torch.float8_e4m3fn).t()      # column-major [K, N] view (fp8.py:262-270)
             else:
@@ -102,7 +106,7 @@ class QuantLinear:
             return K * N // 2 + self.layer.scales.numel() * 2
         if self.kind == "w4a16_24":
             return K * N // 4 + K * N // 8 + self.scales.numel() * 2
-        if self.kind in ("fp8", "int8"):
+        if self.kind in ("fp8", "fp8_static", "int8"):
             return K * N
         return K * N * 2
 
@@ -113,13 +117,21 @@ class QuantLinear:
         if self.kind == "w4a16_24":
             return ops.gptq_marlin_24_gemm(x, self.qweight, self.meta, self.scales, self.workspace, 4, M, self.N,
                                            self.K)
-        if self.kind == "fp8":
-            xq, xs = ops.scaled_fp8_quant(x)
+        if self.kind in ("fp8", "fp8_static"):
+            xq, xs = ops.scaled_fp8_quant(x, self.input_scale)
             return ops.cutlass_scaled_mm(xq, self.weight, xs, self.weight_scale, self.dtype)
         if self.kind == "int8":
             xq, xs = ops.scaled_int8_quant(x)
             return ops.cutlass_scaled_mm(xq, self.weight, xs, self.weight_scale, self.dtype)
         return torch.matmul(x, self.weight.t())
+
+    # ---- W8A8 with the activation quantiser fused into the producing kernel (fp8_static / int8) ----------------------
+    @property
+    def fused_quant_kind(self):
+        return {"fp8_static": "fp8", "int8": "int8_token"}.get(self.kind)
+
+    def mm_quantized(self, xq, xs):
+        return ops.cutlass_scaled_mm(xq, self.weight, xs, self.weight_scale, self.dtype)
 
 
 class SyntheticLlama:
@@ -135,6 +147,7 @@ class SyntheticLlama:
         self.custom_ar = None  # CustomAllreduce once enable_custom_all_reduce() has been called
         self.n_custom_ar_calls = 0  # stand-alone all-reduce kernel launches (bench.py counts them per step)
         self.fuse_gemm_all_reduce = True  # row-parallel W4A16 GEMMs all-reduce in their epilogue when custom_ar is on
+        self.fuse_act_quant = True  # W8A8 with static fp8 / per-token int8 activations: quantiser fused into norm / silu kernels
         self.fuse_attention = True  # rope + cache write + paged attention in one launch when the shape is on the fast path
         s = shape
         self.nlayers = layers if layers is not None else s.layers
@@ -253,18 +266,33 @@ class SyntheticLlama:
         D = s.head_dim
         h = self.embed.index_select(0, token_ids)
         residual = None
+        fq = self.layers[0]["qkv"].fused_quant_kind if self.fuse_act_quant else None
         for li, L in enumerate(self.layers):
-            if residual is None:
-                residual = h
-                x = torch.empty_like(h)
-                ops.rms_norm(x, h, L["ln1"], s.eps)
+            if fq is not None:
+                # norm (+ residual add) and the activation quantiser of qkv_proj in one kernel
+                first = residual is None
+                if first:
+                    residual = h
+                xq, xs = ops.rms_norm_quant(h, L["ln1"], s.eps, fq, L["qkv"].input_scale, None if first else residual)
+                qkv = L["qkv"].mm_quantized(xq, xs)
             else:
-                ops.fused_add_rms_norm(h, residual, L["ln1"], s.eps)
-                x = h
-            qkv = L["qkv"](x)
+                if residual is None:
+                    residual = h
+                    x = torch.empty_like(h)
+                    ops.rms_norm(x, h, L["ln1"], s.eps)
+                else:
+                    ops.fused_add_rms_norm(h, residual, L["ln1"], s.eps)
+                    x = h
+                qkv = L["qkv"](x)
             q, k, v = qkv.split([self.q_size, self.kv_size, self.kv_size], dim=-1)
             a = self._attention(li, q.view(-1, self.H, D), k.view(-1, self.Hkv, D), v.view(-1, self.Hkv, D), positions, meta)
             h = self._row_parallel(L["o"], a)
+            if fq is not None:
+                xq, xs = ops.rms_norm_quant(h, L["ln2"], s.eps, fq, L["gate_up"].input_scale, residual)
+                gu = L["gate_up"].mm_quantized(xq, xs)
+                aq, asc = ops.silu_and_mul_quant(gu, fq, L["down"].input_scale)
+                h = self._all_reduce(L["down"].mm_quantized(aq, asc))
+                continue
             ops.fused_add_rms_norm(h, residual, L["ln2"], s.eps)
             gu = L["gate_up"](h)
             act = torch.empty((gu.shape[0], gu.shape[1] // 2), dtype=gu.dtype, device=gu.device)
