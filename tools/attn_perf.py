@@ -51,11 +51,22 @@ for S, ctx, H, Hkv in CASES:
     for _ in range(3):
         run()
     torch.cuda.synchronize()
-    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(10)]
-    for e0, e1 in evs:
-        e0.record(); run(); e1.record()
-    torch.cuda.synchronize()
-    ts = sorted(e0.elapsed_time(e1) for e0, e1 in evs)
+    # REPS launches replayed from one CUDA graph: removes the host launch latency that dominates a single ~20 us launch
+    REPS = 20
+    st = torch.cuda.Stream()
+    st.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(st):
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr, stream=st):
+            for _ in range(REPS):
+                run()
+        gr.replay()
+        torch.cuda.synchronize()
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(10)]
+        for e0, e1 in evs:
+            e0.record(st); gr.replay(); e1.record(st)
+        torch.cuda.synchronize()
+    ts = sorted(e0.elapsed_time(e1) / REPS for e0, e1 in evs)
     med = ts[len(ts) // 2] * 1e-3
     alg = S * ctx * Hkv * D * 2 * EB + 2 * S * H * D * 2 + 4 * S * nb_seq
     gbs = alg / med / 1e9
