@@ -226,6 +226,11 @@ extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_
                                      void* stream) {
   using namespace b200;
   (void)workspace;
+  // a fused all-reduce requested for "the next GEMM of this thread" (b200_ar_fuse_next_gemm) is consumed HERE, before any
+  // validation: a rejected or empty call must not leave the request armed for some later, unrelated GEMM
+  long long ar_m = 0, ar_n = 0;
+  ArFuse ar_req;
+  const bool ar_pending = ar_take_pending(&ar_req, &ar_m, &ar_n);
   B200_CHECK(num_bits == 4 || num_bits == 8, "num_bits must be 4 or 8. Got = %d", num_bits);
   B200_CHECK(dtype == B200_F16 || dtype == B200_BF16, "gpt_marlin_gemm only supports bfloat16 and float16");
   B200_CHECK(size_n % 64 == 0, "size_n = %lld, is not divisible by min_thread_n = 64", (long long)size_n);
@@ -255,9 +260,7 @@ extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_
     lda = size_k;
     if (!is_k_full) {
       // partial K: per-row scale lookup through g_idx (see marlin_actorder_partial_kernel)
-      long long fm = 0, fn = 0;
-      ArFuse f;
-      if (ar_take_pending(&f, &fm, &fn))
+      if (ar_pending)
         return set_error(B200_ENOTSUP, "gptq_marlin_gemm: the fused all-reduce is not available for act-order with is_k_full=False");
       dim3 g2((unsigned)(size_n / 64), (unsigned)((size_m + 31) / 32));
 #define AOP_GO(TT, BB)                                                                                              \
@@ -287,15 +290,11 @@ extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_
   ga.cluster_s = 0;
   ga.asum = nullptr; ga.asum_stride = 0;
   ga.ar.world = 0;
-  {
-    long long fm = 0, fn = 0;
-    ArFuse f;
-    if (ar_take_pending(&f, &fm, &fn)) {   // b200_ar_fuse_next_gemm: all-reduce this GEMM's output in its epilogue
-      if (fm != size_m || fn != size_n)
-        return set_error(B200_EINVAL, "gptq_marlin_gemm: fused all-reduce was requested for [%lld, %lld], the GEMM is [%lld, %lld]",
-                         fm, fn, (long long)size_m, (long long)size_n);
-      ga.ar = f;
-    }
+  if (ar_pending) {   // b200_ar_fuse_next_gemm: all-reduce this GEMM's output in its epilogue
+    if (ar_m != size_m || ar_n != size_n)
+      return set_error(B200_EINVAL, "gptq_marlin_gemm: fused all-reduce was requested for [%lld, %lld], the GEMM is [%lld, %lld]",
+                       ar_m, ar_n, (long long)size_m, (long long)size_n);
+    ga.ar = ar_req;
   }
   int rc;
   // B200_GEMM_DECODE=1: the experimental small-CTA decode kernels (marlin_decode_kernel.cuh; parity-green, but measured

@@ -84,6 +84,13 @@ class CustomAllreduce:
     def all_reduce(self, inp: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         if out is None:
             out = torch.empty_like(inp)
+        # the kernel works on raw pointers: refuse what should_custom_ar would refuse instead of reducing the wrong memory
+        if not self.should_custom_ar(inp) or out.shape != inp.shape or out.dtype != inp.dtype or not out.is_contiguous() \
+                or out.device != inp.device:
+            raise ValueError("CustomAllreduce.all_reduce: tensor does not qualify (dtype / contiguity / size / device); "
+                             "use custom_all_reduce() which returns None in that case")
+        if inp.device != self.device:
+            raise ValueError("CustomAllreduce.all_reduce: tensor is on %s, the communicator on %s" % (inp.device, self.device))
         st = torch.cuda.current_stream(inp.device).cuda_stream
         self._check(capi.lib().b200_ar_all_reduce(ctypes.c_int64(self._ctx), ctypes.c_void_p(inp.data_ptr()),
                                                   ctypes.c_void_p(out.data_ptr()), ctypes.c_int64(inp.numel()),
