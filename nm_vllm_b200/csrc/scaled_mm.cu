@@ -295,6 +295,14 @@ static int launch_scaled_mm(smm::Args a, const void* A, const void* B, int64_t l
   a.total_units = tiles * a.KS;
   int grid = num_sms();
   if (grid > a.total_units) grid = a.total_units;
+  // every CTA whose range ends inside a tile publishes MT x 128 32-bit partials and the last arriver of the tile re-reads all
+  // of them: with few tiles and a large MT the fix-up outweighs the streaming (qkv shard [8192 x 1280], M = 64: 37.6 us on 148
+  // CTAs, 26 us with 8 k-blocks per CTA; o shard [1024 x 8192], M = 16: 8.0 -> 4.8 us).  Keep at least `min_units` k-blocks
+  // (16 KB of weights each) per CTA.
+  static const int env_minu = getenv("B200_SMM_MIN_UNITS") ? atoi(getenv("B200_SMM_MIN_UNITS")) : 0;
+  const int min_units = env_minu > 0 ? env_minu : 8;   // measured on the 70B TP8 shards (profiles/r2_smm_min_units.txt): 8 beats 1 / 4 / 16 / 32
+  if (grid > a.total_units / min_units) grid = a.total_units / min_units;
+  if (grid < 1) grid = 1;
   int dev = 0;
   cudaGetDevice(&dev);
   GemmScratch sc;
