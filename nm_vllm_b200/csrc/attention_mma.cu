@@ -402,7 +402,8 @@ static int launch_mma_impl(float* exp_sums, float* max_logits, void* out, void* 
   // kernel goes from 78 % to 91 % of the HBM rate (profiles/r2_attn_perf_warps.txt)
   const int pages_per_cta = partitioned ? kPartition / BS : (max_seq_len + BS - 1) / BS;
   int nw = 4;
-  if (ctas > (long long)num_sms() * 3 && pages_per_cta >= 64)
+  // (or when the launch as a whole is long: >= 16k pages in total, e.g. one 32k-token sequence cut into 512 partitions)
+  if (ctas > (long long)num_sms() * 3 && (pages_per_cta >= 64 || ctas * pages_per_cta >= 16384))
     nw = ctas <= (long long)num_sms() * 4 ? 3 : (ctas <= (long long)num_sms() * 6 ? 2 : 4);
   if (force_w >= 2 && force_w <= 4) nw = force_w;
 #define GQA_GO3(TT, KVV, FF, WW)                                                                                        \

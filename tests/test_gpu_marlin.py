@@ -147,3 +147,38 @@ def test_marlin_gemm_alias(ops):
     ws = torch.zeros((N // 64) * 16, dtype=torch.int32, device=DEV)
     out = ops.marlin_gemm(a.to(DEV), mq.to(DEV), ms.to(DEV), ws, M, N, K)
     assert ops_ref.rel_mean_err(out.cpu(), ops_ref.marlin_gemm_ref(a, w_ref)) < 1e-2
+
+
+def test_cuda_graph_survives_scratch_regrow(ops):
+    """a graph captured while the split-K scratch was small must keep replaying correctly after a later call made
+    the scratch grow (the old buffers are retired, never freed)."""
+    import ctypes
+
+    from nm_vllm_b200 import capi
+    M, K, N = 16, 4096, 4096          # split over the SMs: the kernel uses partial slots and tile counters
+    g = torch.Generator().manual_seed(5)
+    qw = torch.randint(-2**31, 2**31 - 1, (K // 16, N * 2), generator=g, dtype=torch.int32).to(DEV)
+    s = (torch.rand((K // 128, N), generator=g) * 0.002 + 0.003).to(torch.bfloat16).to(DEV)
+    a = torch.randn((M, K), generator=g).to(torch.bfloat16).to(DEV)
+    e = torch.empty(0, dtype=torch.int32, device=DEV)
+    ws = torch.zeros((N // 64) * 16, dtype=torch.int32, device=DEV)
+    ref = ops.gptq_marlin_gemm(a, qw, s, e, e, ws, 4, M, N, K, True).clone()
+    st = torch.cuda.Stream()
+    st.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(st):
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr, stream=st):
+            out = ops.gptq_marlin_gemm(a, qw, s, e, e, ws, 4, M, N, K, True)
+    torch.cuda.synchronize()
+    gr.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out, ref)
+    # force the scratch to grow well beyond its first size, then use it from another kernel
+    assert capi.lib().b200_gemm_scratch_reserve(ctypes.c_int64(1024), ctypes.c_int64(65536)) == 0, capi.last_error()
+    big = torch.randn((256, K), generator=g).to(torch.bfloat16).to(DEV)
+    ops.gptq_marlin_gemm(big, qw, s, e, e, ws, 4, 256, N, K, True)
+    torch.cuda.synchronize()
+    out.zero_()
+    gr.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out, ref), "graph replay after a scratch regrow differs"
