@@ -226,13 +226,56 @@ paged_attn_gqa_kernel(float* __restrict__ exp_sums, float* __restrict__ max_logi
   for (int i = 0; i < 8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
 
   const int* btab = block_tables + (int64_t)seq * max_blocks_per_seq;
-  // MMA row r of S^T <-> token: auto: r; fp8: rows 0-7 -> 2r - r%2, rows 8-15 -> that + 2 (so that the transposed P
-  // fragment lines up with the 4-token groups one fp8 V load delivers)
-  const int t_lo = FP8 ? 2 * g - (g & 1) : g;
-  const int t_hi = FP8 ? t_lo + 2 : g + 8;
-  // everything after a page's K / V fragments are in registers: logits, online softmax, P.V
-  auto process_page = [&](uint32_t (&kf)[8][4], uint32_t (&vf)[8][4], const int blk) {
+  for (int blk = start_block + warp; blk < end_block; blk += kWarps) {
+    const int64_t base = (int64_t)btab[blk] * kv_block_stride + (int64_t)kvh * kv_head_stride;
     const int tok0 = blk * BS;
+    // MMA row r of S^T <-> token: auto: r; fp8: rows 0-7 -> 2r - r%2, rows 8-15 -> that + 2 (so that the transposed P
+    // fragment lines up with the 4-token groups one fp8 V load delivers)
+    const int t_lo = FP8 ? 2 * g - (g & 1) : g;
+    const int t_hi = FP8 ? t_lo + 2 : g + 8;
+    uint32_t kf[8][4], vf[8][4];
+    if constexpr (!FP8) {
+      const T* kp = reinterpret_cast<const T*>(k_cache_v) + base + g * 8 + 2 * qd;          // K [D/8][16][8]
+      const T* vp = reinterpret_cast<const T*>(v_cache_v) + base + g * BS + 2 * qd;          // V [D][16]
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        kf[c][0] = ldg32<NC>(kp + (2 * c) * (BS * 8));
+        kf[c][1] = ldg32<NC>(kp + (2 * c) * (BS * 8) + 64);
+        kf[c][2] = ldg32<NC>(kp + (2 * c + 1) * (BS * 8));
+        kf[c][3] = ldg32<NC>(kp + (2 * c + 1) * (BS * 8) + 64);
+      }
+#pragma unroll
+      for (int dm = 0; dm < 8; ++dm) {
+        vf[dm][0] = ldg32<NC>(vp + (16 * dm) * BS);
+        vf[dm][1] = ldg32<NC>(vp + (16 * dm + 8) * BS);
+        vf[dm][2] = ldg32<NC>(vp + (16 * dm) * BS + 8);
+        vf[dm][3] = ldg32<NC>(vp + (16 * dm + 8) * BS + 8);
+      }
+    } else {
+      const uint8_t* kp = reinterpret_cast<const uint8_t*>(k_cache_v) + base + 4 * qd;        // K [D/16][16][16]
+      const uint8_t* vp = reinterpret_cast<const uint8_t*>(v_cache_v) + base + g * BS + 4 * qd;  // V [D][16]
+      uint32_t kr[8][2], vr[8][2];
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        kr[c][0] = ldg32<NC>(kp + c * (BS * 16) + t_lo * 16);
+        kr[c][1] = ldg32<NC>(kp + c * (BS * 16) + t_hi * 16);
+      }
+#pragma unroll
+      for (int dm = 0; dm < 8; ++dm) {
+        vr[dm][0] = ldg32<NC>(vp + (16 * dm) * BS);
+        vr[dm][1] = ldg32<NC>(vp + (16 * dm + 8) * BS);
+      }
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        fp8x4_to_h2<FP8 ? KV : B200_KV_FP8_E4M3>(kr[c][0], kf[c][0], kf[c][2]);
+        fp8x4_to_h2<FP8 ? KV : B200_KV_FP8_E4M3>(kr[c][1], kf[c][1], kf[c][3]);
+      }
+#pragma unroll
+      for (int dm = 0; dm < 8; ++dm) {
+        fp8x4_to_h2<FP8 ? KV : B200_KV_FP8_E4M3>(vr[dm][0], vf[dm][0], vf[dm][2]);
+        fp8x4_to_h2<FP8 ? KV : B200_KV_FP8_E4M3>(vr[dm][1], vf[dm][1], vf[dm][3]);
+      }
+    }
     float s[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
     for (int c = 0; c < 8; ++c) Mma<MT>::run(s, kf[c], qf[c][0], qf[c][1]);
@@ -282,72 +325,6 @@ paged_attn_gqa_kernel(float* __restrict__ exp_sums, float* __restrict__ max_logi
     for (int dm = 0; dm < 8; ++dm) {
       o[dm][0] *= alpha[0]; o[dm][1] *= alpha[1]; o[dm][2] *= alpha[0]; o[dm][3] *= alpha[1];
       Mma<MT>::run(o[dm], vf[dm], pb0, pb1);
-    }
-  };
-  if constexpr (!FP8) {
-    for (int blk = start_block + warp; blk < end_block; blk += kWarps) {
-      const int64_t base = (int64_t)btab[blk] * kv_block_stride + (int64_t)kvh * kv_head_stride;
-      uint32_t kf[8][4], vf[8][4];
-      const T* kp = reinterpret_cast<const T*>(k_cache_v) + base + g * 8 + 2 * qd;          // K [D/8][16][8]
-      const T* vp = reinterpret_cast<const T*>(v_cache_v) + base + g * BS + 2 * qd;          // V [D][16]
-#pragma unroll
-      for (int c = 0; c < 8; ++c) {
-        kf[c][0] = ldg32<NC>(kp + (2 * c) * (BS * 8));
-        kf[c][1] = ldg32<NC>(kp + (2 * c) * (BS * 8) + 64);
-        kf[c][2] = ldg32<NC>(kp + (2 * c + 1) * (BS * 8));
-        kf[c][3] = ldg32<NC>(kp + (2 * c + 1) * (BS * 8) + 64);
-      }
-#pragma unroll
-      for (int dm = 0; dm < 8; ++dm) {
-        vf[dm][0] = ldg32<NC>(vp + (16 * dm) * BS);
-        vf[dm][1] = ldg32<NC>(vp + (16 * dm + 8) * BS);
-        vf[dm][2] = ldg32<NC>(vp + (16 * dm) * BS + 8);
-        vf[dm][3] = ldg32<NC>(vp + (16 * dm + 8) * BS + 8);
-      }
-      process_page(kf, vf, blk);
-    }
-  } else {
-    // fp8 pages are half the bytes: a warp takes TWO pages per turn and issues the loads of both before the first
-    // conversion, so that it keeps the same 8 KB in flight as with a 16-bit cache (ncu on the one-page version, 64 x 2k
-    // ctx: 31 % issue slots busy, long-scoreboard stalls 4.3 per issue, 53 % of DRAM throughput -- latency, not the cvt rate)
-    for (int b0 = start_block + 2 * warp; b0 < end_block; b0 += 2 * kWarps) {
-      const bool two = b0 + 1 < end_block;
-      uint32_t kr[2][8][2], vr[2][8][2];
-#pragma unroll
-      for (int pg = 0; pg < 2; ++pg) {
-        if (pg == 0 || two) {
-          const int64_t base = (int64_t)btab[b0 + pg] * kv_block_stride + (int64_t)kvh * kv_head_stride;
-          const uint8_t* kp = reinterpret_cast<const uint8_t*>(k_cache_v) + base + 4 * qd;        // K [D/16][16][16]
-          const uint8_t* vp = reinterpret_cast<const uint8_t*>(v_cache_v) + base + g * BS + 4 * qd;  // V [D][16]
-#pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            kr[pg][c][0] = ldg32<NC>(kp + c * (BS * 16) + t_lo * 16);
-            kr[pg][c][1] = ldg32<NC>(kp + c * (BS * 16) + t_hi * 16);
-          }
-#pragma unroll
-          for (int dm = 0; dm < 8; ++dm) {
-            vr[pg][dm][0] = ldg32<NC>(vp + (16 * dm) * BS);
-            vr[pg][dm][1] = ldg32<NC>(vp + (16 * dm + 8) * BS);
-          }
-        }
-      }
-#pragma unroll
-      for (int pg = 0; pg < 2; ++pg) {
-        if (pg == 0 || two) {
-          uint32_t kf[8][4], vf[8][4];
-#pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            fp8x4_to_h2<FP8 ? KV : B200_KV_FP8_E4M3>(kr[pg][c][0], kf[c][0], kf[c][2]);
-            fp8x4_to_h2<FP8 ? KV : B200_KV_FP8_E4M3>(kr[pg][c][1], kf[c][1], kf[c][3]);
-          }
-#pragma unroll
-          for (int dm = 0; dm < 8; ++dm) {
-            fp8x4_to_h2<FP8 ? KV : B200_KV_FP8_E4M3>(vr[pg][dm][0], vf[dm][0], vf[dm][2]);
-            fp8x4_to_h2<FP8 ? KV : B200_KV_FP8_E4M3>(vr[pg][dm][1], vf[dm][1], vf[dm][3]);
-          }
-          process_page(kf, vf, b0 + pg);
-        }
-      }
     }
   }
 
