@@ -27,7 +27,7 @@ namespace m24 {
 
 constexpr int kWarps = 4;
 constexpr int kThreads = kWarps * 32;
-constexpr int kPrefetch = 4;
+constexpr int kPrefetch = 8;   // depth of each warp's private cp.async ring of (weights, metadata, scales) stages
 
 struct Args {
   const __half* A;
@@ -44,6 +44,16 @@ struct Args {
   int kb_per_split; // k32 blocks per split (last split may be shorter)
   int n_tiles;
 };
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 __device__ __forceinline__ uint4 ldg_stream(const void* p) {
   uint4 v;
@@ -97,27 +107,46 @@ marlin24_gemm_kernel(const m24::Args args) {
   const uint32_t* mp = args.meta + (size_t)t * 64 + lane;
   const __half* sp_ptr = args.scales + (size_t)t * 64 + col * 8;
 
-  Stage<BITS> st[kPrefetch];
-  auto load_stage = [&](Stage<BITS>& s, int kb) {
+  // Each lane streams ITS OWN 16 (32) bytes of weights, 8 bytes of metadata and 16 bytes of scales of a k32 block into a
+  // private slot of a kPrefetch-deep shared-memory ring with cp.async and reads the same bytes back later: no cross-lane
+  // hazards, no barriers, and kPrefetch x 1.25 KB per warp in flight without holding it in registers (the register-prefetch
+  // version kept 4 stages = 37 KB per SM in flight and ran at 17-28 % of HBM: latency-bound).
+  // slot layout per lane: [weights 16 / 32 B][scales 16 B][metadata 8 B][pad]; lanes are 48 / 80 bytes apart inside a slot so
+  // that the 16-byte reads of a quarter warp fall into distinct banks
+  constexpr int LANE_BYTES = BITS == 4 ? 48 : 80;
+  constexpr int SLOT_BYTES = 32 * LANE_BYTES;
+  const uint32_t ring_off = (uint32_t)warp * (kPrefetch * SLOT_BYTES) + (uint32_t)lane * LANE_BYTES;
+  const uint32_t ring = ptx::smem_u32(smem24) + ring_off;
+  auto issue_stage = [&](int slot, int kb) {
     if (kb < kb1) {
+      const uint32_t dst = ring + slot * SLOT_BYTES;
       const uint32_t* w = wp + (size_t)kb * wrow;
-      const uint4 v0 = ldg_stream(w);
-      s.w[0] = v0.x; s.w[1] = v0.y; s.w[2] = v0.z; s.w[3] = v0.w;
-      if (BITS == 8) {
-        const uint4 v1 = ldg_stream(w + 4);
-        s.w[4 % WPL] = v1.x; s.w[5 % WPL] = v1.y; s.w[6 % WPL] = v1.z; s.w[7 % WPL] = v1.w;
-      }
-      s.e[0] = ldg_stream32(mp + (size_t)kb * args.N);
-      s.e[1] = ldg_stream32(mp + (size_t)kb * args.N + 32);
-      if (GROUPED) {
-        const uint4 sv = *reinterpret_cast<const uint4*>(sp_ptr + (size_t)(kb / gblocks) * args.N);
-        s.s[0] = sv.x; s.s[1] = sv.y; s.s[2] = sv.z; s.s[3] = sv.w;
-      }
+      cp_async16(dst, w);
+      if (BITS == 8) cp_async16(dst + 16, w + 4);
+      if (GROUPED) cp_async16(dst + WPL * 4, sp_ptr + (size_t)(kb / gblocks) * args.N);
+      cp_async4(dst + WPL * 4 + 16, mp + (size_t)kb * args.N);
+      cp_async4(dst + WPL * 4 + 20, mp + (size_t)kb * args.N + 32);
+    }
+    cp_async_commit();   // one group per stage, issued or not, so that the wait below always counts stages
+  };
+  auto read_stage = [&](Stage<BITS>& st_, int slot) {
+    const uint8_t* src = smem24 + ring_off + slot * SLOT_BYTES;
+    const uint4 v0 = *reinterpret_cast<const uint4*>(src);
+    st_.w[0] = v0.x; st_.w[1] = v0.y; st_.w[2] = v0.z; st_.w[3] = v0.w;
+    if (BITS == 8) {
+      const uint4 v1 = *reinterpret_cast<const uint4*>(src + 16);
+      st_.w[4 % WPL] = v1.x; st_.w[5 % WPL] = v1.y; st_.w[6 % WPL] = v1.z; st_.w[7 % WPL] = v1.w;
+    }
+    const uint2 e = *reinterpret_cast<const uint2*>(src + WPL * 4 + 16);
+    st_.e[0] = e.x; st_.e[1] = e.y;
+    if (GROUPED) {
+      const uint4 sv = *reinterpret_cast<const uint4*>(src + WPL * 4);
+      st_.s[0] = sv.x; st_.s[1] = sv.y; st_.s[2] = sv.z; st_.s[3] = sv.w;
     }
   };
   // weights / metadata / scales do not depend on the previous kernel: start streaming before the PDL wait
 #pragma unroll
-  for (int u = 0; u < kPrefetch; ++u) load_stage(st[u], kb0 + warp + u * kWarps);
+  for (int u = 0; u < kPrefetch; ++u) issue_stage(u, kb0 + warp + u * kWarps);
   pdl_wait();
   pdl_launch_dependents();
 
@@ -170,16 +199,19 @@ marlin24_gemm_kernel(const m24::Args args) {
     }
   };
 
-  for (int kb = kb0 + warp; kb < kb1; kb += kPrefetch * kWarps) {
-#pragma unroll
-    for (int u = 0; u < kPrefetch; ++u) {
-      const int k = kb + u * kWarps;
-      if (k < kb1) {
-        compute(st[u], k);
-        load_stage(st[u], k + kPrefetch * kWarps);
-      }
+  {
+    int slot = 0;
+    for (int kb = kb0 + warp; kb < kb1; kb += kWarps) {
+      cp_async_wait<kPrefetch - 1>();      // the oldest stage of this lane has landed
+      Stage<BITS> st_;
+      read_stage(st_, slot);
+      issue_stage(slot, kb + kPrefetch * kWarps);   // refill the slot just read (same lane: no hazard)
+      compute(st_, kb);
+      if (++slot == kPrefetch) slot = 0;
     }
+    cp_async_wait<0>();
   }
+  __syncthreads();   // the ring is reused as the reduction buffer below
 
   // ---- sum the 8 warps' partials, un-permute into a [MC][64] tile ------------------------------------------------------
   float* red = reinterpret_cast<float*>(smem24);
@@ -259,7 +291,9 @@ static int launch_m24(m24::Args a, cudaStream_t st) {
   if (int e = gemm_ensure_scratch(dev, splits > 1 ? (size_t)a.n_tiles * m_chunks * splits * MC * 64 : 1, a.n_tiles * m_chunks, st, &sc)) return e;
   a.scratch = sc.partials;
   a.counters = sc.counters;
-  const size_t smem = (size_t)(kWarps * 32 * MB * 32 + MC * 64) * 4;
+  const size_t smem_red = (size_t)(kWarps * 32 * MB * 32 + MC * 64) * 4;
+  const size_t smem_ring = (size_t)kThreads * kPrefetch * (BITS == 4 ? 48 : 80);
+  const size_t smem = smem_red > smem_ring ? smem_red : smem_ring;
   auto kern = marlin24_gemm_kernel<BITS, MB, GROUPED, NH>;
   static bool attr_set[64] = {};
   if (!attr_set[dev & 63]) {
