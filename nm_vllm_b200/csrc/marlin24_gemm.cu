@@ -27,7 +27,6 @@ namespace m24 {
 
 constexpr int kWarps = 4;
 constexpr int kThreads = kWarps * 32;
-constexpr int kPrefetch = 8;   // depth of each warp's private cp.async ring of (weights, metadata, scales) stages
 
 struct Args {
   const __half* A;
@@ -75,12 +74,29 @@ __device__ __forceinline__ void mma_sp(float* c, const uint32_t* a, const uint32
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]), "r"(b[2]), "r"(b[3]), "r"(e), "n"(SEL));
 }
 
-template <int BITS>
+__device__ __forceinline__ void cp_async16_zfill(uint32_t dst, const void* src, uint32_t src_bytes) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr) : "memory");
+}
+
+template <int BITS, int MB, int NH>
 struct Stage {
   uint32_t w[BITS == 4 ? 4 : 8];
   uint32_t e[2];
   uint32_t s[4];
+  uint32_t b[MB][NH][4];   // activation fragments (B operand of mma.sp) of the k32 block
 };
+
+// bytes of one warp's ring slot (32 private lane parts + 8 x 80 bytes per 8-row activation half block) and the ring depth
+// that keeps a CTA at <= 54 KB of shared memory (4 CTAs per SM: a 448-tile GEMM must not spill into a second wave)
+constexpr int slot_bytes(int bits, int mb, int nh) { return 32 * (bits == 4 ? 48 : 80) + mb * nh * 640; }
+constexpr int prefetch_depth(int bits, int mb, int nh) {
+  int d = (54 * 1024) / (kWarps * slot_bytes(bits, mb, nh));
+  return d > 8 ? 8 : d;
+}
 
 }  // namespace m24
 
@@ -101,36 +117,64 @@ marlin24_gemm_kernel(const m24::Args args) {
   const int kb0 = sp * args.kb_per_split;
   const int kb1 = min(KB, kb0 + args.kb_per_split);
   const int wrow = args.N * (BITS == 4 ? 2 : 4);
-  const int gblocks = GROUPED ? (args.K / args.num_groups) / 32 : 1;   // k32 blocks per scale group
-
+  // (walking the k32 blocks in a per-CTA rotated order, so that the SMs do not all ask L2 for the same activation lines at
+  // the same moment, was measured: no gain, and it breaks the DRAM page locality of neighbouring tiles.)
+  const int n_it = (kb1 - kb0 + kWarps - 1) / kWarps;
+  auto kb_of = [&](int i) { return i < n_it ? kb0 + i * kWarps + warp : kb1; };   // k32 block of this warp's i-th iteration
   const uint32_t* wp = args.Bq + (size_t)t * (32 * WPL) + lane * WPL;
   const uint32_t* mp = args.meta + (size_t)t * 64 + lane;
   const __half* sp_ptr = args.scales + (size_t)t * 64 + col * 8;
 
   // Each lane streams ITS OWN 16 (32) bytes of weights, 8 bytes of metadata and 16 bytes of scales of a k32 block into a
-  // private slot of a kPrefetch-deep shared-memory ring with cp.async and reads the same bytes back later: no cross-lane
-  // hazards, no barriers, and kPrefetch x 1.25 KB per warp in flight without holding it in registers (the register-prefetch
-  // version kept 4 stages = 37 KB per SM in flight and ran at 17-28 % of HBM: latency-bound).
-  // slot layout per lane: [weights 16 / 32 B][scales 16 B][metadata 8 B][pad]; lanes are 48 / 80 bytes apart inside a slot so
-  // that the 16-byte reads of a quarter warp fall into distinct banks
-  constexpr int LANE_BYTES = BITS == 4 ? 48 : 80;
-  constexpr int SLOT_BYTES = 32 * LANE_BYTES;
-  const uint32_t ring_off = (uint32_t)warp * (kPrefetch * SLOT_BYTES) + (uint32_t)lane * LANE_BYTES;
-  const uint32_t ring = ptx::smem_u32(smem24) + ring_off;
-  auto issue_stage = [&](int slot, int kb) {
+  // private part of a kPrefetch-deep shared-memory ring with cp.async and reads the same bytes back later (no cross-lane
+  // hazard).  The activation fragments ride the same ring: each 8-row half block is 8 x 64 bytes, copied by the warp as 32
+  // 16-byte cp.async (rows beyond M zero-filled) into rows 80 bytes apart and read back with ONE ldmatrix.x4 whose matrix i
+  // is the 16-byte column i of the 8 rows -- exactly word 4 i + q of row col, the B fragment of mma.sp.  History
+  // (profiles/r2_m24_ncu.txt): with the activations as LDGs every warp iteration stalled ~2000 clk on the first HMMA.SP
+  // (long scoreboard) however far ahead they were issued; as 4-byte cp.async per fragment word the MIO queue became the
+  // limiter (12 LDGSTS per iteration).
+  constexpr int LANE_BYTES = BITS == 4 ? 48 : 80;   // odd multiple of 16: a quarter warp's 16-byte reads hit distinct banks
+  constexpr int ACT_ROW = 80;                       // same for the ldmatrix rows
+  constexpr int ACT_OFF = 32 * LANE_BYTES;
+  constexpr int SLOT_BYTES = m24::slot_bytes(BITS, MB, NH);
+  constexpr int kPrefetch = m24::prefetch_depth(BITS, MB, NH);
+  const uint32_t ring_off = (uint32_t)warp * (kPrefetch * SLOT_BYTES);
+  const uint32_t lane_off = ring_off + (uint32_t)lane * LANE_BYTES;
+  const uint32_t ring = ptx::smem_u32(smem24) + lane_off;
+  const uint32_t act_dst = ptx::smem_u32(smem24) + ring_off + ACT_OFF + (lane >> 2) * ACT_ROW + (lane & 3) * 16;
+  const uint32_t act_src = ptx::smem_u32(smem24) + ring_off + ACT_OFF + (lane & 7) * ACT_ROW + (lane >> 3) * 16;
+  const __half* arow[MB][NH];
+  uint32_t arow_bytes[MB][NH];   // 16 = real row, 0 = beyond M (cp.async zero-fills)
+#pragma unroll
+  for (int mb = 0; mb < MB; ++mb)
+#pragma unroll
+    for (int h = 0; h < NH; ++h) {
+      const int m = m0 + 16 * mb + 8 * h + col;
+      arow_bytes[mb][h] = m < args.M ? 16u : 0u;
+      arow[mb][h] = args.A + (size_t)(m < args.M ? m : 0) * args.lda + q * 8;
+    }
+  auto issue_weights = [&](int slot, int kb) {
     if (kb < kb1) {
       const uint32_t dst = ring + slot * SLOT_BYTES;
       const uint32_t* w = wp + (size_t)kb * wrow;
       cp_async16(dst, w);
       if (BITS == 8) cp_async16(dst + 16, w + 4);
-      if (GROUPED) cp_async16(dst + WPL * 4, sp_ptr + (size_t)(kb / gblocks) * args.N);
+      if (GROUPED) cp_async16(dst + WPL * 4, sp_ptr + (size_t)(kb >> 2) * args.N);   // group_size 128 = 4 k32 blocks
       cp_async4(dst + WPL * 4 + 16, mp + (size_t)kb * args.N);
       cp_async4(dst + WPL * 4 + 20, mp + (size_t)kb * args.N + 32);
     }
-    cp_async_commit();   // one group per stage, issued or not, so that the wait below always counts stages
   };
-  auto read_stage = [&](Stage<BITS>& st_, int slot) {
-    const uint8_t* src = smem24 + ring_off + slot * SLOT_BYTES;
+  auto issue_acts = [&](int slot, int kb) {
+    if (kb < kb1) {
+#pragma unroll
+      for (int mb = 0; mb < MB; ++mb)
+#pragma unroll
+        for (int h = 0; h < NH; ++h)
+          cp_async16_zfill(act_dst + slot * SLOT_BYTES + (mb * NH + h) * (8 * ACT_ROW), arow[mb][h] + kb * 32, arow_bytes[mb][h]);
+    }
+  };
+  auto read_stage = [&](Stage<BITS, MB, NH>& st_, int slot) {
+    const uint8_t* src = smem24 + lane_off + slot * SLOT_BYTES;
     const uint4 v0 = *reinterpret_cast<const uint4*>(src);
     st_.w[0] = v0.x; st_.w[1] = v0.y; st_.w[2] = v0.z; st_.w[3] = v0.w;
     if (BITS == 8) {
@@ -143,38 +187,26 @@ marlin24_gemm_kernel(const m24::Args args) {
       const uint4 sv = *reinterpret_cast<const uint4*>(src + WPL * 4);
       st_.s[0] = sv.x; st_.s[1] = sv.y; st_.s[2] = sv.z; st_.s[3] = sv.w;
     }
-  };
-  // weights / metadata / scales do not depend on the previous kernel: start streaming before the PDL wait
 #pragma unroll
-  for (int u = 0; u < kPrefetch; ++u) issue_stage(u, kb0 + warp + u * kWarps);
+    for (int mb = 0; mb < MB; ++mb)
+#pragma unroll
+      for (int h = 0; h < NH; ++h) ldmatrix_x4(st_.b[mb][h], act_src + slot * SLOT_BYTES + (mb * NH + h) * (8 * ACT_ROW));
+  };
+  // weights / metadata / scales do not depend on the previous kernel: start streaming them before the PDL wait; the
+  // activations follow as kPrefetch more groups.  wait_group<kPrefetch-1> in iteration i then covers both halves of stage i
+  // (groups retire in order: W0..W{P-1}, A0..A{P-1}, then one combined group per iteration).
+#pragma unroll
+  for (int u = 0; u < kPrefetch; ++u) { issue_weights(u, kb_of(u)); cp_async_commit(); }
   pdl_wait();
   pdl_launch_dependents();
+#pragma unroll
+  for (int u = 0; u < kPrefetch; ++u) { issue_acts(u, kb_of(u)); cp_async_commit(); }
 
   float acc[NACC];
 #pragma unroll
   for (int i = 0; i < NACC; ++i) acc[i] = 0.f;
-  // activation fragments come straight from global memory through L1 (every CTA of the SM re-reads the same few rows, so
-  // they stay L1/L2 resident); rows beyond M read as zero
-  const uint32_t* arow[MB][NH];
-  bool arow_ok[MB][NH];
-#pragma unroll
-  for (int mb = 0; mb < MB; ++mb)
-#pragma unroll
-    for (int h = 0; h < NH; ++h) {
-      const int m = m0 + 16 * mb + 8 * h + col;
-      arow_ok[mb][h] = m < args.M;
-      arow[mb][h] = reinterpret_cast<const uint32_t*>(args.A + (size_t)(arow_ok[mb][h] ? m : 0) * args.lda) + q;
-    }
 
-  auto compute = [&](const Stage<BITS>& s, int kb) {
-    uint32_t b[MB][NH][4];
-#pragma unroll
-    for (int mb = 0; mb < MB; ++mb)
-#pragma unroll
-      for (int h = 0; h < NH; ++h)
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-          b[mb][h][i] = arow_ok[mb][h] ? __ldg(arow[mb][h] + kb * 16 + 4 * i) : 0u;
+  auto compute = [&](const Stage<BITS, MB, NH>& s) {
 #pragma unroll
     for (int jj = 0; jj < 4; ++jj) {
       uint32_t a[4];
@@ -193,20 +225,26 @@ marlin24_gemm_kernel(const m24::Args args) {
 #pragma unroll
         for (int h = 0; h < NH; ++h) {
           float* c = &acc[((mb * 4 + jj) * 2 + h) * 4];
-          if (jj & 1) mma_sp<1>(c, a, b[mb][h], e);
-          else mma_sp<0>(c, a, b[mb][h], e);
+          if (jj & 1) mma_sp<1>(c, a, s.b[mb][h], e);
+          else mma_sp<0>(c, a, s.b[mb][h], e);
         }
     }
   };
 
   {
     int slot = 0;
-    for (int kb = kb0 + warp; kb < kb1; kb += kWarps) {
-      cp_async_wait<kPrefetch - 1>();      // the oldest stage of this lane has landed
-      Stage<BITS> st_;
+    for (int i = 0; i < n_it; ++i) {
+      const bool live = kb_of(i) < kb1;      // the last round is ragged when the split is not a multiple of kWarps
+      cp_async_wait<kPrefetch - 1>();        // the oldest stage of this lane has landed ...
+      __syncwarp();                          // ... and of every other lane (the activation rows are shared by the warp)
+      Stage<BITS, MB, NH> st_;
       read_stage(st_, slot);
-      issue_stage(slot, kb + kPrefetch * kWarps);   // refill the slot just read (same lane: no hazard)
-      compute(st_, kb);
+      __syncwarp();                          // everybody has read the slot before anybody refills it
+      const int kn = kb_of(i + kPrefetch);   // refill the slot just read (same lane: no hazard)
+      issue_weights(slot, kn);
+      issue_acts(slot, kn);
+      cp_async_commit();                     // one group per iteration, issued or not, so that the wait always counts stages
+      if (live) compute(st_);
       if (++slot == kPrefetch) slot = 0;
     }
     cp_async_wait<0>();
@@ -292,7 +330,7 @@ static int launch_m24(m24::Args a, cudaStream_t st) {
   a.scratch = sc.partials;
   a.counters = sc.counters;
   const size_t smem_red = (size_t)(kWarps * 32 * MB * 32 + MC * 64) * 4;
-  const size_t smem_ring = (size_t)kThreads * kPrefetch * (BITS == 4 ? 48 : 80);
+  const size_t smem_ring = (size_t)kWarps * prefetch_depth(BITS, MB, NH) * slot_bytes(BITS, MB, NH);
   const size_t smem = smem_red > smem_ring ? smem_red : smem_ring;
   auto kern = marlin24_gemm_kernel<BITS, MB, GROUPED, NH>;
   static bool attr_set[64] = {};
