@@ -217,7 +217,12 @@ def gemm_roofline(model, batch, peaks, brief=False):
     ach = alg / t / 1e9
     if brief:
         return {"achieved": ach, "frac": ach / peak, "avg_launch_us": t / len(lin) * 1e6, "gemm_ms_per_step": t * 1e3}
-    return {"bound": "hbm", "kernel": "marlin_gemm_kernel (gptq_marlin_gemm W4A16 g128)", "achieved": ach, "peak": peak,
+    kernel = {"w4a16": "marlin_gemm_kernel (gptq_marlin_gemm W4A16 g128)",
+              "w4a16_24": "marlin24_gemm_kernel (gptq_marlin_24_gemm 2:4 W4A16 g128)",
+              "fp8": "scaled_mm_kernel (cutlass_scaled_mm fp8, per-token x per-channel)",
+              "fp8_static": "scaled_mm_kernel (cutlass_scaled_mm fp8, per-tensor x per-channel)",
+              "int8": "scaled_mm_kernel (cutlass_scaled_mm int8, per-token x per-channel)"}.get(lin[0].kind, lin[0].kind)
+    return {"bound": "hbm", "kernel": kernel, "achieved": ach, "peak": peak,
             "unit": "GB/s", "frac": ach / peak,
             # dram bytes per launch are NOT measured in this run (ncu only): see profiles/r1_gemm_traffic.json for the
             # N=1 batch-64 capture (29.3 MB per launch vs 30.3 MB algorithmic)

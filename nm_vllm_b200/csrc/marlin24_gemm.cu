@@ -14,19 +14,23 @@
 // So the compressed operand goes straight from global memory into the sparse tensor-core instruction: no shared-memory
 // staging of weights, no shuffles.
 //
-// Work decomposition (HBM-bound, M <= 64 per pass): many small CTAs instead of a deep async pipeline.  CTA = (64-column
-// tile, K split s of S); its 8 warps take the k32 blocks of the split round-robin, each streaming its 512 B weight +
-// 256 B metadata rows with a 4-deep register prefetch (ld.global.nc, L1 bypass); 4-6 CTAs are resident per SM.  Warp
-// partials are summed in shared memory; K splits are summed through fp32 slots in CTA order by the last split to arrive
-// (atomic ticket): deterministic, nobody spins.  NOTE this kernel uses the warp-level sparse MMA (HMMA.SP); feeding
-// tcgen05.mma.sp from TMEM is the planned next step.
+// Work decomposition (HBM-bound, M <= 64 per pass).  CTA = (four adjacent 64-column tiles, K split s of S, 64-row pass):
+// warp w streams the weights / metadata / scales of tile w % 4 lane-privately (cp.async into a multi-stage shared-memory
+// ring, read back by the same lane); the activation rows of the k32 block are copied ONCE per CTA (16-byte cp.async, rows
+// 80 bytes apart) and every warp takes its B fragments from them with one ldmatrix.x4 per 8-row half block.  One
+// __syncthreads per k32 block (classic multistage pipeline).  With more than 32 rows a second group of four warps works on
+// rows 32..63 of the same tiles from the same staged weights, so the weights cross L2 once per 64 rows.  No cross-warp
+// reduction: every warp owns its (rows, tile) outputs; K splits are summed through fp32 slots in split order by the last
+// split to arrive (atomic ticket): deterministic, nobody spins.
+// History (profiles/r2_m24_ncu.txt): the first version gave every warp its own k32 blocks and loaded its activation
+// fragments with LDGs -- 105 MB (M = 16) to 470 MB (M = 64) of L2->SM activation traffic against 46 MB of weights, and every
+// iteration stalled ~2000 clk on the first HMMA.SP.  NOTE this kernel uses the warp-level sparse MMA (HMMA.SP); feeding
+// tcgen05.mma.sp (dequantised tile in shared memory, metadata in TMEM) is not done.
 #include "marlin_gemm_kernel.cuh"
 
 namespace b200 {
 namespace m24 {
 
-constexpr int kWarps = 4;
-constexpr int kThreads = kWarps * 32;
 
 struct Args {
   const __half* A;
@@ -41,7 +45,8 @@ struct Args {
   int num_groups;   // 1 = channelwise
   int splits;       // K splits per tile
   int kb_per_split; // k32 blocks per split (last split may be shorter)
-  int n_tiles;
+  int n_tiles;      // 64-column tiles
+  int n_ctiles;     // CTA columns (four tiles each)
 };
 
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
@@ -82,272 +87,278 @@ __device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr) : "memory");
 }
 
-template <int BITS, int MB, int NH>
-struct Stage {
-  uint32_t w[BITS == 4 ? 4 : 8];
-  uint32_t e[2];
-  uint32_t s[4];
-  uint32_t b[MB][NH][4];   // activation fragments (B operand of mma.sp) of the k32 block
-};
-
-// bytes of one warp's ring slot (32 private lane parts + 8 x 80 bytes per 8-row activation half block) and the ring depth
-// that keeps a CTA at <= 54 KB of shared memory (4 CTAs per SM: a 448-tile GEMM must not spill into a second wave)
-constexpr int slot_bytes(int bits, int mb, int nh) { return 32 * (bits == 4 ? 48 : 80) + mb * nh * 640; }
-constexpr int prefetch_depth(int bits, int mb, int nh) {
-  int d = (54 * 1024) / (kWarps * slot_bytes(bits, mb, nh));
+// shared-memory stage of one k32 block for a CTA: [4 tiles x 32 lanes x weights][4 x 32 x 8 B metadata][4 x 8 cols x 16 B
+// scales][MC activation rows x 80 B]
+constexpr int kActRow = 80;   // odd multiple of 16 bytes: the 8 rows of an ldmatrix phase hit distinct banks
+constexpr int w_bytes(int bits) { return 32 * (bits == 4 ? 16 : 32); }
+constexpr int e_off(int bits) { return 4 * w_bytes(bits); }
+constexpr int s_off(int bits) { return e_off(bits) + 4 * 256; }
+constexpr int a_off(int bits) { return s_off(bits) + 4 * 128; }
+constexpr int stage_bytes(int bits, int mc) { return a_off(bits) + mc * kActRow; }
+// ring depth: <= 54 KB per 128-thread CTA (4 CTAs per SM), <= 100 KB per 256-thread CTA (2 per SM)
+constexpr int ring_depth(int bits, int mc, int mh) {
+  int d = ((mh == 1 ? 54 : 100) * 1024) / stage_bytes(bits, mc);
   return d > 8 ? 8 : d;
 }
 
 }  // namespace m24
 
-// NH = 8-row activation halves per 16-row block that carry real rows (1 when M <= 8: half the tensor-core work)
-template <int BITS, int MB, bool GROUPED, int NH>
-__global__ void __launch_bounds__(m24::kThreads, 4)
+// MB = 16-row blocks per warp, NH = 8-row halves of a block that carry real rows (1 when M <= 8: half the tensor-core
+// work), MH = groups of four warps (each group takes 16 MB rows of the same four tiles)
+template <int BITS, int MB, bool GROUPED, int NH, int MH>
+__global__ void __launch_bounds__(128 * MH, MH == 1 ? 4 : 2)
 marlin24_gemm_kernel(const m24::Args args) {
   using namespace m24;
   constexpr int WPL = BITS == 4 ? 4 : 8;   // packed int32 per lane per (k32 block, 64-column tile)
-  constexpr int MC = 16 * MB;              // activation rows per pass
+  constexpr int MCW = 16 * MB;             // activation rows per warp
+  constexpr int MC = MCW * MH;             // activation rows per CTA pass
   constexpr int NACC = 32 * MB;            // fp32 accumulators per thread
+  constexpr int THREADS = 128 * MH;
+  constexpr int WB = w_bytes(BITS), E_OFF = e_off(BITS), S_OFF = s_off(BITS), A_OFF = a_off(BITS);
+  constexpr int STAGE = stage_bytes(BITS, MC);
+  constexpr int P = ring_depth(BITS, MC, MH);
+  static_assert(P >= 3, "ring too shallow");
   extern __shared__ __align__(16) uint8_t smem24[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tw = warp & 3, mh = warp >> 2;
   const int col = lane >> 2, q = lane & 3;
-  const int t = blockIdx.x / args.splits, sp = blockIdx.x - t * args.splits;
+  const int ct = blockIdx.x / args.splits, sp = blockIdx.x - ct * args.splits;
+  const int t = ct * 4 + tw;
+  const bool tile_ok = t < args.n_tiles;   // N is a multiple of 128, not of 256: the last CTA may own two tiles
   const int m0 = blockIdx.y * MC;
   const int KB = args.K / 32;
   const int kb0 = sp * args.kb_per_split;
   const int kb1 = min(KB, kb0 + args.kb_per_split);
+  const int n_it = kb1 - kb0;
   const int wrow = args.N * (BITS == 4 ? 2 : 4);
-  // (walking the k32 blocks in a per-CTA rotated order, so that the SMs do not all ask L2 for the same activation lines at
-  // the same moment, was measured: no gain, and it breaks the DRAM page locality of neighbouring tiles.)
-  const int n_it = (kb1 - kb0 + kWarps - 1) / kWarps;
-  auto kb_of = [&](int i) { return i < n_it ? kb0 + i * kWarps + warp : kb1; };   // k32 block of this warp's i-th iteration
+
+  const uint32_t smem_base = ptx::smem_u32(smem24);
+  // weights, metadata, scales: group 0 of warps copies them (lane-private slots; the other group reads the same slots)
+  const bool w_issuer = tile_ok && mh == 0;
   const uint32_t* wp = args.Bq + (size_t)t * (32 * WPL) + lane * WPL;
   const uint32_t* mp = args.meta + (size_t)t * 64 + lane;
   const __half* sp_ptr = args.scales + (size_t)t * 64 + col * 8;
+  const uint32_t w_dst = smem_base + tw * WB + lane * (WPL * 4);
+  const uint32_t e_dst = smem_base + E_OFF + tw * 256 + lane * 8;
+  const uint32_t s_dst = smem_base + S_OFF + tw * 128 + col * 16;
+  // activations: thread c copies 16-byte chunk c & 3 of row c >> 2 of the pass (rows beyond M are zero-filled)
+  constexpr int A_ROWS = NH == 1 ? 8 : MC;
+  const int a_row = threadIdx.x >> 2;
+  const bool a_issuer = a_row < A_ROWS;
+  const uint32_t a_bytes = (a_issuer && m0 + a_row < args.M) ? 16u : 0u;
+  const __half* a_src = args.A + (size_t)(a_bytes ? m0 + a_row : 0) * args.lda + (threadIdx.x & 3) * 8;
+  const uint32_t a_dst = smem_base + A_OFF + a_row * kActRow + (threadIdx.x & 3) * 16;
+  const uint32_t a_frag = smem_base + A_OFF + (mh * MCW + (lane & 7)) * kActRow + (lane >> 3) * 16;
 
-  // Each lane streams ITS OWN 16 (32) bytes of weights, 8 bytes of metadata and 16 bytes of scales of a k32 block into a
-  // private part of a kPrefetch-deep shared-memory ring with cp.async and reads the same bytes back later (no cross-lane
-  // hazard).  The activation fragments ride the same ring: each 8-row half block is 8 x 64 bytes, copied by the warp as 32
-  // 16-byte cp.async (rows beyond M zero-filled) into rows 80 bytes apart and read back with ONE ldmatrix.x4 whose matrix i
-  // is the 16-byte column i of the 8 rows -- exactly word 4 i + q of row col, the B fragment of mma.sp.  History
-  // (profiles/r2_m24_ncu.txt): with the activations as LDGs every warp iteration stalled ~2000 clk on the first HMMA.SP
-  // (long scoreboard) however far ahead they were issued; as 4-byte cp.async per fragment word the MIO queue became the
-  // limiter (12 LDGSTS per iteration).
-  constexpr int LANE_BYTES = BITS == 4 ? 48 : 80;   // odd multiple of 16: a quarter warp's 16-byte reads hit distinct banks
-  constexpr int ACT_ROW = 80;                       // same for the ldmatrix rows
-  constexpr int ACT_OFF = 32 * LANE_BYTES;
-  constexpr int SLOT_BYTES = m24::slot_bytes(BITS, MB, NH);
-  constexpr int kPrefetch = m24::prefetch_depth(BITS, MB, NH);
-  const uint32_t ring_off = (uint32_t)warp * (kPrefetch * SLOT_BYTES);
-  const uint32_t lane_off = ring_off + (uint32_t)lane * LANE_BYTES;
-  const uint32_t ring = ptx::smem_u32(smem24) + lane_off;
-  const uint32_t act_dst = ptx::smem_u32(smem24) + ring_off + ACT_OFF + (lane >> 2) * ACT_ROW + (lane & 3) * 16;
-  const uint32_t act_src = ptx::smem_u32(smem24) + ring_off + ACT_OFF + (lane & 7) * ACT_ROW + (lane >> 3) * 16;
-  const __half* arow[MB][NH];
-  uint32_t arow_bytes[MB][NH];   // 16 = real row, 0 = beyond M (cp.async zero-fills)
-#pragma unroll
-  for (int mb = 0; mb < MB; ++mb)
-#pragma unroll
-    for (int h = 0; h < NH; ++h) {
-      const int m = m0 + 16 * mb + 8 * h + col;
-      arow_bytes[mb][h] = m < args.M ? 16u : 0u;
-      arow[mb][h] = args.A + (size_t)(m < args.M ? m : 0) * args.lda + q * 8;
-    }
   auto issue_weights = [&](int slot, int kb) {
-    if (kb < kb1) {
-      const uint32_t dst = ring + slot * SLOT_BYTES;
+    if (w_issuer) {
+      const uint32_t so = slot * STAGE;
       const uint32_t* w = wp + (size_t)kb * wrow;
-      cp_async16(dst, w);
-      if (BITS == 8) cp_async16(dst + 16, w + 4);
-      if (GROUPED) cp_async16(dst + WPL * 4, sp_ptr + (size_t)(kb >> 2) * args.N);   // group_size 128 = 4 k32 blocks
-      cp_async4(dst + WPL * 4 + 16, mp + (size_t)kb * args.N);
-      cp_async4(dst + WPL * 4 + 20, mp + (size_t)kb * args.N + 32);
+      cp_async16(w_dst + so, w);
+      if (BITS == 8) cp_async16(w_dst + so + 16, w + 4);
+      cp_async4(e_dst + so, mp + (size_t)kb * args.N);
+      cp_async4(e_dst + so + 4, mp + (size_t)kb * args.N + 32);
+      if (GROUPED && q == 0) cp_async16(s_dst + so, sp_ptr + (size_t)(kb >> 2) * args.N);   // group_size 128 = 4 k32 blocks
     }
   };
   auto issue_acts = [&](int slot, int kb) {
-    if (kb < kb1) {
-#pragma unroll
-      for (int mb = 0; mb < MB; ++mb)
-#pragma unroll
-        for (int h = 0; h < NH; ++h)
-          cp_async16_zfill(act_dst + slot * SLOT_BYTES + (mb * NH + h) * (8 * ACT_ROW), arow[mb][h] + kb * 32, arow_bytes[mb][h]);
-    }
+    if (a_issuer) cp_async16_zfill(a_dst + slot * STAGE, a_src + kb * 32, a_bytes);
   };
-  auto read_stage = [&](Stage<BITS, MB, NH>& st_, int slot) {
-    const uint8_t* src = smem24 + lane_off + slot * SLOT_BYTES;
-    const uint4 v0 = *reinterpret_cast<const uint4*>(src);
-    st_.w[0] = v0.x; st_.w[1] = v0.y; st_.w[2] = v0.z; st_.w[3] = v0.w;
-    if (BITS == 8) {
-      const uint4 v1 = *reinterpret_cast<const uint4*>(src + 16);
-      st_.w[4 % WPL] = v1.x; st_.w[5 % WPL] = v1.y; st_.w[6 % WPL] = v1.z; st_.w[7 % WPL] = v1.w;
-    }
-    const uint2 e = *reinterpret_cast<const uint2*>(src + WPL * 4 + 16);
-    st_.e[0] = e.x; st_.e[1] = e.y;
-    if (GROUPED) {
-      const uint4 sv = *reinterpret_cast<const uint4*>(src + WPL * 4);
-      st_.s[0] = sv.x; st_.s[1] = sv.y; st_.s[2] = sv.z; st_.s[3] = sv.w;
-    }
-#pragma unroll
-    for (int mb = 0; mb < MB; ++mb)
-#pragma unroll
-      for (int h = 0; h < NH; ++h) ldmatrix_x4(st_.b[mb][h], act_src + slot * SLOT_BYTES + (mb * NH + h) * (8 * ACT_ROW));
-  };
+
   // weights / metadata / scales do not depend on the previous kernel: start streaming them before the PDL wait; the
-  // activations follow as kPrefetch more groups.  wait_group<kPrefetch-1> in iteration i then covers both halves of stage i
-  // (groups retire in order: W0..W{P-1}, A0..A{P-1}, then one combined group per iteration).
+  // activations follow as P-1 more groups.  wait_group<P-2> in iteration i then covers both halves of stage i (groups
+  // retire in order: W0..W{P-2}, A0..A{P-2}, then one combined group per iteration).
 #pragma unroll
-  for (int u = 0; u < kPrefetch; ++u) { issue_weights(u, kb_of(u)); cp_async_commit(); }
+  for (int u = 0; u < P - 1; ++u) { if (u < n_it) issue_weights(u, kb0 + u); cp_async_commit(); }
   pdl_wait();
   pdl_launch_dependents();
 #pragma unroll
-  for (int u = 0; u < kPrefetch; ++u) { issue_acts(u, kb_of(u)); cp_async_commit(); }
+  for (int u = 0; u < P - 1; ++u) { if (u < n_it) issue_acts(u, kb0 + u); cp_async_commit(); }
 
   float acc[NACC];
 #pragma unroll
   for (int i = 0; i < NACC; ++i) acc[i] = 0.f;
 
-  auto compute = [&](const Stage<BITS, MB, NH>& s) {
-#pragma unroll
-    for (int jj = 0; jj < 4; ++jj) {
-      uint32_t a[4];
-      if (BITS == 4) dequant4<__half>(s.w[jj], a);
-      else dequant8<__half>(s.w[(2 * jj) % WPL], s.w[(2 * jj + 1) % WPL], a);
-      if (GROUPED) {
-        const uint32_t s0 = bcast16(s.s[jj]), s1 = bcast16_hi(s.s[jj]);   // rows 0-7 (n), rows 8-15 (n + 4)
-        a[0] = Pack2<__half>::mul(a[0], s0);
-        a[2] = Pack2<__half>::mul(a[2], s0);
-        a[1] = Pack2<__half>::mul(a[1], s1);
-        a[3] = Pack2<__half>::mul(a[3], s1);
+  int slot = 0, slot_fill = P - 1;
+  for (int i = 0; i < n_it; ++i) {
+    cp_async_wait<P - 2>();   // this thread's copies of stage i have landed ...
+    __syncthreads();          // ... and everybody else's; everybody is also done reading the slot refilled below
+    if (i + P - 1 < n_it) { issue_weights(slot_fill, kb0 + i + P - 1); issue_acts(slot_fill, kb0 + i + P - 1); }
+    cp_async_commit();        // one group per iteration, issued or not, so that the wait always counts stages
+    if (tile_ok) {
+      const uint8_t* st = smem24 + slot * STAGE;
+      uint32_t w[WPL], s4[4] = {0, 0, 0, 0};
+      const uint4 v0 = *reinterpret_cast<const uint4*>(st + tw * WB + lane * (WPL * 4));
+      w[0] = v0.x; w[1] = v0.y; w[2] = v0.z; w[3] = v0.w;
+      if (BITS == 8) {
+        const uint4 v1 = *reinterpret_cast<const uint4*>(st + tw * WB + lane * (WPL * 4) + 16);
+        w[4 % WPL] = v1.x; w[5 % WPL] = v1.y; w[6 % WPL] = v1.z; w[7 % WPL] = v1.w;
       }
-      const uint32_t e = s.e[jj >> 1];
+      const uint2 e2 = *reinterpret_cast<const uint2*>(st + E_OFF + tw * 256 + lane * 8);
+      if (GROUPED) {
+        const uint4 sv = *reinterpret_cast<const uint4*>(st + S_OFF + tw * 128 + col * 16);
+        s4[0] = sv.x; s4[1] = sv.y; s4[2] = sv.z; s4[3] = sv.w;
+      }
+      uint32_t b[MB][NH][4];
 #pragma unroll
       for (int mb = 0; mb < MB; ++mb)
 #pragma unroll
-        for (int h = 0; h < NH; ++h) {
-          float* c = &acc[((mb * 4 + jj) * 2 + h) * 4];
-          if (jj & 1) mma_sp<1>(c, a, s.b[mb][h], e);
-          else mma_sp<0>(c, a, s.b[mb][h], e);
+        for (int h = 0; h < NH; ++h) ldmatrix_x4(b[mb][h], a_frag + slot * STAGE + (16 * mb + 8 * h) * kActRow);
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj) {
+        uint32_t a[4];
+        if (BITS == 4) dequant4<__half>(w[jj], a);
+        else dequant8<__half>(w[(2 * jj) % WPL], w[(2 * jj + 1) % WPL], a);
+        if (GROUPED) {
+          const uint32_t s0 = bcast16(s4[jj]), s1 = bcast16_hi(s4[jj]);   // rows 0-7 (n), rows 8-15 (n + 4)
+          a[0] = Pack2<__half>::mul(a[0], s0);
+          a[2] = Pack2<__half>::mul(a[2], s0);
+          a[1] = Pack2<__half>::mul(a[1], s1);
+          a[3] = Pack2<__half>::mul(a[3], s1);
         }
+        const uint32_t e = jj < 2 ? e2.x : e2.y;
+#pragma unroll
+        for (int mb = 0; mb < MB; ++mb)
+#pragma unroll
+          for (int h = 0; h < NH; ++h) {
+            float* c = &acc[((mb * 4 + jj) * 2 + h) * 4];
+            if (jj & 1) mma_sp<1>(c, a, b[mb][h], e);
+            else mma_sp<0>(c, a, b[mb][h], e);
+          }
+      }
     }
-  };
-
-  {
-    int slot = 0;
-    for (int i = 0; i < n_it; ++i) {
-      const bool live = kb_of(i) < kb1;      // the last round is ragged when the split is not a multiple of kWarps
-      cp_async_wait<kPrefetch - 1>();        // the oldest stage of this lane has landed ...
-      __syncwarp();                          // ... and of every other lane (the activation rows are shared by the warp)
-      Stage<BITS, MB, NH> st_;
-      read_stage(st_, slot);
-      __syncwarp();                          // everybody has read the slot before anybody refills it
-      const int kn = kb_of(i + kPrefetch);   // refill the slot just read (same lane: no hazard)
-      issue_weights(slot, kn);
-      issue_acts(slot, kn);
-      cp_async_commit();                     // one group per iteration, issued or not, so that the wait always counts stages
-      if (live) compute(st_);
-      if (++slot == kPrefetch) slot = 0;
-    }
-    cp_async_wait<0>();
+    if (++slot == P) slot = 0;
+    if (++slot_fill == P) slot_fill = 0;
   }
-  __syncthreads();   // the ring is reused as the reduction buffer below
+  cp_async_wait<0>();
+  __syncthreads();   // the ring is reused as the un-permute buffer below
 
-  // ---- sum the 8 warps' partials, un-permute into a [MC][64] tile ------------------------------------------------------
-  float* red = reinterpret_cast<float*>(smem24);
-  float* tile = red + kWarps * NACC * 32;
+  // ---- every warp un-permutes its own [MCW][64] outputs through shared memory ---------------------------------------------
+  constexpr int TP = 65;   // row pitch in floats
+  float* tile = reinterpret_cast<float*>(smem24) + warp * (MCW * TP);
 #pragma unroll
-  for (int i = 0; i < NACC; ++i) red[(warp * NACC + i) * 32 + lane] = acc[i];
-  __syncthreads();
-  for (int idx = threadIdx.x; idx < NACC * 32; idx += kThreads) {
-    const int a = idx >> 5, l = idx & 31;
-    float v = 0.f;
-#pragma unroll
-    for (int w = 0; w < kWarps; ++w) v += red[(w * NACC + a) * 32 + l];
+  for (int a = 0; a < NACC; ++a) {
     const int ci = a & 3, h = (a >> 2) & 1, jj = (a >> 3) & 3, mb = a >> 5;
-    const int n_local = 8 * (l >> 2) + jj + 4 * (ci >> 1);
-    const int m_local = 16 * mb + 8 * h + 2 * (l & 3) + (ci & 1);
-    tile[m_local * 64 + n_local] = v;
+    if (NH == 1 && h == 1) continue;
+    const int n_local = 8 * col + jj + 4 * (ci >> 1);
+    const int m_local = 16 * mb + 8 * h + 2 * q + (ci & 1);
+    tile[m_local * TP + n_local] = acc[a];
   }
-  __syncthreads();
+  __syncwarp();
 
-  const int m_valid = min(MC, args.M - m0);
-  __half* cdst = args.C + (size_t)m0 * args.N + (size_t)t * 64;
-  auto finish = [&](int idx, float v) {
-    const int m = idx >> 6, n = idx & 63;
+  const int mw0 = m0 + mh * MCW;                       // first row of this warp
+  const int m_valid = max(0, min(NH == 1 ? 8 : MCW, args.M - mw0));
+  auto finish = [&](int r, int n, float v) {
     if (!GROUPED) v *= __half2float(args.scales[(size_t)t * 64 + n]);
-    cdst[(size_t)m * args.N + n] = __float2half_rn(v);
+    args.C[(size_t)(mw0 + r) * args.N + (size_t)t * 64 + n] = __float2half_rn(v);
   };
   if (args.splits == 1) {
-    for (int idx = threadIdx.x; idx < m_valid * 64; idx += kThreads) finish(idx, tile[idx]);
+    if (tile_ok)
+      for (int idx = lane; idx < m_valid * 64; idx += 32) finish(idx >> 6, idx & 63, tile[(idx >> 6) * TP + (idx & 63)]);
     return;
   }
   // ---- K splits: fp32 slots + ticket; the last split to arrive sums the slots in split order ------------------------------
   __shared__ int s_last;
-  const int tile_id = blockIdx.y * args.n_tiles + t;
-  float* slots = args.scratch + (size_t)tile_id * args.splits * (MC * 64);
-  for (int idx = threadIdx.x; idx < m_valid * 64; idx += kThreads) __stcg(slots + (size_t)sp * (MC * 64) + idx, tile[idx]);
-  __threadfence();
+  const int cta_id = blockIdx.y * args.n_ctiles + ct;
+  float* cta_slots = args.scratch + (size_t)cta_id * args.splits * (MC * 256);
+  if (tile_ok) {
+    float* mine = cta_slots + (size_t)sp * (MC * 256) + (size_t)(mh * MCW) * 256 + tw * 64;
+    for (int idx = lane; idx < m_valid * 64; idx += 32) __stcg(mine + (idx >> 6) * 256 + (idx & 63), tile[(idx >> 6) * TP + (idx & 63)]);
+  }
   __syncthreads();
   if (threadIdx.x == 0) {
-    const int old = atomicAdd(&args.counters[tile_id], 1);
+    __threadfence();   // release: cumulative over the CTA's slot writes ordered before it by the barrier
+    const int old = atomicAdd(&args.counters[cta_id], 1);
     s_last = (old == args.splits - 1);
-    if (s_last) args.counters[tile_id] = 0;
+    if (s_last) args.counters[cta_id] = 0;
+    __threadfence();   // acquire
   }
   __syncthreads();
   if (!s_last) return;
-  __threadfence();
-  for (int idx = threadIdx.x; idx < m_valid * 64; idx += kThreads) {
-    float v = 0.f;
-    for (int s = 0; s < args.splits; ++s) v += __ldcg(slots + (size_t)s * (MC * 64) + idx);
-    finish(idx, v);
+  // the whole CTA sums the [rows][256] slot planes, four columns per thread, four splits in flight per accumulator (the
+  // ncu capture of a per-warp scalar loop showed this tail as the top stall of the kernel)
+  const int rows = min(NH == 1 ? 8 : MC, args.M - m0);
+  const int n_cols = min(256, args.N - ct * 256);
+  for (int idx = threadIdx.x; idx < rows * 64; idx += THREADS) {
+    const int r = idx >> 6, n = (idx & 63) * 4;
+    if (n >= n_cols) continue;
+    const float* src = cta_slots + r * 256 + n;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    int s2 = 0;
+    for (; s2 + 4 <= args.splits; s2 += 4) {
+      const float4 x0 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(s2 + 0) * (MC * 256)));
+      const float4 x1 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(s2 + 1) * (MC * 256)));
+      const float4 x2 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(s2 + 2) * (MC * 256)));
+      const float4 x3 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(s2 + 3) * (MC * 256)));
+      v.x += x0.x; v.y += x0.y; v.z += x0.z; v.w += x0.w;
+      v.x += x1.x; v.y += x1.y; v.z += x1.z; v.w += x1.w;
+      v.x += x2.x; v.y += x2.y; v.z += x2.z; v.w += x2.w;
+      v.x += x3.x; v.y += x3.y; v.z += x3.z; v.w += x3.w;
+    }
+    for (; s2 < args.splits; ++s2) {
+      const float4 x0 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)s2 * (MC * 256)));
+      v.x += x0.x; v.y += x0.y; v.z += x0.z; v.w += x0.w;
+    }
+    const size_t nn = (size_t)ct * 256 + n;
+    if (!GROUPED) {
+      const __half2 c0 = *reinterpret_cast<const __half2*>(args.scales + nn), c1 = *reinterpret_cast<const __half2*>(args.scales + nn + 2);
+      v.x *= __low2float(c0); v.y *= __high2float(c0); v.z *= __low2float(c1); v.w *= __high2float(c1);
+    }
+    const __half2 o0 = __floats2half2_rn(v.x, v.y), o1 = __floats2half2_rn(v.z, v.w);
+    uint2 o;
+    o.x = *reinterpret_cast<const uint32_t*>(&o0);
+    o.y = *reinterpret_cast<const uint32_t*>(&o1);
+    *reinterpret_cast<uint2*>(args.C + (size_t)(m0 + r) * args.N + nn) = o;
   }
 }
 
 // ---- host side -------------------------------------------------------------------------------------------------------
-template <int BITS, int MB, bool GROUPED, int NH>
+template <int BITS, int MB, bool GROUPED, int NH, int MH>
 static int launch_m24(m24::Args a, cudaStream_t st) {
   using namespace m24;
-  constexpr int MC = 16 * MB;
+  constexpr int MC = 16 * MB * MH;
   const int KB = a.K / 32;
   const int m_chunks = (a.M + MC - 1) / MC;
   a.n_tiles = a.N / 64;
-  // ~4 CTAs per SM; a split is at least 8 k32 blocks per warp (amortises the CTA prologue / reduction) and a whole
-  // number of scale groups
-  const int target = num_sms() * 4;
-  int splits = target / (a.n_tiles * m_chunks);
-  int min_kb = 8 * kWarps;
-  if (GROUPED) { const int gb = (a.K / a.num_groups) / 32; if (min_kb % gb) min_kb = ((min_kb + gb - 1) / gb) * gb; }
+  a.n_ctiles = (a.n_tiles + 3) / 4;
+  // one wave of resident CTAs (4 per SM at 128 threads, 2 at 256); a split is at least 16 k32 blocks (amortises the prologue
+  // and the slot traffic) and a whole number of scale groups
+  const int target = num_sms() * (MH == 1 ? 4 : 2);
+  int splits = target / (a.n_ctiles * m_chunks);
+  const int min_kb = 16;
   if (splits > KB / min_kb) splits = KB / min_kb;
   if (splits < 1) splits = 1;
   int kbps = (KB + splits - 1) / splits;
-  if (GROUPED) { const int gb = (a.K / a.num_groups) / 32; kbps = ((kbps + gb - 1) / gb) * gb; }
+  if (GROUPED) kbps = ((kbps + 3) / 4) * 4;   // group_size 128 = 4 k32 blocks
   splits = (KB + kbps - 1) / kbps;
   a.splits = splits;
   a.kb_per_split = kbps;
   int dev = 0;
   cudaGetDevice(&dev);
   GemmScratch sc;
-  if (int e = gemm_ensure_scratch(dev, splits > 1 ? (size_t)a.n_tiles * m_chunks * splits * MC * 64 : 1, a.n_tiles * m_chunks, st, &sc)) return e;
+  if (int e = gemm_ensure_scratch(dev, splits > 1 ? (size_t)a.n_ctiles * m_chunks * splits * MC * 256 : 1, a.n_ctiles * m_chunks, st, &sc)) return e;
   a.scratch = sc.partials;
   a.counters = sc.counters;
-  const size_t smem_red = (size_t)(kWarps * 32 * MB * 32 + MC * 64) * 4;
-  const size_t smem_ring = (size_t)kWarps * prefetch_depth(BITS, MB, NH) * slot_bytes(BITS, MB, NH);
-  const size_t smem = smem_red > smem_ring ? smem_red : smem_ring;
-  auto kern = marlin24_gemm_kernel<BITS, MB, GROUPED, NH>;
+  const size_t smem_tile = (size_t)(4 * MH) * (16 * MB) * 65 * 4;
+  const size_t smem_ring = (size_t)ring_depth(BITS, MC, MH) * stage_bytes(BITS, MC);
+  const size_t smem = smem_tile > smem_ring ? smem_tile : smem_ring;
+  auto kern = marlin24_gemm_kernel<BITS, MB, GROUPED, NH, MH>;
   static bool attr_set[64] = {};
   if (!attr_set[dev & 63]) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     attr_set[dev & 63] = true;
   }
-  cudaError_t e = launch_pdl(kern, dim3(a.n_tiles * splits, m_chunks), dim3(kThreads), smem, st, a);
+  cudaError_t e = launch_pdl(kern, dim3(a.n_ctiles * splits, m_chunks), dim3(128 * MH), smem, st, a);
   if (e != cudaSuccess) return set_error(B200_ECUDA, "gptq_marlin_24_gemm launch: %s", cudaGetErrorString(e));
   return B200_OK;
 }
 
 template <int BITS, bool GROUPED>
 static int dispatch_m24(const m24::Args& a, cudaStream_t st) {
-  if (a.M <= 8) return launch_m24<BITS, 1, GROUPED, 1>(a, st);
-  if (a.M <= 16) return launch_m24<BITS, 1, GROUPED, 2>(a, st);
-  return launch_m24<BITS, 2, GROUPED, 2>(a, st);   // M > 32: passes of 32 rows (grid.y), weights re-read through L2
+  if (a.M <= 8) return launch_m24<BITS, 1, GROUPED, 1, 1>(a, st);
+  if (a.M <= 16) return launch_m24<BITS, 1, GROUPED, 2, 1>(a, st);
+  if (a.M <= 32) return launch_m24<BITS, 2, GROUPED, 2, 1>(a, st);
+  return launch_m24<BITS, 2, GROUPED, 2, 2>(a, st);   // M > 64: passes of 64 rows (grid.y), weights re-read through L2
 }
 
 }  // namespace b200
@@ -382,7 +393,7 @@ extern "C" int b200_gptq_marlin_24_gemm(void* c, const void* a, const int32_t* b
   ga.M = (int)size_m; ga.N = (int)size_n; ga.K = (int)size_k;
   ga.lda = lda;
   ga.num_groups = num_groups;
-  ga.splits = 1; ga.kb_per_split = 0; ga.n_tiles = 0;
+  ga.splits = 1; ga.kb_per_split = 0; ga.n_tiles = 0; ga.n_ctiles = 0;
   cudaStream_t st = (cudaStream_t)stream;
   int rc;
   if (num_groups > 1) rc = num_bits == 4 ? dispatch_m24<4, true>(ga, st) : dispatch_m24<8, true>(ga, st);
