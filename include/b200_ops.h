@@ -119,6 +119,23 @@ int b200_gptq_marlin_24_gemm(void* c, const void* a, const int32_t* b_q_weight, 
                              int num_bits, int64_t size_m, int64_t size_n, int64_t size_k,
                              int64_t lda, int num_groups, int dtype, void* stream);
 
+/* ---- Sparse-Marlin 2:4 without any allocation ---------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments,
+ * preconditions, kernel and results as b200_gptq_marlin_24_gemm; the K-split scratch is a file-scope
+ * `static __device__` array of the sizes below (20 MiB + 16 KiB, held by every GPU that loads the library
+ * until exit), so the call performs no cudaMalloc / cudaFree / allocating library routine.  A problem whose
+ * K-split needs more (the decomposition is sized from the SM count: every shape fits on a 148-SM B200)
+ * returns B200_EINVAL with the required and available sizes.  All calls share the array: calls that overlap
+ * on the GPU (different streams or threads on one device) race; calls on one stream are safe. */
+#define B200_M24_STATIC_MAX_PARTIAL_FLOATS (5u * 1024u * 1024u)
+#define B200_M24_STATIC_MAX_COUNTERS 4096
+int b200_gptq_marlin_24_gemm_static(void* c, const void* a, const int32_t* b_q_weight,
+                                    const int16_t* b_meta, const void* b_scales, int32_t* workspace,
+                                    int64_t workspace_numel, int num_bits, int64_t size_m,
+                                    int64_t size_n, int64_t size_k, int64_t lda, int num_groups,
+                                    int dtype, void* stream);
+
 /* ---- W8A8 scaled GEMM: csrc/ops.h:96-102, cutlass_w8a8/scaled_mm_entry.cu:48-100 -------------------
  * out[M,N] = a_scales (.) (b_scales (.) (a[M,K] . b[K,N])) (+ bias); a row-major (lda elements),
  * b COLUMN-major (ldb = b.stride(1) elements), out row-major (ldc); a_scales fp32 numel 1 or M,

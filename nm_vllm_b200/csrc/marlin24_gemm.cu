@@ -361,6 +361,95 @@ static int dispatch_m24(const m24::Args& a, cudaStream_t st) {
   return launch_m24<BITS, 2, GROUPED, 2, 2>(a, st);   // M > 64: passes of 64 rows (grid.y), weights re-read through L2
 }
 
+// ---- allocation-free variant (b200_gptq_marlin_24_gemm_static) ------------------------------------------------------------
+// The K-split slots and tile counters live in file-scope device arrays instead of the grow-on-demand scratch of
+// gemm_ensure_scratch(): nothing is allocated, ever.  Every GPU that loads the library holds the 20 MiB + 16 KiB until exit.
+// All calls share the arrays: calls that overlap on the GPU (two streams, or two threads on one device) race.
+constexpr size_t kStaticPartialFloats = B200_M24_STATIC_MAX_PARTIAL_FLOATS;   // 5 Mi floats = 20 MiB
+constexpr int kStaticCounters = B200_M24_STATIC_MAX_COUNTERS;                 // 4096 ints
+static __device__ __align__(256) float m24_static_partials[kStaticPartialFloats];
+static __device__ __align__(256) int m24_static_counters[kStaticCounters];
+
+// In host code the two names above are host-side stand-ins, not device addresses: the addresses a kernel can use come from
+// cudaGetSymbolAddress, once per device, with that device current.
+static int m24_static_scratch(int dev, float** partials, int** counters) {
+  static float* p_cache[64];
+  static int* c_cache[64];
+  static bool have[64];
+  if (dev < 0 || dev >= 64) return set_error(B200_EINVAL, "gptq_marlin_24_gemm_static: device index %d out of range", dev);
+  if (!have[dev]) {
+    float* p = nullptr;
+    int* c = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&p, m24_static_partials);
+    if (e != cudaSuccess) return set_error(B200_ECUDA, "gptq_marlin_24_gemm_static: cudaGetSymbolAddress(partials): %s", cudaGetErrorString(e));
+    e = cudaGetSymbolAddress((void**)&c, m24_static_counters);
+    if (e != cudaSuccess) return set_error(B200_ECUDA, "gptq_marlin_24_gemm_static: cudaGetSymbolAddress(counters): %s", cudaGetErrorString(e));
+    p_cache[dev] = p;
+    c_cache[dev] = c;
+    have[dev] = true;
+  }
+  *partials = p_cache[dev];
+  *counters = c_cache[dev];
+  return B200_OK;
+}
+
+// same work decomposition and kernel as launch_m24; only the origin of the scratch differs
+template <int BITS, int MB, bool GROUPED, int NH, int MH>
+static int launch_m24_static(m24::Args a, cudaStream_t st) {
+  using namespace m24;
+  constexpr int MC = 16 * MB * MH;
+  const int KB = a.K / 32;
+  const int m_chunks = (a.M + MC - 1) / MC;
+  a.n_tiles = a.N / 64;
+  a.n_ctiles = (a.n_tiles + 3) / 4;
+  const int target = num_sms() * (MH == 1 ? 4 : 2);
+  int splits = target / (a.n_ctiles * m_chunks);
+  const int min_kb = 16;
+  if (splits > KB / min_kb) splits = KB / min_kb;
+  if (splits < 1) splits = 1;
+  int kbps = (KB + splits - 1) / splits;
+  if (GROUPED) kbps = ((kbps + 3) / 4) * 4;
+  splits = (KB + kbps - 1) / kbps;
+  a.splits = splits;
+  a.kb_per_split = kbps;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (int e = m24_static_scratch(dev, &a.scratch, &a.counters)) return e;
+  if (splits > 1) {
+    const size_t need = (size_t)a.n_ctiles * m_chunks * splits * MC * 256;
+    const size_t need_counters = (size_t)a.n_ctiles * m_chunks;
+    if (need > kStaticPartialFloats || need_counters > (size_t)kStaticCounters)
+      return set_error(B200_EINVAL,
+                       "gptq_marlin_24_gemm_static: M=%d N=%d K=%d needs %zu fp32 K-split slots and %zu tile counters; the static "
+                       "scratch holds %zu and %d (use b200_gptq_marlin_24_gemm)",
+                       a.M, a.N, a.K, need, need_counters, kStaticPartialFloats, kStaticCounters);
+    // the counters must start at zero; the kernel leaves them zero, but an aborted earlier call may not have.  The slots
+    // are written before they are read, so they need no clearing.
+    cudaError_t e = cudaMemsetAsync(a.counters, 0, need_counters * sizeof(int), st);
+    if (e != cudaSuccess) return set_error(B200_ECUDA, "gptq_marlin_24_gemm_static: clearing the tile counters: %s", cudaGetErrorString(e));
+  }
+  const size_t smem_tile = (size_t)(4 * MH) * (16 * MB) * 65 * 4;
+  const size_t smem_ring = (size_t)ring_depth(BITS, MC, MH) * stage_bytes(BITS, MC);
+  const size_t smem = smem_tile > smem_ring ? smem_tile : smem_ring;
+  auto kern = marlin24_gemm_kernel<BITS, MB, GROUPED, NH, MH>;
+  static bool attr_set[64] = {};
+  if (!attr_set[dev & 63]) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    attr_set[dev & 63] = true;
+  }
+  cudaError_t e = launch_pdl(kern, dim3(a.n_ctiles * splits, m_chunks), dim3(128 * MH), smem, st, a);
+  if (e != cudaSuccess) return set_error(B200_ECUDA, "gptq_marlin_24_gemm_static launch: %s", cudaGetErrorString(e));
+  return B200_OK;
+}
+
+template <int BITS, bool GROUPED>
+static int dispatch_m24_static(const m24::Args& a, cudaStream_t st) {
+  if (a.M <= 8) return launch_m24_static<BITS, 1, GROUPED, 1, 1>(a, st);
+  if (a.M <= 16) return launch_m24_static<BITS, 1, GROUPED, 2, 1>(a, st);
+  if (a.M <= 32) return launch_m24_static<BITS, 2, GROUPED, 2, 1>(a, st);
+  return launch_m24_static<BITS, 2, GROUPED, 2, 2>(a, st);
+}
+
 }  // namespace b200
 
 extern "C" int b200_gptq_marlin_24_gemm(void* c, const void* a, const int32_t* b_q_weight, const int16_t* b_meta,
@@ -400,5 +489,49 @@ extern "C" int b200_gptq_marlin_24_gemm(void* c, const void* a, const int32_t* b
   else rc = num_bits == 4 ? dispatch_m24<4, false>(ga, st) : dispatch_m24<8, false>(ga, st);
   if (rc) return rc;
   B200_LAUNCH_CHECK("gptq_marlin_24_gemm");
+  return B200_OK;
+}
+
+// Allocation-free variant of b200_gptq_marlin_24_gemm (no counterpart in the reference; see include/b200_ops.h).  Same
+// arguments, preconditions, kernel and results; the K-split scratch is the file-scope device array above.  Calls no
+// cudaMalloc / cudaFree / allocating library routine.
+extern "C" int b200_gptq_marlin_24_gemm_static(void* c, const void* a, const int32_t* b_q_weight, const int16_t* b_meta,
+                                               const void* b_scales, int32_t* workspace, int64_t workspace_numel,
+                                               int num_bits, int64_t size_m, int64_t size_n, int64_t size_k, int64_t lda,
+                                               int num_groups, int dtype, void* stream) {
+  using namespace b200;
+  (void)workspace;
+  B200_CHECK(num_bits == 4 || num_bits == 8, "num_bits must be 4 or 8. Got = %d", num_bits);
+  B200_CHECK(dtype == B200_F16, "gptq_marlin_24_gemm_static only supports float16 activations (gptq_marlin_24.py:145-147)");
+  B200_CHECK(size_m >= 0 && size_m <= INT32_MAX && size_n > 0 && size_n <= INT32_MAX && size_k > 0 && size_k <= INT32_MAX,
+             "sizes out of range: m=%lld n=%lld k=%lld", (long long)size_m, (long long)size_n, (long long)size_k);
+  B200_CHECK(size_k % 128 == 0, "size_k = %lld is not divisible by tile_k_size = 128", (long long)size_k);
+  B200_CHECK(size_n % 128 == 0, "size_n = %lld is not divisible by tile_n_size = 128", (long long)size_n);
+  B200_CHECK(num_groups >= 1 && size_k % num_groups == 0, "size_k = %lld is not divisible by b_scales.size(0) = %d",
+             (long long)size_k, num_groups);
+  const int gs = (int)(size_k / num_groups);
+  if (num_groups > 1) B200_CHECK(gs == 128, "Unexpected group_size = %d (Sparse-Marlin supports -1 and 128)", gs);
+  B200_CHECK(workspace_numel >= (size_n / 128) * 64, "workspace.numel = %lld is below min_workspace_size = %lld",
+             (long long)workspace_numel, (long long)((size_n / 128) * 64));
+  B200_CHECK((reinterpret_cast<uintptr_t>(a) & 15) == 0 && (lda * 2) % 16 == 0, "A must be 16-byte aligned with a 16-byte multiple row pitch");
+  if (size_m == 0) return B200_OK;
+  m24::Args ga;
+  ga.A = reinterpret_cast<const __half*>(a);
+  ga.Bq = reinterpret_cast<const uint32_t*>(b_q_weight);
+  ga.meta = reinterpret_cast<const uint32_t*>(b_meta);
+  ga.scales = reinterpret_cast<const __half*>(b_scales);
+  ga.C = reinterpret_cast<__half*>(c);
+  ga.scratch = nullptr;
+  ga.counters = nullptr;
+  ga.M = (int)size_m; ga.N = (int)size_n; ga.K = (int)size_k;
+  ga.lda = lda;
+  ga.num_groups = num_groups;
+  ga.splits = 1; ga.kb_per_split = 0; ga.n_tiles = 0; ga.n_ctiles = 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc;
+  if (num_groups > 1) rc = num_bits == 4 ? dispatch_m24_static<4, true>(ga, st) : dispatch_m24_static<8, true>(ga, st);
+  else rc = num_bits == 4 ? dispatch_m24_static<4, false>(ga, st) : dispatch_m24_static<8, false>(ga, st);
+  if (rc) return rc;
+  B200_LAUNCH_CHECK("gptq_marlin_24_gemm_static");
   return B200_OK;
 }
