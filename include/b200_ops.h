@@ -111,6 +111,16 @@ int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_weight, con
                           int64_t size_k, int64_t lda, int num_groups, int is_k_full, int dtype,
                           void* stream);
 
+/* Fused gate_up GEMM + SiluAndMul (decode step: MergedColumnParallelLinear gate_up_proj followed by SiluAndMul,
+ * vllm/model_executor/models/llama.py:74-90; replaces gptq_marlin_gemm + silu_and_mul, csrc/activation_kernels.cu:14-76,
+ * with one launch): out[M, N/2] = silu(g) * u where [g | u] = a . dequant(b_q_weight) is rounded to `dtype` first, so the
+ * result is bit-identical to the two-op chain.  Stored layouts are unchanged (the kernel pairs column n with n + N/2).
+ * size_n is the GEMM's N (= 2 x intermediate size, N/2 % 64 == 0); no act-order. */
+int b200_gptq_marlin_gemm_silu_and_mul(void* out, const void* a, const int32_t* b_q_weight, const void* b_scales,
+                                       int32_t* workspace, int64_t workspace_numel, int num_bits, int64_t size_m,
+                                       int64_t size_n, int64_t size_k, int64_t lda, int num_groups, int dtype,
+                                       void* stream);
+
 /* ---- Sparse-Marlin 2:4: csrc/ops.h:79-84, marlin/sparse/marlin_24_cuda_kernel.cu:1017-1125 --------
  * b_q_weight int32 [K/32, N*16/pf]; b_meta int16 [K/32, 2N] (viewed [K/16... see DESIGN.md);
  * b_scales fp16 [num_groups,N]; fp16 only (gptq_marlin_24.py:145-147). */
@@ -238,6 +248,23 @@ int b200_ar_dispose(int64_t ctx);
  * one-shot range where the stand-alone two-shot kernel is faster): run the two calls separately then.  Replaces RowParallelLinear.forward's GEMM -> tensor_model_parallel_all_reduce pair
  * (vllm/model_executor/layers/linear.py:779-803). */
 int b200_ar_fuse_next_gemm(int64_t ctx, int64_t m, int64_t n);
+
+/* ---- prefill attention over the paged cache: context_attention_fwd, vllm/attention/ops/prefix_prefill.py:674-799
+ * (Triton kernels :14-672 in the reference; caller PagedAttention.forward_prefix, vllm/attention/ops/paged_attn.py:185-216).
+ * o,q [tokens, num_heads, head_size]; k,v [tokens, num_kv_heads, head_size] (the call's new tokens); k_cache
+ * [NB, Hkv, head_size/8, block_size, 8], v_cache [NB, Hkv, head_size, block_size] of the same 16-bit dtype;
+ * block_tables int32 [batch, *] (row stride bt_stride); b_start_loc / b_seq_len / b_ctx_len int32 [batch]: first
+ * query token, total length and cached-context length of each sequence.  Query token i of a sequence attends to its
+ * b_ctx_len cached tokens and to new tokens 0..i; scale = 1/sqrt(head_size); sliding_window <= 0 disables the window;
+ * alibi_slopes float [num_heads] or NULL.  qkvo_strides = element strides {q tok, q head, k tok, k head, v tok, v head,
+ * o tok, o head}.  head_size % 8 == 0 and <= 128 (B200_ENOTSUP above). */
+int b200_context_attention_fwd(void* o, const void* q, const void* k, const void* v, const void* k_cache,
+                               const void* v_cache, const int32_t* block_tables, int64_t bt_stride,
+                               const int32_t* b_start_loc, const int32_t* b_seq_len, const int32_t* b_ctx_len,
+                               int batch, int max_input_len, int num_heads, int num_kv_heads, int head_size,
+                               int block_size, int x, const int64_t* qkvo_strides, int64_t kc_block_stride,
+                               int64_t kc_head_stride, int64_t vc_block_stride, int64_t vc_head_stride,
+                               const float* alibi_slopes, int sliding_window, int dtype, void* stream);
 
 #ifdef __cplusplus
 }

@@ -69,6 +69,17 @@ def rope_cache_paged_attention(out: torch.Tensor, exp_sums: Optional[torch.Tenso
                                              block_tables, seq_lens, block_size, max_seq_len, kv_cache_dtype, kv_scale)
 
 
+def context_attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, o: torch.Tensor, k_cache: torch.Tensor,
+                          v_cache: torch.Tensor, b_loc: torch.Tensor, b_start_loc: torch.Tensor, b_seq_len: torch.Tensor,
+                          b_ctx_len: torch.Tensor, max_input_len: int, alibi_slopes: Optional[torch.Tensor] = None,
+                          sliding_window: Optional[int] = None) -> None:
+    """Prefill attention over the paged cache, same signature as vllm/attention/ops/prefix_prefill.py:674-686 (Triton in
+    the reference, one CUDA kernel here): query token i of sequence b attends to the b_ctx_len[b] cached tokens of its
+    block-table row and to the call's new tokens 0..i (k, v); writes `o` in place."""
+    _ops().context_attention_fwd(q, k, v, o, k_cache, v_cache, b_loc, b_start_loc, b_seq_len, b_ctx_len, max_input_len,
+                                 alibi_slopes, 0 if sliding_window is None or sliding_window <= 0 else sliding_window)
+
+
 _Q_DTYPE = {"fp8": torch.float8_e4m3fn, "int8": torch.int8, "int8_token": torch.int8}
 
 
@@ -150,6 +161,14 @@ def gptq_marlin_gemm(a: torch.Tensor, b_q_weight: torch.Tensor, b_scales: torch.
                      size_k: int, is_k_full: bool) -> torch.Tensor:
     return _ops().gptq_marlin_gemm(a, b_q_weight, b_scales, g_idx, perm, workspace, num_bits, size_m, size_n, size_k,
                                    is_k_full)
+
+
+def gptq_marlin_gemm_silu_and_mul(a: torch.Tensor, b_q_weight: torch.Tensor, b_scales: torch.Tensor,
+                                  workspace: torch.Tensor, num_bits: int, size_m: int, size_n: int,
+                                  size_k: int) -> torch.Tensor:
+    """gate_up_proj + SiluAndMul in one launch (llama.py:74-90 issues gptq_marlin_gemm then silu_and_mul): returns
+    [size_m, size_n // 2], bit-identical to the two-op chain; the stored weight / scale layouts are untouched."""
+    return _ops().gptq_marlin_gemm_silu_and_mul(a, b_q_weight, b_scales, workspace, num_bits, size_m, size_n, size_k)
 
 
 # ---- fp8 / int8 activation quantizers: vllm/_custom_ops.py:284-350 --------------------------------------------------

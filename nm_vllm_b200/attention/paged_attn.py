@@ -1,7 +1,7 @@
 """`PagedAttention` + `PagedAttentionMetadata`: mirror of vllm/attention/ops/paged_attn.py:13-239 -- cache shape and
 views (:37-59), `write_to_paged_cache` (:62-79), `forward_decode` with the v1 / v2 heuristic and the
 tmp_out / exp_sums / max_logits allocation (:82-182), block maintenance (:213-239).  `forward_prefix` (prefill over a
-cached prefix, Triton in the reference) is not on the decode path and raises.  New: `forward_decode_fused` runs the
+cached prefix, Triton in the reference) runs the CUDA prefill kernel of csrc/attention_prefill.cu.  New: `forward_decode_fused` runs the
 step's rotary embedding, cache write and attention as one launch (csrc/attention_mma.cu) when the shape allows."""
 from dataclasses import dataclass
 from typing import List, Optional, Tuple
@@ -107,16 +107,24 @@ class PagedAttention:
                        alibi_slopes: Optional[torch.Tensor], sliding_window: Optional[int], kv_cache_dtype: str = "auto",
                        kv_scale: float = 1.0, scale: Optional[float] = None) -> torch.Tensor:
         """Prefill over a cached prefix (paged_attn.py:185-211 -> context_attention_fwd, prefix_prefill.py:674): query token i of
-        a sequence attends to the sequence's first context_len + i + 1 tokens.  The reference has already written the new
-        tokens' K / V into the paged cache at this point (write_to_paged_cache runs first, xformers.py:262-270), so causal
-        prefill IS paged decode attention with one row per QUERY TOKEN: same block-table row, seq_len = context_len + i + 1.
-        That is what this does, through paged_attention_v1 / v2 -- exact, but every query token re-reads its KV prefix
-        (served by L2 for neighbouring tokens): a functional path, not a tuned prefill kernel.  `key` / `value` are unused
-        (already in the cache); the reference's trailing arguments are extended with the cache dtype / scale it leaves implicit."""
-        del key, value, max_query_len
-        if sliding_window is not None:
-            raise NotImplementedError("sliding-window prefix attention")
+        a sequence attends to the sequence's first context_len + i + 1 tokens.  16-bit caches go through the prefill kernel
+        (`ops.context_attention_fwd`, csrc/attention_prefill.cu: context from the block-table cache, new tokens from `key` /
+        `value`, sliding window and ALiBi like the reference).  fp8 caches (which the reference's Triton kernel does not take
+        either) fall back to the observation that the new tokens' K / V are already in the paged cache at this point
+        (write_to_paged_cache runs first, xformers.py:262-270), so causal prefill IS paged decode attention with one row per
+        QUERY TOKEN -- exact, but every query token re-reads its KV prefix.  The reference's trailing arguments are extended
+        with the cache dtype / scale it leaves implicit."""
         num_tokens, num_heads, head_size = query.shape
+        if (kv_cache_dtype == "auto" and key is not None and value is not None and head_size <= 128 and head_size % 8 == 0
+                and (scale is None or abs(scale - float(head_size) ** -0.5) < 1e-7 * scale)):
+            # the reference's path: one prefill kernel over (cached context, new tokens), csrc/attention_prefill.cu
+            output = torch.empty_like(query)
+            ops.context_attention_fwd(query, key, value, output, key_cache, value_cache, block_tables, query_start_loc[:-1],
+                                      seq_lens_tensor, context_lens, max_query_len, alibi_slopes, sliding_window)
+            return output
+        del key, value, max_query_len
+        if sliding_window is not None and sliding_window > 0:
+            raise NotImplementedError("sliding-window prefix attention over an fp8 cache")
         num_kv_heads = value_cache.shape[1]
         if scale is None:
             scale = float(head_size) ** -0.5

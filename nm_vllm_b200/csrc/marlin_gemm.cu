@@ -219,11 +219,11 @@ extern "C" int b200_gemm_scratch_reserve(int64_t max_m, int64_t max_n) {
   return gemm_ensure_scratch(dev, want, (int)(tiles < (1u << 20) ? tiles : (1u << 20)), 0, nullptr);
 }
 
-extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_weight, const void* b_scales,
-                                     const int32_t* g_idx, const int32_t* perm, int32_t* workspace,
-                                     int64_t workspace_numel, int num_bits, int64_t size_m, int64_t size_n,
-                                     int64_t size_k, int64_t lda, int num_groups, int is_k_full, int dtype,
-                                     void* stream) {
+// silu: 0 = plain GEMM into c [M, N]; 1 = gate_up layer, c [M, N / 2] = silu_and_mul(GEMM) (see the header)
+static int marlin_gemm_impl(void* c, const void* a, const int32_t* b_q_weight, const void* b_scales, const int32_t* g_idx,
+                            const int32_t* perm, int32_t* workspace, int64_t workspace_numel, int num_bits, int64_t size_m,
+                            int64_t size_n, int64_t size_k, int64_t lda, int num_groups, int is_k_full, int dtype,
+                            void* stream, int silu) {
   using namespace b200;
   (void)workspace;
   // a fused all-reduce requested for "the next GEMM of this thread" (b200_ar_fuse_next_gemm) is consumed HERE, before any
@@ -231,6 +231,11 @@ extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_
   long long ar_m = 0, ar_n = 0;
   ArFuse ar_req;
   const bool ar_pending = ar_take_pending(&ar_req, &ar_m, &ar_n);
+  if (silu) {
+    B200_CHECK(!ar_pending, "gptq_marlin_gemm_silu_and_mul: gate_up is column-parallel, a fused all-reduce does not apply");
+    B200_CHECK(g_idx == nullptr && perm == nullptr, "gptq_marlin_gemm_silu_and_mul: act-order layers are not supported");
+    B200_CHECK(size_n % 128 == 0, "gptq_marlin_gemm_silu_and_mul: size_n / 2 = %lld must be a multiple of 64", (long long)(size_n / 2));
+  }
   B200_CHECK(num_bits == 4 || num_bits == 8, "num_bits must be 4 or 8. Got = %d", num_bits);
   B200_CHECK(dtype == B200_F16 || dtype == B200_BF16, "gpt_marlin_gemm only supports bfloat16 and float16");
   B200_CHECK(size_n % 64 == 0, "size_n = %lld, is not divisible by min_thread_n = 64", (long long)size_n);
@@ -289,6 +294,11 @@ extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_
   ga.prof = nullptr; ga.trace = nullptr; ga.trace_cta = 0; ga.exp = 0;
   ga.cluster_s = 0;
   ga.asum = nullptr; ga.asum_stride = 0;
+  ga.silu_inter = 0;
+  if (silu) {
+    ga.silu_inter = (int)(size_n / 2);
+    ga.n_tiles = (int)(size_n / 128);   // one tile = 64 gate + 64 up columns
+  }
   ga.ar.world = 0;
   if (ar_pending) {   // b200_ar_fuse_next_gemm: all-reduce this GEMM's output in its epilogue
     if (ar_m != size_m || ar_n != size_n)
@@ -300,7 +310,7 @@ extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_
   // B200_GEMM_DECODE=1: the experimental small-CTA decode kernels (marlin_decode_kernel.cuh; parity-green, but measured
   // slower than the kernel below on every Llama shape -- DESIGN.md section 6b has the numbers and the ncu evidence)
   static const int use_decode = getenv("B200_GEMM_DECODE") ? atoi(getenv("B200_GEMM_DECODE")) : 0;
-  if (size_m <= 64 && ga.ar.world <= 1 && use_decode && ga.n_tiles <= kDecMaxTiles) {
+  if (size_m <= 64 && ga.ar.world <= 1 && use_decode && !silu && ga.n_tiles <= kDecMaxTiles) {
     if (dtype == B200_F16) rc = (num_bits == 4) ? dispatch_decode_f16_4(ga, a, lda, st) : dispatch_decode_f16_8(ga, a, lda, st);
     else rc = (num_bits == 4) ? dispatch_decode_bf16_4(ga, a, lda, st) : dispatch_decode_bf16_8(ga, a, lda, st);
     if (rc) return rc;
@@ -312,4 +322,21 @@ extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_
   if (rc) return rc;
   B200_LAUNCH_CHECK("gptq_marlin_gemm");
   return B200_OK;
+}
+
+extern "C" int b200_gptq_marlin_gemm(void* c, const void* a, const int32_t* b_q_weight, const void* b_scales,
+                                     const int32_t* g_idx, const int32_t* perm, int32_t* workspace,
+                                     int64_t workspace_numel, int num_bits, int64_t size_m, int64_t size_n,
+                                     int64_t size_k, int64_t lda, int num_groups, int is_k_full, int dtype,
+                                     void* stream) {
+  return marlin_gemm_impl(c, a, b_q_weight, b_scales, g_idx, perm, workspace, workspace_numel, num_bits, size_m, size_n, size_k,
+                          lda, num_groups, is_k_full, dtype, stream, 0);
+}
+
+extern "C" int b200_gptq_marlin_gemm_silu_and_mul(void* out, const void* a, const int32_t* b_q_weight, const void* b_scales,
+                                                  int32_t* workspace, int64_t workspace_numel, int num_bits, int64_t size_m,
+                                                  int64_t size_n, int64_t size_k, int64_t lda, int num_groups, int dtype,
+                                                  void* stream) {
+  return marlin_gemm_impl(out, a, b_q_weight, b_scales, nullptr, nullptr, workspace, workspace_numel, num_bits, size_m, size_n,
+                          size_k, lda, num_groups, 1, dtype, stream, 1);
 }

@@ -91,7 +91,10 @@ struct GemmCfg {
   static constexpr int NW = NW_RAW > 12 ? 12 : NW_RAW;
   static constexpr int NBARS = 2 * NW + 2 * NA + 4 * NOWN + 2 * NOWN * NBUF + 2 * NSC;
   static constexpr int BAR_BYTES = NBARS * 8 + 16;
-  static constexpr int SMEM_BYTES = 1024 /*align slack*/ + NW * W_STAGE_BYTES + NA * AS_STAGE_BYTES + NSC * SCQ_STAGE_BYTES + BAR_BYTES;
+  // SiLU(gate) * up epilogue (args.silu_inter > 0): the 64 "up" channels of a tile hand their MPAD outputs to the 64 "gate"
+  // channels through this buffer, [MPAD][64] in the activation dtype
+  static constexpr int XCH_BYTES = MPAD * 64 * 2;
+  static constexpr int SMEM_BYTES = 1024 /*align slack*/ + NW * W_STAGE_BYTES + NA * AS_STAGE_BYTES + NSC * SCQ_STAGE_BYTES + BAR_BYTES + XCH_BYTES;
   static_assert(NW >= 2 && NA >= 2, "pipeline needs at least two stages per ring");
   static_assert(ACC_COL0 + NOWN * NBUF * MPAD <= 512, "TMEM budget");
   static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
@@ -116,6 +119,9 @@ struct GemmArgs {
   const float* asum;           // decode kernel v2: per-(group of 128 k, row) activation sums, fp32 [K/128][asum_stride]
   int asum_stride;
   uint32_t shmul[3];           // decode kernel v2: 2^28, 2^24, 2^20 -- right shifts done as IMAD.HI on the FMA pipe
+  int silu_inter;              // > 0: gate_up layer with SiLU(gate) * up fused into the epilogue.  N = 2 * silu_inter, tile t = gate
+                               // columns [64 t, 64 t + 64) (TMEM lanes 0..63) + up columns silu_inter + [64 t, 64 t + 64) (lanes
+                               // 64..127); C is [M, silu_inter]
   int exp;                     // bring-up ablations (B200_GEMM_EXP, prof builds only): 1 no dequant ALU, 2 no MMAs, 3 no epilogue reads, 4 no TMEM stores
 };
 
@@ -369,6 +375,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
   auto scfull_bar = [&](int s) { return bar_base + 8u * (NR + 4 * NOWN + 2 * NOWN * NBUF + s); };
   auto scempty_bar = [&](int s) { return bar_base + 8u * (NR + 4 * NOWN + 2 * NOWN * NBUF + NSC + s); };
   const uint32_t tmem_slot = bar_base + 8u * Cfg::NBARS;
+  const uint32_t xch_base = bar_base + Cfg::BAR_BYTES;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));  // generic pointer to the aligned base
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -422,6 +429,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
   const int u_end = u_base + part.start((clustered ? c_rank : (int)blockIdx.x) + 1);
   const int n_units = u_end - u_begin;
   const int gps = args.groups_per_stage;
+  const int silu = FUSE ? 0 : args.silu_inter;   // the all-reduce instantiation carries none of the SiLU code
 
   // everyone but the producers needs the TMEM base address: named barrier 2 after the allocator warp's tcgen05.alloc
   auto get_tmem_base = [&]() -> uint32_t {
@@ -452,10 +460,15 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         TRACE(9, it, 0);
         int nt, mc, ks;
         coords(it, nt, mc, ks);
+        // the tile's two 64-column halves are separate boxes ([half][slab][64 columns] in shared memory): adjacent
+        // columns normally, the gate / up pair (n, n + inter) when the SiLU epilogue is on
+        const int col0 = silu ? nt * 64 : nt * kTileN;
+        const int col1 = silu ? silu + nt * 64 : nt * kTileN + 64;
         if (elect_one()) {
           mbar_arrive_expect_tx(wfull_bar(s), Cfg::W_STAGE_BYTES);
-          tma_2d_g2s_hint(w_base + s * Cfg::W_STAGE_BYTES, &tmap_w, nt * (Cfg::W_ROW_BYTES / 8), ks * (kStageK / 16),
-                          wfull_bar(s), pol_w);
+          tma_2d_g2s_hint(w_base + s * Cfg::W_STAGE_BYTES, &tmap_w, col0 * (BITS / 4), ks * (kStageK / 16), wfull_bar(s), pol_w);
+          tma_2d_g2s_hint(w_base + s * Cfg::W_STAGE_BYTES + Cfg::W_STAGE_BYTES / 2, &tmap_w, col1 * (BITS / 4),
+                          ks * (kStageK / 16), wfull_bar(s), pol_w);
         }
         __syncwarp();
         if (GM == kGroup128) {
@@ -464,7 +477,8 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
           if (it >= NSC) mbar_wait(scempty_bar(q), ((it / NSC) & 1) ^ 1);
           if (elect_one()) {
             mbar_arrive_expect_tx(scfull_bar(q), Cfg::SCQ_STAGE_BYTES);
-            tma_2d_g2s_hint(scq_base + q * Cfg::SCQ_STAGE_BYTES, &tmap_s, nt * kTileN, ks * 2, scfull_bar(q), pol_s);
+            tma_2d_g2s_hint(scq_base + q * Cfg::SCQ_STAGE_BYTES, &tmap_s, col0, ks * 2, scfull_bar(q), pol_s);
+            tma_2d_g2s_hint(scq_base + q * Cfg::SCQ_STAGE_BYTES + Cfg::SCQ_STAGE_BYTES / 2, &tmap_s, col1, ks * 2, scfull_bar(q), pol_s);
           }
           __syncwarp();
         }
@@ -482,8 +496,11 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         if (elect_one()) {
           mbar_arrive_expect_tx(actfull_bar(s), tx);
           tma_3d_g2s_hint(act_base + s * Cfg::A_STAGE_BYTES, &tmap_a, 0, mc * MPAD, ks * (kStageK / 64), actfull_bar(s), pol_a);
-          if (GM == kGroupSmall)
-            tma_2d_g2s_hint(sc_base + s * Cfg::S_STAGE_BYTES, &tmap_s, nt * kTileN, ks * gps, actfull_bar(s), pol_a);
+          if (GM == kGroupSmall) {
+            tma_2d_g2s_hint(sc_base + s * Cfg::S_STAGE_BYTES, &tmap_s, silu ? nt * 64 : nt * kTileN, ks * gps, actfull_bar(s), pol_a);
+            tma_2d_g2s_hint(sc_base + s * Cfg::S_STAGE_BYTES + gps * 128, &tmap_s, silu ? silu + nt * 64 : nt * kTileN + 64,
+                            ks * gps, actfull_bar(s), pol_a);
+          }
         }
         __syncwarp();
       }
@@ -564,9 +581,11 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     const int gph = gps >> 1;                      // scale rows per half stage (kGroupSmall: 2 or 4)
     const int lspg = gph == 4 ? 1 : 2;             // log2(slabs per group) for kGroupSmall
     const uint32_t a_col = tmem_base + ((uint32_t)(32 * qd) << 16) + 64 * o;
-    const uint8_t* wsm = smem_gen + (w_base - smem_base) + h * Cfg::W_HALF_BYTES + t64 * (Cfg::W_ROW_BYTES / 2) +
+    // weight stage in shared memory: [64-column half t64][16 slabs][32 lanes x 16 B (4-bit) / 32 B (8-bit)]
+    const uint8_t* wsm = smem_gen + (w_base - smem_base) + t64 * (Cfg::W_STAGE_BYTES / 2) + h * (Cfg::W_HALF_BYTES / 2) +
                          lane * (4 * BITS) + jpair * (2 * BITS);
-    const uint8_t* ssm = smem_gen + (sc_base - smem_base) + h * gph * 256 + (64 * t64 + 8 * c + 4 * jpair) * 2;
+    // small-group scale rows: [half t64][gps rows][64 columns]
+    const uint8_t* ssm = smem_gen + (sc_base - smem_base) + t64 * gps * 128 + h * gph * 128 + (8 * c + 4 * jpair) * 2;
     long long p_mark = PROF_ON(args.prof) ? clock64() : 0, p_wfull = 0, p_lds = 0, p_waempty = 0, p_deq = 0, p_st = 0;
     int jc = 0;
     for (int hu = o; hu < 2 * n_units; hu += NOWN, ++jc) {
@@ -580,10 +599,10 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
 #pragma unroll
       for (int r = 0; r < kSlabs; ++r) {
         if (BITS == 4) {
-          const uint2 v = *reinterpret_cast<const uint2*>(wsm + s * Cfg::W_STAGE_BYTES + r * Cfg::W_ROW_BYTES);
+          const uint2 v = *reinterpret_cast<const uint2*>(wsm + s * Cfg::W_STAGE_BYTES + r * (Cfg::W_ROW_BYTES / 2));
           w[r][0] = v.x; w[r][1] = v.y;
         } else {
-          const uint4 v = *reinterpret_cast<const uint4*>(wsm + s * Cfg::W_STAGE_BYTES + r * Cfg::W_ROW_BYTES);
+          const uint4 v = *reinterpret_cast<const uint4*>(wsm + s * Cfg::W_STAGE_BYTES + r * (Cfg::W_ROW_BYTES / 2));
           w[r][0] = v.x; w[r][1] = v.y; w[r][2] = v.z; w[r][3] = v.w;
         }
       }
@@ -592,7 +611,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       // 64-chunk holds column c + 8 b'; this thread needs b' = 4 jpair .. 4 jpair + 3 -> one 8-byte read
       uint32_t s2[4] = {0, 0, 0, 0};  // broadcast scales for (jj, b): index 2 jj + b
       auto load_scales = [&](int row) {
-        const uint2 raw = *reinterpret_cast<const uint2*>(ssm + sa * Cfg::S_STAGE_BYTES + row * 256);
+        const uint2 raw = *reinterpret_cast<const uint2*>(ssm + sa * Cfg::S_STAGE_BYTES + row * 128);
         s2[0] = bcast16(raw.x);
         s2[1] = bcast16_hi(raw.x);
         s2[2] = bcast16(raw.y);
@@ -689,7 +708,8 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     const int jb = (et >> 7) * ACCW;                   // columns jb .. jb + ACCW - 1 (two warpgroups split them at MPAD >= 64)
     constexpr int CH = ACCW < 32 ? ACCW : 32;          // accumulator columns per TMEM read batch
     // position of this channel's scale in a 128-column slice of a scale row (scale_perm, 64-chunks: pos 8 c + b' <-> col c + 8 b')
-    const int sc_pos = 64 * (row >> 6) + 8 * (row & 7) + ((row & 63) >> 3);
+    // (the ring slot holds [64-column half][2 rows][64 positions])
+    const int sc_pos = 128 * (row >> 6) + 8 * (row & 7) + ((row & 63) >> 3);
     const uint32_t acc_lane = tmem_base + ((uint32_t)(32 * qd) << 16) + Cfg::ACC_COL0;
     pdl_wait();   // C, the partial slots and the tile counters may still be in use by the previous kernel
     constexpr bool fuse = FUSE;   // separate instantiation: the plain kernel carries none of the exchange code
@@ -706,6 +726,29 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     auto ar_owner = [&](int n) { return args.ar.two_shot ? (n >> 5) % args.ar.world : -1; };
     // stores this thread's ACCW final outputs (or, fused, exchanges them with the peers first): rows jb .. jb + ACCW - 1
     auto store_rows = [&](float (&acc)[ACCW], float ch_scale, T* cdst, int n, bool n_ok, int m_valid) {
+      if (silu) {
+        // gate_up layer: round both halves to T (what the unfused GEMM would have stored), hand the up values to the gate
+        // threads through shared memory, then silu_and_mul with the reference's roundings (activation_kernels.cu:14-40:
+        // T(x / (1 + e^-x)) * y).  Every epilogue thread of the CTA gets here together (CTA-uniform branch).
+        T* xch = reinterpret_cast<T*>(smem_gen + (xch_base - smem_base));
+        if (row >= 64) {
+#pragma unroll
+          for (int j = 0; j < ACCW; ++j) xch[(jb + j) * 64 + (row - 64)] = from_f32<T>(acc[j] * ch_scale);
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(Cfg::NEPI * 32) : "memory");
+        if (row < 64) {
+#pragma unroll
+          for (int j = 0; j < ACCW; ++j) {
+            if (jb + j < m_valid) {
+              const float x = to_f32<T>(from_f32<T>(acc[j] * ch_scale));
+              const float y = to_f32<T>(xch[(jb + j) * 64 + row]);
+              cdst[(size_t)(jb + j) * silu] = from_f32<T>(to_f32<T>(from_f32<T>(x / (1.0f + expf(-x)))) * y);
+            }
+          }
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(Cfg::NEPI * 32) : "memory");
+        return;
+      }
       if (!n_ok) return;
       if constexpr (FUSE) {
 #pragma unroll
@@ -733,13 +776,14 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
       const int len = min(KS - ks0, u_end - u);
       const int it0 = u - u_begin, it1 = it0 + len;
       const int nt = tile % args.n_tiles, mc = tile / args.n_tiles;
-      const int n = nt * kTileN + row;
+      const int n = silu ? (row < 64 ? nt * 64 + row : silu + nt * 64 + (row - 64)) : nt * kTileN + row;
       const int m0 = mc * MPAD;
       const int m_valid = min(MPAD, args.M - m0);
       const bool n_ok = n < args.N;
       const bool full_k = (ks0 == 0 && len == KS);
       const bool owner = (ks0 == 0 && !full_k && !clustered);   // this CTA reduces the tile; the others only contribute
-      T* cdst = reinterpret_cast<T*>(args.C) + (size_t)m0 * args.N + n;
+      T* cdst = silu ? reinterpret_cast<T*>(args.C) + (size_t)m0 * silu + nt * 64 + (row & 63)
+                     : reinterpret_cast<T*>(args.C) + (size_t)m0 * args.N + n;
       float acc[ACCW];
 #pragma unroll
       for (int j = 0; j < ACCW; ++j) acc[j] = 0.f;
@@ -752,7 +796,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
           mbar_wait(scfull_bar(q), (it / NSC) & 1);
           const uint8_t* sp = smem_gen + (scq_base - smem_base) + q * Cfg::SCQ_STAGE_BYTES + 2 * sc_pos;
           sc_h[0] = to_f32<T>(*reinterpret_cast<const T*>(sp));
-          sc_h[1] = to_f32<T>(*reinterpret_cast<const T*>(sp + 256));
+          sc_h[1] = to_f32<T>(*reinterpret_cast<const T*>(sp + 128));
           __syncwarp();
           if (lane == 0) mbar_arrive(scempty_bar(q));
         }
@@ -936,7 +980,7 @@ int launch_gemm(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t s
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
     attr_set[dev & 63] = true;
   }
-  if (!no_cluster && a.m_chunks == 1 && tiles * 2 <= num_sms()) {
+  if (!no_cluster && a.silu_inter == 0 && a.m_chunks == 1 && tiles * 2 <= num_sms()) {
     // largest cluster size whose clusters are all co-resident (GPC boundaries limit this: 45 clusters of 3 on B200)
     static int max_active[64][9] = {};
     int cs = num_sms() / tiles;
@@ -976,14 +1020,14 @@ int launch_gemm(const GemmArgs& a_in, const void* A, int64_t lda, cudaStream_t s
   // activations [M, K] (row pitch lda) as {64, M, K/64}: one box = 4 chunks of 64 (k) x MPAD rows, 128-byte swizzle,
   // rows beyond M and chunks beyond K read as zero
   bool ok = make_tmap_act3d(&tmap_a, A, dt, (uint64_t)a.M, (uint64_t)a.K, (uint64_t)lda * 2, MPAD, kStageK / 64);
-  // packed weights [K/16, N*16*BITS/8 bytes] viewed as 8-byte elements: box = 16 slabs x one 128-column tile
+  // packed weights [K/16, N*16*BITS/8 bytes] viewed as 8-byte elements: box = 16 slabs x one 64-column half tile
   const uint64_t wrow_bytes = (uint64_t)a.N * 16 * BITS / 8;
   ok = ok && make_tmap_2d(&tmap_w, a.B, CU_TENSOR_MAP_DATA_TYPE_UINT64, 8, (uint64_t)a.K / 16, wrow_bytes / 8, wrow_bytes,
-                          kStageK / 16, Cfg::W_ROW_BYTES / 8, CU_TENSOR_MAP_SWIZZLE_NONE);
-  // group scales [num_groups, N]: box = (scale rows of one stage) x 128 columns
+                          kStageK / 16, Cfg::W_ROW_BYTES / 16, CU_TENSOR_MAP_SWIZZLE_NONE);
+  // group scales [num_groups, N]: box = (scale rows of one stage) x 64 columns
   if (GM != kChannelwise)
     ok = ok && make_tmap_2d(&tmap_s, a.scales, dt, 2, (uint64_t)a.num_groups, (uint64_t)a.N, (uint64_t)a.N * 2,
-                            (uint32_t)a.groups_per_stage, kTileN, CU_TENSOR_MAP_SWIZZLE_NONE);
+                            (uint32_t)a.groups_per_stage, kTileN / 2, CU_TENSOR_MAP_SWIZZLE_NONE);
   else
     tmap_s = tmap_a;
   if (!ok)

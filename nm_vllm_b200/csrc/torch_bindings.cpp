@@ -321,6 +321,42 @@ torch::Tensor gptq_marlin_repack(torch::Tensor& b_q_weight, torch::Tensor& perm,
   return out;
 }
 
+// ---------------------------------------------------------------- prefill attention over the paged cache
+// context_attention_fwd (vllm/attention/ops/prefix_prefill.py:674-799, Triton in the reference): same argument order
+void context_attention_fwd(torch::Tensor& q, torch::Tensor& k, torch::Tensor& v, torch::Tensor& o, torch::Tensor& k_cache,
+                           torch::Tensor& v_cache, torch::Tensor& b_loc, torch::Tensor& b_start_loc,
+                           torch::Tensor& b_seq_len, torch::Tensor& b_ctx_len, int64_t max_input_len,
+                           const c10::optional<torch::Tensor>& alibi_slopes, int64_t sliding_window) {
+  TORCH_CHECK(q.dim() == 3 && k.dim() == 3 && v.dim() == 3 && o.dim() == 3, "q / k / v / o must be [tokens, heads, head_size]");
+  TORCH_CHECK(q.size(2) == k.size(2) && k.size(2) == v.size(2), "head sizes of q, k, v differ");   // prefix_prefill.py:691-692
+  TORCH_CHECK(k_cache.dim() == 5 && v_cache.dim() == 4, "k_cache must be 5-D [NB, Hkv, D/x, BS, x], v_cache 4-D [NB, Hkv, D, BS]");
+  TORCH_CHECK(q.stride(2) == 1 && k.stride(2) == 1 && v.stride(2) == 1 && o.stride(2) == 1, "head dimension must be contiguous");
+  TORCH_CHECK(k_cache.scalar_type() == q.scalar_type() && v_cache.scalar_type() == q.scalar_type(),
+              "context_attention_fwd: the cache must hold the query dtype");
+  TORCH_CHECK(k_cache.stride(4) == 1 && k_cache.stride(3) == k_cache.size(4) && k_cache.stride(2) == k_cache.size(3) * k_cache.size(4) &&
+              v_cache.stride(3) == 1 && v_cache.stride(2) == v_cache.size(3), "cache blocks must be contiguous per kv head");
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(q));
+  auto i32 = [&](torch::Tensor& t) { return t.scalar_type() == at::ScalarType::Int ? t : t.to(at::ScalarType::Int); };
+  torch::Tensor bt = i32(b_loc), st = i32(b_start_loc).contiguous(), sl = i32(b_seq_len).contiguous(), cl = i32(b_ctx_len).contiguous();
+  TORCH_CHECK(bt.dim() == 2 && bt.stride(1) == 1, "b_loc must be [batch, max_blocks] with contiguous rows");
+  const int batch = (int)sl.size(0);
+  TORCH_CHECK(st.size(0) >= batch && cl.size(0) == batch && bt.size(0) >= batch, "b_start_loc / b_ctx_len / b_loc do not match b_seq_len");
+  const int64_t strides[8] = {q.stride(0), q.stride(1), k.stride(0), k.stride(1), v.stride(0), v.stride(1), o.stride(0), o.stride(1)};
+  const float* alibi = nullptr;
+  if (alibi_slopes.has_value()) {
+    TORCH_CHECK(alibi_slopes->scalar_type() == at::ScalarType::Float && alibi_slopes->is_contiguous() && alibi_slopes->numel() == q.size(1),
+                "alibi_slopes must be float32 [num_heads]");
+    alibi = alibi_slopes->data_ptr<float>();
+  }
+  raise_if(b200_context_attention_fwd(o.data_ptr(), q.data_ptr(), k.data_ptr(), v.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
+                                      bt.data_ptr<int>(), bt.stride(0), st.data_ptr<int>(), sl.data_ptr<int>(), cl.data_ptr<int>(), batch,
+                                      (int)max_input_len, (int)q.size(1), (int)k.size(1), (int)q.size(2), (int)v_cache.size(3),
+                                      (int)k_cache.size(4), strides, k_cache.stride(0), k_cache.stride(1), v_cache.stride(0),
+                                      v_cache.stride(1), alibi, (int)sliding_window,
+                                      dtype_enum(q.scalar_type(), "context_attention_fwd"), cur_stream(q)),
+           "context_attention_fwd");
+}
+
 // ---------------------------------------------------------------- Marlin GEMMs
 // gptq_marlin.cu:1735-1868
 torch::Tensor gptq_marlin_gemm(torch::Tensor& a, torch::Tensor& b_q_weight, torch::Tensor& b_scales,
@@ -370,6 +406,37 @@ torch::Tensor gptq_marlin_gemm(torch::Tensor& a, torch::Tensor& b_q_weight, torc
                                  dtype_enum(a.scalar_type(), "gptq_marlin_gemm"), cur_stream(a)),
            "gptq_marlin_gemm");
   return c;
+}
+
+// gate_up_proj GEMM with SiluAndMul in its epilogue (no counterpart op in the reference: it launches gptq_marlin_gemm and
+// silu_and_mul, llama.py:74-90); same argument checks as gptq_marlin_gemm, output [size_m, size_n / 2]
+torch::Tensor gptq_marlin_gemm_silu_and_mul(torch::Tensor& a, torch::Tensor& b_q_weight, torch::Tensor& b_scales,
+                                            torch::Tensor& workspace, int64_t num_bits, int64_t size_m, int64_t size_n,
+                                            int64_t size_k) {
+  TORCH_CHECK(num_bits == 4 || num_bits == 8, "num_bits must be 4 or 8. Got = ", num_bits);
+  const int pack_factor = 32 / (int)num_bits;
+  TORCH_CHECK(a.dim() == 2 && a.size(0) == size_m && a.size(1) == size_k, "Shape mismatch: a is not [size_m, size_k]");
+  TORCH_CHECK(size_k % 16 == 0 && (size_k / 16) == b_q_weight.size(0), "Shape mismatch: b_q_weight.size(0) = ",
+              b_q_weight.size(0), ", size_k = ", size_k);
+  TORCH_CHECK(b_q_weight.size(1) % 16 == 0 && size_n == (b_q_weight.size(1) / 16) * pack_factor, "size_n = ", size_n,
+              " does not match b_q_weight");
+  TORCH_CHECK(a.device().is_cuda() && a.stride(1) == 1, "A is not on GPU / not row-major");
+  TORCH_CHECK(b_q_weight.device().is_cuda() && b_q_weight.is_contiguous(), "b_q_weight is not on GPU / not contiguous");
+  TORCH_CHECK(b_scales.device().is_cuda() && b_scales.is_contiguous(), "b_scales is not on GPU / not contiguous");
+  TORCH_CHECK(b_scales.dim() == 2 && b_scales.size(1) == size_n, "b_scales dim 1 = ", b_scales.size(1), " is not size_n = ", size_n);
+  TORCH_CHECK(b_scales.scalar_type() == a.scalar_type(), "b_scales must have the dtype of a");
+  TORCH_CHECK(size_n % 128 == 0, "size_n / 2 = ", size_n / 2, " is not divisible by 64");
+  TORCH_CHECK(workspace.numel() >= (size_n / 64) * 16, "workspace.numel = ", workspace.numel(), " is below min_workspace_size");
+  TORCH_CHECK(a.scalar_type() == at::ScalarType::Half || a.scalar_type() == at::ScalarType::BFloat16,
+              "gptq_marlin_gemm_silu_and_mul only supports bfloat16 and float16");
+  const at::cuda::OptionalCUDAGuard device_guard(device_of(a));
+  torch::Tensor out = torch::empty({size_m, size_n / 2}, a.options());
+  raise_if(b200_gptq_marlin_gemm_silu_and_mul(out.data_ptr(), a.data_ptr(), b_q_weight.data_ptr<int>(), b_scales.data_ptr(),
+                                              workspace.data_ptr<int>(), workspace.numel(), (int)num_bits, size_m, size_n,
+                                              size_k, a.stride(0), (int)b_scales.size(0),
+                                              dtype_enum(a.scalar_type(), "gptq_marlin_gemm_silu_and_mul"), cur_stream(a)),
+           "gptq_marlin_gemm_silu_and_mul");
+  return out;
 }
 
 // marlin/dense/marlin_cuda_kernel.cu:1044-1136 (W4A16, fp16, groups -1/128): same layout family, same kernel.
@@ -610,6 +677,13 @@ TORCH_LIBRARY(_b200_C, ops) {
   ops.impl("gptq_marlin_24_gemm", torch::kCUDA, &gptq_marlin_24_gemm);
   ops.def("gptq_marlin_gemm", &gptq_marlin_gemm);
   ops.impl("gptq_marlin_gemm", torch::kCUDA, &gptq_marlin_gemm);
+  ops.def(
+      "context_attention_fwd(Tensor q, Tensor k, Tensor v, Tensor! o, Tensor k_cache, Tensor v_cache, Tensor b_loc,"
+      "    Tensor b_start_loc, Tensor b_seq_len, Tensor b_ctx_len, int max_input_len, Tensor? alibi_slopes,"
+      "    int sliding_window) -> ()");
+  ops.impl("context_attention_fwd", torch::kCUDA, &context_attention_fwd);
+  ops.def("gptq_marlin_gemm_silu_and_mul", &gptq_marlin_gemm_silu_and_mul);
+  ops.impl("gptq_marlin_gemm_silu_and_mul", torch::kCUDA, &gptq_marlin_gemm_silu_and_mul);
   ops.def("gptq_marlin_repack", &gptq_marlin_repack);
   ops.impl("gptq_marlin_repack", torch::kCUDA, &gptq_marlin_repack);
 

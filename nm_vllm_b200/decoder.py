@@ -11,6 +11,7 @@ column-parallel qkv / gate_up shard N, row-parallel o / down shard K and are fol
 `DecodeEngine` is the public entry the end-to-end number is measured through: host (pinned) step inputs in, sampled
 token ids out, with the whole device step captured in one CUDA graph (model_runner.py:910-1118 does the same).
 """
+import os
 from dataclasses import dataclass
 from typing import Optional
 
@@ -125,6 +126,15 @@ class QuantLinear:
             return ops.cutlass_scaled_mm(xq, self.weight, xs, self.weight_scale, self.dtype)
         return torch.matmul(x, self.weight.t())
 
+    def silu_and_mul(self, x):
+        """gate_up layers: SiluAndMul(self(x)); one launch for the W4A16 kind (GEMM epilogue), two otherwise."""
+        if self.kind == "w4a16" and self.method.can_fuse_silu_and_mul(self.layer):
+            return self.method.apply_silu_and_mul(self.layer, x)
+        gu = self(x)
+        act = torch.empty((gu.shape[0], gu.shape[1] // 2), dtype=gu.dtype, device=gu.device)
+        ops.silu_and_mul(act, gu)
+        return act
+
     # ---- W8A8 with the activation quantiser fused into the producing kernel (fp8_static / int8) ----------------------
     @property
     def fused_quant_kind(self):
@@ -149,6 +159,7 @@ class SyntheticLlama:
         self.fuse_gemm_all_reduce = True  # row-parallel W4A16 GEMMs all-reduce in their epilogue when custom_ar is on
         self.fuse_act_quant = True  # W8A8 with static fp8 / per-token int8 activations: quantiser fused into norm / silu kernels
         self.fuse_attention = True  # rope + cache write + paged attention in one launch when the shape is on the fast path
+        self.fuse_silu = os.environ.get("B200_NO_FUSE_SILU", "0") != "1"   # SiluAndMul in the epilogue of the W4A16 gate_up GEMM
         s = shape
         self.nlayers = layers if layers is not None else s.layers
         assert s.heads % tp_size == 0
@@ -294,9 +305,12 @@ class SyntheticLlama:
                 h = self._all_reduce(L["down"].mm_quantized(aq, asc))
                 continue
             ops.fused_add_rms_norm(h, residual, L["ln2"], s.eps)
-            gu = L["gate_up"](h)
-            act = torch.empty((gu.shape[0], gu.shape[1] // 2), dtype=gu.dtype, device=gu.device)
-            ops.silu_and_mul(act, gu)
+            if self.fuse_silu:
+                act = L["gate_up"].silu_and_mul(h)
+            else:
+                gu = L["gate_up"](h)
+                act = torch.empty((gu.shape[0], gu.shape[1] // 2), dtype=gu.dtype, device=gu.device)
+                ops.silu_and_mul(act, gu)
             h = self._row_parallel(L["down"], act)
         ops.fused_add_rms_norm(h, residual, self.norm, s.eps)
         logits = self.lm_head(h)

@@ -168,3 +168,44 @@ def rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox):
         return th.reshape(t.shape)
 
     return rope(query), rope(key)
+
+
+# ---- prefill attention over the paged cache ---------------------------------------------------------------------------
+def context_attention_ref(q, k, v, k_cache, v_cache, b_loc, b_start_loc, b_seq_len, b_ctx_len, alibi_slopes=None,
+                          sliding_window=0):
+    """ORACLE of `context_attention_fwd` (vllm/attention/ops/prefix_prefill.py:674-799).  The reference kernel is Triton (it
+    cannot run here), so this restates what ITS OWN test checks it against (tests/kernels/test_prefix_prefill.py:157-196):
+    plain softmax attention with xformers' BlockDiagonalCausalFromBottomRightMask (+ make_local_attention_from_bottomright
+    for the sliding window) over the concatenation [cached context (gathered through the block table), new tokens], GQA by
+    repeating kv heads, scale 1/sqrt(head_size); ALiBi as in the kernel (:551-557): slope * (key_pos - query_pos).
+    Parity for this row is pinned by that definition, not by stored vectors.  q [T, H, D]; k, v [T, Hkv, D]; caches in the
+    vLLM layouts; returns [T, H, D] in q's dtype (fp32 softmax, probabilities rounded to the value dtype before P.V)."""
+    T, H, D = q.shape
+    Hkv = k.shape[1]
+    G = H // Hkv
+    BS = v_cache.shape[3]
+    out = torch.zeros_like(q)
+    scale = 1.0 / (D ** 0.5)
+    for b in range(len(b_seq_len)):
+        ctx, L = int(b_ctx_len[b]), int(b_seq_len[b])
+        ql, st = L - ctx, int(b_start_loc[b])
+        if ql <= 0:
+            continue
+        nb = (ctx + BS - 1) // BS
+        blocks = b_loc[b, :nb].long()
+        kc = k_cache[blocks].permute(0, 3, 1, 2, 4).reshape(nb * BS, Hkv, D)[:ctx]
+        vc = v_cache[blocks].permute(0, 3, 1, 2).reshape(nb * BS, Hkv, D)[:ctx]
+        kk = torch.cat([kc, k[st:st + ql]], 0).float().repeat_interleave(G, dim=1)      # [L, H, D]
+        vv = torch.cat([vc, v[st:st + ql]], 0).repeat_interleave(G, dim=1)
+        w = scale * torch.einsum("qhd,khd->hqk", q[st:st + ql].float(), kk)              # [H, ql, L]
+        qpos = ctx + torch.arange(ql).view(-1, 1)
+        kpos = torch.arange(L).view(1, -1)
+        if alibi_slopes is not None:
+            w = w + alibi_slopes.float().view(-1, 1, 1) * (kpos - qpos).float()
+        mask = kpos <= qpos
+        if sliding_window and sliding_window > 0:
+            mask = mask & (qpos - kpos < sliding_window)
+        w = w.masked_fill(~mask, float("-inf"))
+        p = torch.softmax(w, dim=-1).to(q.dtype)
+        out[st:st + ql] = torch.einsum("hqk,khd->qhd", p.float(), vv.float()).to(q.dtype)
+    return out

@@ -111,3 +111,36 @@ def test_fp8_codec_corner_cases():
     x = torch.linspace(-2, 2, 101)
     r = ops_ref.fp8_dequant(ops_ref.fp8_quant(x, 0.05, "fp8"), 0.05, torch.float32, "fp8")
     assert torch.allclose(r, x, atol=1e-3, rtol=0.1)
+
+
+def test_context_attention_oracle_agrees_with_the_paged_attention_oracle():
+    """Two independent restatements meet: prefill over (cached context + new tokens) == one paged-attention row per query
+    token once the new tokens' K / V sit in the cache (the paged-attention oracle is pinned to the reference's CPU op)."""
+    import torch
+    from oracle import ops_ref
+    H, Hkv, D, BS, NB = 4, 2, 32, 16, 24
+    ctx, ql = [20, 0, 33], [5, 17, 1]
+    g = torch.Generator().manual_seed(4)
+    T = sum(ql)
+    q = torch.randn((T, H, D), generator=g).to(torch.bfloat16)
+    k = torch.randn((T, Hkv, D), generator=g).to(torch.bfloat16)
+    v = torch.randn((T, Hkv, D), generator=g).to(torch.bfloat16)
+    kc = torch.randn((NB, Hkv, D // 8, BS, 8), generator=g).to(torch.bfloat16)
+    vc = torch.randn((NB, Hkv, D, BS), generator=g).to(torch.bfloat16)
+    maxb = 4
+    bt = torch.randperm(NB, generator=g)[:3 * maxb].view(3, maxb).to(torch.int32)
+    start = torch.tensor([0, 5, 22], dtype=torch.int32)
+    seq = torch.tensor([c + n for c, n in zip(ctx, ql)], dtype=torch.int32)
+    out = ops_ref.context_attention_ref(q, k, v, kc, vc, bt, start, seq, torch.tensor(ctx, dtype=torch.int32))
+    # write the new tokens into a copy of the cache, then decode-style rows
+    kc2, vc2 = kc.clone(), vc.clone()
+    slots = []
+    for b in range(3):
+        for i in range(ql[b]):
+            p = ctx[b] + i
+            slots.append(int(bt[b, p // BS]) * BS + p % BS)
+    ops_ref.reshape_and_cache(k, v, kc2, vc2, torch.tensor(slots, dtype=torch.int64))
+    rows_bt = torch.stack([bt[b] for b in range(3) for _ in range(ql[b])])
+    rows_len = torch.tensor([ctx[b] + i + 1 for b in range(3) for i in range(ql[b])], dtype=torch.int32)
+    ref = ops_ref.paged_attention(q, kc2, vc2, rows_bt, rows_len, D ** -0.5)
+    torch.testing.assert_close(out.float(), ref.float(), atol=2e-2, rtol=2e-2)
