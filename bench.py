@@ -343,7 +343,7 @@ def run_b200(a):
     num_blocks = max(a.batch * nb_seq * 2, 1024)
     model = decoder.SyntheticLlama(shape, quant=a.quant, dtype=dtype, device=dev, tp_size=world, tp_rank=rank,
                                    kv_cache_dtype=a.kv, kv_scale=1.0 if a.kv == "auto" else 0.0376,
-                                   num_blocks=num_blocks, max_pos=max(a.ctx + 1, 512), layers=a.layers)
+                                   num_blocks=num_blocks, max_pos=max(a.ctx + 1, 2048 + 16), layers=a.layers)
     ar_kind = "none"
     model.fuse_gemm_all_reduce = not a.no_fuse
     if world > 1:
@@ -485,6 +485,28 @@ def run_b200(a):
             for b in (1, 16):
                 if b != a.batch:
                     out["roofline"]["by_batch"][str(b)] = gemm_roofline(model, b, peaks, brief=True)
+    if not a.no_sweep and world == 1 and a.layers is None:
+        # BASELINE.json configs[2] names "decode + 2k prefill": one 2048-token prompt through the same model (M = 2048 GEMMs,
+        # rotary, reshape_and_cache, prefill attention over the paged cache, last-token logits), device-timed, median of 5
+        try:
+            T = 2048
+            toks = torch.randint(0, shape.vocab, (T,), device=dev)
+            bt = torch.randperm(model.num_blocks)[:T // model.block_size].to(torch.int32).view(1, -1)
+            pos, pmeta = model.prefill_meta([T], [0], bt)
+            model.forward(toks, pos, pmeta)
+            torch.cuda.synchronize()
+            ts = []
+            for _ in range(5):
+                e0.record()
+                model.forward(toks, pos, pmeta)
+                e1.record()
+                torch.cuda.synchronize()
+                ts.append(e0.elapsed_time(e1))
+            ts.sort()
+            out["prefill_2k"] = {"tokens": T, "ms": ts[2], "tok_s": T / ts[2] * 1e3,
+                                 "what": "1 x 2048-token prompt, eager launches, kv auto; not part of `value`"}
+        except Exception as e:   # never lose the headline line to the extra
+            out["prefill_2k"] = {"error": repr(e)[:200]}
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
         from oracle import cpu_decode
         r = cpu_decode.time_decode(shape, a.batch, a.ctx, layer_reps=3, threads=os.cpu_count())

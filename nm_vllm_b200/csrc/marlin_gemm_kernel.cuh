@@ -727,23 +727,31 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     // stores this thread's ACCW final outputs (or, fused, exchanges them with the peers first): rows jb .. jb + ACCW - 1
     auto store_rows = [&](float (&acc)[ACCW], float ch_scale, T* cdst, int n, bool n_ok, int m_valid) {
       if (silu) {
-        // gate_up layer: round both halves to T (what the unfused GEMM would have stored), hand the up values to the gate
-        // threads through shared memory, then silu_and_mul with the reference's roundings (activation_kernels.cu:14-40:
-        // T(x / (1 + e^-x)) * y).  Every epilogue thread of the CTA gets here together (CTA-uniform branch).
+        // gate_up layer: round gate and up to T (what the unfused GEMM would have stored), pair them through shared memory,
+        // then silu_and_mul with the reference's roundings (activation_kernels.cu:14-40: T(x / (1 + e^-x)) * y).  Every
+        // epilogue thread of the CTA gets here together (CTA-uniform branch).
         T* xch = reinterpret_cast<T*>(smem_gen + (xch_base - smem_base));
-        if (row >= 64) {
+        // the activation math is split evenly: the gate thread of a channel finishes the first half of its columns, the up
+        // thread the second half; each hands the partner the half it does NOT finish ([column][64 channels] in xch).  (Only
+        // the gate threads doing all of it stalled the accumulator hand-off for ~3 us per tile at M = 64.)
+        constexpr int HW = ACCW / 2;
+        const bool is_up = row >= 64;
+        const int r64 = row & 63;
+        const int j_send = is_up ? 0 : HW, j_keep = is_up ? HW : 0;
 #pragma unroll
-          for (int j = 0; j < ACCW; ++j) xch[(jb + j) * 64 + (row - 64)] = from_f32<T>(acc[j] * ch_scale);
+        for (int j = 0; j < HW; ++j) {
+          const float send = is_up ? acc[j] : acc[HW + j];
+          xch[(jb + j_send + j) * 64 + r64] = from_f32<T>(send * ch_scale);
         }
         asm volatile("bar.sync 1, %0;" ::"n"(Cfg::NEPI * 32) : "memory");
-        if (row < 64) {
 #pragma unroll
-          for (int j = 0; j < ACCW; ++j) {
-            if (jb + j < m_valid) {
-              const float x = to_f32<T>(from_f32<T>(acc[j] * ch_scale));
-              const float y = to_f32<T>(xch[(jb + j) * 64 + row]);
-              cdst[(size_t)(jb + j) * silu] = from_f32<T>(to_f32<T>(from_f32<T>(x / (1.0f + expf(-x)))) * y);
-            }
+        for (int j = 0; j < HW; ++j) {
+          const int col = jb + j_keep + j;
+          if (col < m_valid) {
+            const float own = to_f32<T>(from_f32<T>((is_up ? acc[HW + j] : acc[j]) * ch_scale));
+            const float other = to_f32<T>(xch[col * 64 + r64]);
+            const float x = is_up ? other : own, y = is_up ? own : other;
+            cdst[(size_t)col * silu] = from_f32<T>(to_f32<T>(from_f32<T>(x / (1.0f + expf(-x)))) * y);
           }
         }
         asm volatile("bar.sync 1, %0;" ::"n"(Cfg::NEPI * 32) : "memory");

@@ -53,6 +53,8 @@ class QuantLinear:
        fp8/int8  cutlass_scaled_mm with per-tensor weight scale + dynamic activation quant fp8.py:240-379
        bf16      unquantized (lm_head default: gptq_marlin.py:154-157)"""
 
+    fuse_silu_max_m = int(os.environ.get("B200_FUSE_SILU_MAX_M", "64"))
+
     def __init__(self, kind, K, N, dtype, gen, device, group=128):
         self.kind, self.K, self.N, self.dtype = kind, K, N, dtype
         dev = device
@@ -128,7 +130,10 @@ class QuantLinear:
 
     def silu_and_mul(self, x):
         """gate_up layers: SiluAndMul(self(x)); one launch for the W4A16 kind (GEMM epilogue), two otherwise."""
-        if self.kind == "w4a16" and self.method.can_fuse_silu_and_mul(self.layer):
+        # measured on B200 (profiles/r2_silu_fusion_ab.txt): +2.3 .. 4.6 % tok/s at every batch 1..64 once the activation math
+        # is split over the gate AND up threads of the epilogue (gate threads alone stalled the accumulator hand-off: -1 .. 2 %
+        # at batch 32 / 64); prefill-sized M keeps the two launches (not measured)
+        if self.kind == "w4a16" and x.shape[0] <= self.fuse_silu_max_m and self.method.can_fuse_silu_and_mul(self.layer):
             return self.method.apply_silu_and_mul(self.layer, x)
         gu = self(x)
         act = torch.empty((gu.shape[0], gu.shape[1] // 2), dtype=gu.dtype, device=gu.device)
@@ -246,6 +251,16 @@ class SyntheticLlama:
         PagedAttention.write_to_paged_cache / forward_decode), or the one-launch fusion of the three."""
         kc, vc = self.kv[li]
         B, D = q.shape[0], self.shape.head_dim
+        if "query_start_loc" in meta:
+            # prefill (prompt or chunk): rotary -> cache write -> attention over (cached context, the chunk itself);
+            # the prefill branch of the reference's backends (xformers.py:262-300 -> PagedAttention.forward_prefix)
+            from .attention import PagedAttention
+            ops.rotary_embedding(positions, q.view(B, self.H * D), k.view(B, self.Hkv * D), D, self.cos_sin, True)
+            ops.reshape_and_cache(k, v, kc, vc, meta["slot_mapping"], self.kv_cache_dtype, self.kv_scale)
+            out = PagedAttention.forward_prefix(q, k, v, kc, vc, meta["block_tables"], meta["query_start_loc"],
+                                                meta["seq_lens"], meta["context_lens"], meta["max_query_len"], None, None,
+                                                self.kv_cache_dtype, self.kv_scale, self.scale)
+            return out.view(B, self.H * D)
         out = torch.empty((B, self.H, D), dtype=q.dtype, device=q.device)
         max_len = meta["max_seq_len"]
         nparts = (max_len + PARTITION_SIZE - 1) // PARTITION_SIZE
@@ -272,7 +287,11 @@ class SyntheticLlama:
                                    self.kv_scale)
         return out.view(B, self.H * D)
 
-    def forward(self, token_ids, positions, meta):
+    def forward(self, token_ids, positions, meta, return_logits=False):
+        """One step over `token_ids` [T].  Decode: T = batch, `meta` = slot_mapping / block_tables / seq_lens / max_seq_len.
+        Prefill: `meta` additionally holds query_start_loc [S + 1], context_lens [S], max_query_len (seq_lens = context +
+        query length); logits are then computed for the LAST token of every sequence only (logits_processor.py
+        _prune_hidden_states)."""
         s = self.shape
         D = s.head_dim
         h = self.embed.index_select(0, token_ids)
@@ -313,12 +332,35 @@ class SyntheticLlama:
                 ops.silu_and_mul(act, gu)
             h = self._row_parallel(L["down"], act)
         ops.fused_add_rms_norm(h, residual, self.norm, s.eps)
+        if "query_start_loc" in meta:
+            h = h.index_select(0, (meta["query_start_loc"][1:] - 1).long())
         logits = self.lm_head(h)
         if self.tp > 1:  # vocab-parallel logits gathered once per step
             parts = [torch.empty_like(logits) for _ in range(self.tp)]
             torch.distributed.all_gather(parts, logits, group=self.group)
             logits = torch.cat(parts, dim=-1)
+        if return_logits:
+            return logits
         return ops.greedy_sample(logits)
+
+    def prefill_meta(self, query_lens, context_lens, block_tables):
+        """Device metadata of a prefill call: sequence b contributes query_lens[b] new tokens at positions context_lens[b]..,
+        stored through its row of `block_tables` (int32 [S, max_blocks], CPU or device).  Returns (positions, meta)."""
+        dev = self.device
+        bt = block_tables.to(dev)
+        pos, slots, starts = [], [], [0]
+        btc = block_tables.cpu()
+        for b, (n, c) in enumerate(zip(query_lens, context_lens)):
+            p = torch.arange(c, c + n)
+            pos.append(p)
+            slots.append(btc[b, (p // self.block_size).long()].long() * self.block_size + p % self.block_size)
+            starts.append(starts[-1] + n)
+        meta = dict(slot_mapping=torch.cat(slots).to(dev), block_tables=bt,
+                    query_start_loc=torch.tensor(starts, dtype=torch.int32, device=dev),
+                    seq_lens=torch.tensor([n + c for n, c in zip(query_lens, context_lens)], dtype=torch.int32, device=dev),
+                    context_lens=torch.tensor(list(context_lens), dtype=torch.int32, device=dev),
+                    max_query_len=max(query_lens))
+        return torch.cat(pos).to(dev), meta
 
 
 class DecodeEngine:

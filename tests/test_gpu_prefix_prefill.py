@@ -98,3 +98,46 @@ def test_rejects_unsupported_shapes(built_extension):
     with pytest.raises(RuntimeError):
         context_attention_fwd(q.to(DEV), k.to(DEV), v.to(DEV), torch.empty_like(q).to(DEV), kc.to(DEV), vc.to(DEV), bt.to(DEV),
                               start.to(DEV), seq.to(DEV), ctx.to(DEV), 4)
+
+
+def test_model_prefill_equals_token_by_token_decode(built_extension):
+    """Size-independent property of the whole path: prefilling a prompt in one call (M = prompt length GEMMs, rotary,
+    reshape_and_cache, prefill attention) gives the logits of feeding the same tokens one decode step at a time (M = 1
+    GEMMs, fused decode attention), and leaves the same KV cache behind.  Also: a chunked prefill (second chunk attends to
+    the first through the paged cache) ends in the same logits."""
+    from nm_vllm_b200 import decoder
+    torch.manual_seed(0)
+    T, BS = 40, 16
+    m = decoder.SyntheticLlama(decoder.MINI, quant="w4a16", device=DEV, num_blocks=64)
+    toks = torch.randint(0, decoder.MINI.vocab, (T,), device=DEV)
+    bt = torch.tensor([[5, 9, 2, 7]], dtype=torch.int32)
+
+    def clear():
+        for kc, vc in m.kv:
+            kc.zero_(); vc.zero_()
+
+    # token by token
+    clear()
+    for t in range(T):
+        p = torch.tensor([t], device=DEV)
+        meta = dict(slot_mapping=(bt[0, t // BS].long() * BS + t % BS).view(1).to(DEV), block_tables=bt.to(DEV),
+                    seq_lens=torch.tensor([t + 1], dtype=torch.int32, device=DEV), max_seq_len=t + 1)
+        ref = m.forward(toks[t:t + 1], p, meta, return_logits=True)
+    kv_ref = [(k.clone(), v.clone()) for k, v in m.kv]
+    # one prefill call
+    clear()
+    pos, meta = m.prefill_meta([T], [0], bt)
+    got = m.forward(toks, pos, meta, return_logits=True)
+    assert got.shape == ref.shape == (1, decoder.MINI.vocab)
+    err = float((got.float() - ref.float()).abs().mean() / ref.float().abs().mean())
+    assert err < 2e-2, "prefill vs decode logits: mean relative error %g" % err
+    for (k, v), (k0, v0) in zip(m.kv, kv_ref):
+        assert torch.allclose(k.float(), k0.float(), atol=3e-2, rtol=3e-2) and torch.allclose(v.float(), v0.float(), atol=3e-2, rtol=3e-2)
+    # chunked: 24 tokens, then 16 more over the cached 24
+    clear()
+    pos, meta = m.prefill_meta([24], [0], bt)
+    m.forward(toks[:24], pos, meta, return_logits=True)
+    pos, meta = m.prefill_meta([T - 24], [24], bt)
+    got2 = m.forward(toks[24:], pos, meta, return_logits=True)
+    err2 = float((got2.float() - ref.float()).abs().mean() / ref.float().abs().mean())
+    assert err2 < 2e-2, "chunked prefill vs decode logits: mean relative error %g" % err2
