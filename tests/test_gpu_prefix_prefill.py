@@ -31,11 +31,20 @@ def _case(seed, bs, H, Hkv, D, BS, dtype, q_lens, c_lens, amp=1.0):
     return q, k, v, kc, vc, perm, start, seq, ctx
 
 
-def _run(case, max_q, alibi=None, sw=None):
+def _misaligned(t):
+    """Same values at a 4-byte (not 16-byte) aligned address: takes the direct-from-global kernel instead of the tiled one."""
+    buf = torch.empty(t.numel() + 2, dtype=t.dtype, device=DEV)
+    out = buf[2:].view(t.shape)
+    out.copy_(t)
+    return out
+
+
+def _run(case, max_q, alibi=None, sw=None, direct=False):
     from nm_vllm_b200.attention.prefix_prefill import context_attention_fwd
     q, k, v, kc, vc, bt, start, seq, ctx = case
     o = torch.full_like(q, float("nan")).to(DEV)
-    context_attention_fwd(q.to(DEV), k.to(DEV), v.to(DEV), o, kc.to(DEV), vc.to(DEV), bt.to(DEV), start.to(DEV), seq.to(DEV),
+    kd, vd = (_misaligned(k), _misaligned(v)) if direct else (k.to(DEV), v.to(DEV))
+    context_attention_fwd(q.to(DEV), kd, vd, o, kc.to(DEV), vc.to(DEV), bt.to(DEV), start.to(DEV), seq.to(DEV),
                           ctx.to(DEV), max_q, None if alibi is None else alibi.to(DEV), sw)
     ref = ops_ref.context_attention_ref(q, k, v, kc, vc, bt, start, seq, ctx, alibi, sw or 0)
     got = o.cpu()
@@ -46,30 +55,47 @@ def _run(case, max_q, alibi=None, sw=None):
         int(bad.sum()), bad.numel(), float((got.float() - ref.float()).abs().max()))
 
 
+@pytest.mark.parametrize("direct", [False, True], ids=["tiled", "direct"])
 @pytest.mark.parametrize("G", [1, 8, 64])
 @pytest.mark.parametrize("D", [128, 96, 24])
 @pytest.mark.parametrize("sw", [0, 16, 256])
-def test_contexted_kv_attention_like_the_reference_test(built_extension, G, D, sw):
+def test_contexted_kv_attention_like_the_reference_test(built_extension, G, D, sw, direct):
     random.seed(G * 1000 + D + sw)
     bs, H = 4, 64
     q_lens = [random.randint(16, 200) for _ in range(bs)]
     c_lens = [random.randint(16, 300) for _ in range(bs)]
-    _run(_case(G + D + sw, bs, H, H // G, D, 32, torch.float16, q_lens, c_lens), max(q_lens), sw=sw)
+    _run(_case(G + D + sw, bs, H, H // G, D, 32, torch.float16, q_lens, c_lens), max(q_lens), sw=sw, direct=direct)
 
 
+@pytest.mark.parametrize("direct", [False, True], ids=["tiled", "direct"])
 @pytest.mark.parametrize("BS", [8, 16, 32])
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
-def test_block_sizes_dtypes_and_ragged_edges(built_extension, BS, dtype):
+def test_block_sizes_dtypes_and_ragged_edges(built_extension, BS, dtype, direct):
     # context 0 (pure causal prefill), query of 1 token (a decode step), lengths that are not tile multiples
     q_lens = [1, 17, 64, 65, 5]
     c_lens = [33, 0, 15, 129, 1]
-    _run(_case(BS, 5, 8, 2, 64, BS, dtype, q_lens, c_lens), max(q_lens))
+    _run(_case(BS, 5, 8, 2, 64, BS, dtype, q_lens, c_lens), max(q_lens), direct=direct)
 
 
-def test_alibi(built_extension):
+def test_stale_cache_beyond_the_context_is_never_read_as_a_value(built_extension):
+    # NaN in every cache slot past the context (and in unused blocks): outputs stay finite and correct
+    q, k, v, kc, vc, bt, start, seq, ctx = _case(21, 2, 8, 2, 128, 16, torch.bfloat16, [30, 70], [37, 5])
+    kc2, vc2 = torch.full_like(kc, float("nan")), torch.full_like(vc, float("nan"))
+    for b in range(2):
+        c = int(ctx[b])
+        for p in range(c):
+            blk, off = int(bt[b, p // 16]), p % 16
+            kc2[blk, :, :, off, :] = kc[blk, :, :, off, :]
+            vc2[blk, :, :, off] = vc[blk, :, :, off]
+    for direct in (False, True):
+        _run((q, k, v, kc2, vc2, bt, start, seq, ctx), 70, direct=direct)
+
+
+@pytest.mark.parametrize("direct", [False, True], ids=["tiled", "direct"])
+def test_alibi(built_extension, direct):
     H = 8
     slopes = torch.tensor([2.0 ** (-(i + 1)) for i in range(H)], dtype=torch.float32)
-    _run(_case(3, 3, H, 4, 128, 16, torch.float16, [40, 7, 100], [50, 120, 0]), 100, alibi=slopes)
+    _run(_case(3, 3, H, 4, 128, 16, torch.float16, [40, 7, 100], [50, 120, 0]), 100, alibi=slopes, direct=direct)
 
 
 def test_empty_query_sequence_and_padding_rows(built_extension):
