@@ -122,7 +122,7 @@ struct GemmArgs {
   int silu_inter;              // > 0: gate_up layer with SiLU(gate) * up fused into the epilogue.  N = 2 * silu_inter, tile t = gate
                                // columns [64 t, 64 t + 64) (TMEM lanes 0..63) + up columns silu_inter + [64 t, 64 t + 64) (lanes
                                // 64..127); C is [M, silu_inter]
-  int exp;                     // bring-up ablations (B200_GEMM_EXP, prof builds only): 1 no dequant ALU, 2 no MMAs, 3 no epilogue reads, 4 no TMEM stores
+  int exp;                     // bring-up ablations (B200_GEMM_EXP, prof / ablate builds only): 1 no dequant ALU, 2 no MMAs, 3 no epilogue reads, 4 no TMEM stores, 5 no activation TMA, 6 no weight TMA
 };
 
 // ---- dequantisation ------------------------------------------------------------------------------------------
@@ -265,7 +265,11 @@ __device__ __forceinline__ int ld_acquire_gpu(const int* p) {
 #define EXP_IS(x) (args.exp == (x))
 #define TRACE(role, idx, ev) if (args.trace && (int)blockIdx.x == args.trace_cta && lane == 0 && (idx) < 64) { args.trace[((role) * 64 + (idx)) * 8 + (ev)] = clock64(); }
 #else
+#ifdef B200_GEMM_ABLATE   // ablation switches without the cycle counters (tools/build_variant.py ablate -DB200_GEMM_ABLATE)
+#define EXP_IS(x) (args.exp == (x))
+#else
 #define EXP_IS(x) false
+#endif
 #define TRACE(role, idx, ev)
 #define PROF_ON(x) false
 #define PROF_ACC(var)
@@ -443,27 +447,39 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     setmaxnreg_dec<Cfg::REG_LOW>();
     // ================= TMA producers: warp 0 streams packed weights, warp 1 activations + group scales ================
     // (the whole warp runs the loops so that coordinates / descriptors stay warp-uniform; one elected lane issues)
-    auto coords = [&](int it, int& nt, int& mc, int& ks) {
-      const int u = u_begin + it;
-      const int tile = u / KS;
-      ks = u - tile * KS;
-      nt = tile % args.n_tiles;
-      mc = tile / args.n_tiles;
+    // (tile, k-stage) of the first unit by division ONCE, then stepped: runtime integer divisions cost ~50 dependent
+    // instructions each, and three of them per unit made this single warp the slowest stage of the whole pipeline
+    // (ablations that removed the dequant ALU work, the MMAs, the TMEM traffic or the TMA traffic itself left the kernel
+    // time unchanged: profiles/r2_gemm_ablations.txt)
+    int ks, nt, mc;
+    {
+      const int tile0 = u_begin / KS;
+      ks = u_begin - tile0 * KS;
+      nt = tile0 % args.n_tiles;
+      mc = tile0 / args.n_tiles;
+    }
+    auto advance = [&]() {
+      if (++ks == KS) {
+        ks = 0;
+        if (++nt == args.n_tiles) { nt = 0; ++mc; }
+      }
     };
     if (warp == 0) {
       // weights do not depend on the previous kernel of the stream: no PDL wait on this path at all
       const uint64_t pol_w = policy_evict_first();   // weights are streamed exactly once
       const uint64_t pol_s = policy_evict_first();
+      int s = 0, q = 0;
+      uint32_t ph = 1, qph = 1;                      // parity to wait for on the "empty" barriers: ((it / ring) & 1) ^ 1
       for (int it = 0; it < n_units; ++it) {
-        const int s = it % NW;
-        if (it >= NW) mbar_wait(wempty_bar(s), ((it / NW) & 1) ^ 1);
+        if (it >= NW) mbar_wait(wempty_bar(s), ph);
         TRACE(9, it, 0);
-        int nt, mc, ks;
-        coords(it, nt, mc, ks);
         // the tile's two 64-column halves are separate boxes ([half][slab][64 columns] in shared memory): adjacent
         // columns normally, the gate / up pair (n, n + inter) when the SiLU epilogue is on
         const int col0 = silu ? nt * 64 : nt * kTileN;
         const int col1 = silu ? silu + nt * 64 : nt * kTileN + 64;
+        if (EXP_IS(6)) {   // ablation: no weight traffic at all
+          if (elect_one()) mbar_arrive(wfull_bar(s));
+        } else
         if (elect_one()) {
           mbar_arrive_expect_tx(wfull_bar(s), Cfg::W_STAGE_BYTES);
           tma_2d_g2s_hint(w_base + s * Cfg::W_STAGE_BYTES, &tmap_w, col0 * (BITS / 4), ks * (kStageK / 16), wfull_bar(s), pol_w);
@@ -473,26 +489,30 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         __syncwarp();
         if (GM == kGroup128) {
           // the stage's two group-scale rows (static data like the weights) -> the epilogue's scale ring
-          const int q = it % NSC;
-          if (it >= NSC) mbar_wait(scempty_bar(q), ((it / NSC) & 1) ^ 1);
+          if (it >= NSC) mbar_wait(scempty_bar(q), qph);
           if (elect_one()) {
             mbar_arrive_expect_tx(scfull_bar(q), Cfg::SCQ_STAGE_BYTES);
             tma_2d_g2s_hint(scq_base + q * Cfg::SCQ_STAGE_BYTES, &tmap_s, col0, ks * 2, scfull_bar(q), pol_s);
             tma_2d_g2s_hint(scq_base + q * Cfg::SCQ_STAGE_BYTES + Cfg::SCQ_STAGE_BYTES / 2, &tmap_s, col1, ks * 2, scfull_bar(q), pol_s);
           }
           __syncwarp();
+          if (++q == NSC) { q = 0; qph ^= 1; }
         }
+        if (++s == NW) { s = 0; ph ^= 1; }
+        advance();
       }
     } else {
       const uint64_t pol_a = policy_evict_last();    // activations / scales are re-read by every CTA
       const uint32_t tx = Cfg::A_STAGE_BYTES + (GM == kGroupSmall ? (uint32_t)gps * 256u : 0u);
       pdl_wait();
+      int s = 0;
+      uint32_t ph = 1;
       for (int it = 0; it < n_units; ++it) {
-        const int s = it % NA;
-        if (it >= NA) mbar_wait(actempty_bar(s), ((it / NA) & 1) ^ 1);
+        if (it >= NA) mbar_wait(actempty_bar(s), ph);
         TRACE(10, it, 0);
-        int nt, mc, ks;
-        coords(it, nt, mc, ks);
+        if (EXP_IS(5)) {   // ablation: no activation traffic at all
+          if (elect_one()) mbar_arrive(actfull_bar(s));
+        } else
         if (elect_one()) {
           mbar_arrive_expect_tx(actfull_bar(s), tx);
           tma_3d_g2s_hint(act_base + s * Cfg::A_STAGE_BYTES, &tmap_a, 0, mc * MPAD, ks * (kStageK / 64), actfull_bar(s), pol_a);
@@ -503,6 +523,8 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
           }
         }
         __syncwarp();
+        if (++s == NA) { s = 0; ph ^= 1; }
+        advance();
       }
     }
   } else if (warp < kIssuerWarp0) {

@@ -40,7 +40,19 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+// non-blocking poll in a tight loop: mbarrier.try_wait may suspend the thread, and the wake-up after the phase completes
+// was measured at 100-400 clk per hand-off in the Marlin GEMM pipeline; test_wait sees the flip one shared-memory round
+// trip later at the price of issue slots
+__device__ __forceinline__ void mbar_wait_spin(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "SPIN_%=:\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@!p bra SPIN_%=;\n\t}\n" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_wait_block(uint32_t bar, uint32_t parity) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
       "WAIT_%=:\n\t"
@@ -50,6 +62,17 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       "DONE_%=:\n\t}\n" ::"r"(bar),
       "r"(parity)
       : "memory");
+}
+
+#ifndef B200_MBAR_SPIN
+#define B200_MBAR_SPIN 0
+#endif
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+#if B200_MBAR_SPIN
+  mbar_wait_spin(bar, parity);
+#else
+  mbar_wait_block(bar, parity);
+#endif
 }
 
 // generic-proxy writes to smem -> visible to the async proxy (UMMA / TMA reads)

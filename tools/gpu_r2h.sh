@@ -1,0 +1,8 @@
+#!/bin/bash
+mkdir -p gpurun_out
+{
+echo "=== warm-up (discard)"; timeout 200 python tools/gemm_perf.py 64 bf16 o 2>&1 | grep "M="
+echo "=== current build"; timeout 200 python tools/gemm_perf.py 1,16,64 bf16 2>&1 | grep "M="
+} > gpurun_out/gemm_now.txt 2>&1
+cat gpurun_out/gemm_now.txt
+timeout 900 python -m pytest tests/test_gpu_marlin.py tests/test_gpu_gemm_silu.py -m gpu -x -q > gpurun_out/pytest_marlin.log 2>&1; echo "pytest rc=$?"; tail -4 gpurun_out/pytest_marlin.log
