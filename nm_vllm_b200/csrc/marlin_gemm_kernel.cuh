@@ -830,7 +830,7 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
           __syncwarp();
           if (lane == 0) mbar_arrive(scempty_bar(q));
         }
-        const float sc = sc_h[hu & 1];
+        const float sc = (MPAD >= 128) ? ((hu & 1) ? sc_h[1] : sc_h[0]) : sc_h[hu & 1];   // (static indices keep sc_h in registers next to the asm below)
         if (et < 32) TRACE(8, hu, 0);
         mbar_wait(accfull_bar(o, ab), (jc / NBUF) & 1);
         PROF_ACC(p_wacc);
@@ -849,8 +849,25 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
             __syncwarp();
             if (lane == 0) mbar_arrive(accempty_bar(o, ab));
           }
+          if constexpr (MPAD >= 128) {
+            // prefill-sized M: packed fp32 FMA (FFMA2) halves the arithmetic of the 64-column epilogue threads (2k-token
+            // Llama-3-8B prefill 38.0 -> 35.7 ms).  NOT used below 128: measured 5-8 % SLOWER on the decode shapes, whose
+            // timing is sensitive to the instruction schedule of this loop (profiles/r2_gemm_ablations.txt)
 #pragma unroll
-          for (int j = 0; j < CH; ++j) acc[c0 + j] = fmaf(sc, __uint_as_float(t[j]), acc[c0 + j]);
+            for (int j = 0; j < CH; j += 2) {
+              float2 av = make_float2(acc[c0 + j], acc[c0 + j + 1]);
+              const float2 tv = make_float2(__uint_as_float(t[j]), __uint_as_float(t[j + 1]));
+              const float2 sv = make_float2(sc, sc);
+              asm("fma.rn.f32x2 %0, %1, %2, %0;"
+                  : "+l"(*reinterpret_cast<unsigned long long*>(&av))
+                  : "l"(*reinterpret_cast<const unsigned long long*>(&sv)), "l"(*reinterpret_cast<const unsigned long long*>(&tv)));
+              acc[c0 + j] = av.x;
+              acc[c0 + j + 1] = av.y;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < CH; ++j) acc[c0 + j] = fmaf(sc, __uint_as_float(t[j]), acc[c0 + j]);
+          }
         }
         PROF_ACC(p_epi);
         if (et < 32) TRACE(8, hu, 3);
