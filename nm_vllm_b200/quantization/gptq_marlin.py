@@ -182,7 +182,13 @@ class GPTQMarlinLinearMethod(LinearMethodBase):
     def can_fuse_silu_and_mul(self, layer: torch.nn.Module) -> bool:
         """gate_up_proj layers whose SiluAndMul can run in the GEMM epilogue (one launch instead of two)."""
         n_part = layer.output_size_per_partition
-        return (not self.quant_config.desc_act) and n_part % 128 == 0
+        if self.quant_config.desc_act or n_part % 128 != 0:
+            return False
+        # The fused epilogue lives on the stream-K path of the kernel.  A layer with few tiles (a TP shard: tiles * 2 <= SMs)
+        # takes the cluster split-K path instead, which is 1.5-2x faster than stream-K there (profiles/r2_gemm_cluster_vs_streamk.txt)
+        # -- measured: fusing on such shards made the TP4 / TP8 step slower (2.31 -> 2.43 ms), so they keep the two launches.
+        sms = torch.cuda.get_device_properties(layer.qweight.device).multi_processor_count
+        return (n_part // 128) * 2 > sms
 
     def apply_silu_and_mul(self, layer: torch.nn.Module, x: torch.Tensor) -> torch.Tensor:
         """`SiluAndMul()(self.apply(layer, x))` for a merged gate_up layer (llama.py:74-90) in one kernel launch:
