@@ -5,11 +5,11 @@ Only what the path needs lives here:
   _custom_ops.py        mirror of vllm/_custom_ops.py for the hot-path operators (same names / argument order / returns)
   quantization/         QuantizationConfig / LinearMethodBase mirrors: gptq_marlin, marlin, gptq_marlin_24, fp8 (+ the fp8
                         kv-scale method), compressed-tensors (WNA16, W4A16 2:4, W8A8) + Marlin scale permutation helpers
-  attention/            PagedAttention (+ metadata), the decode half of the AttentionBackend / Impl / Metadata contract,
-                        the Attention layer that owns kv_scale
+  attention/            PagedAttention (+ metadata; forward_decode, forward_prefix), prefix_prefill.context_attention_fwd, the
+                        decode half of the AttentionBackend / Impl / Metadata contract, the Attention layer that owns kv_scale
   custom_all_reduce.py  host side of the NVLink all-reduce kernels (mirror of the reference's CustomAllreduce)
   tp.py                 tensor-parallel sharding rules of the linear layers (column / row parallel, Marlin shard validity)
-  decoder.py            synthetic Llama decode step built from the pieces above (bench / smoke / e2e harness)
+  decoder.py            synthetic Llama decode step and prefill built from the pieces above (bench / smoke / e2e harness)
   capi.py               ctypes view of the C ABI
 
 There is no CPU fallback: calling an operator without the built extension raises.
