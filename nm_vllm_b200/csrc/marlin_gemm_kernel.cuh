@@ -431,8 +431,12 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
   const int u_base = clustered ? (int)(blockIdx.x / CS) * KS : 0;
   const int u_begin = u_base + part.start(clustered ? c_rank : (int)blockIdx.x);
   const int u_end = u_base + part.start((clustered ? c_rank : (int)blockIdx.x) + 1);
+#ifdef B200_GEMM_ABLATE
   // ablation 8: every role finds an empty unit range -> the kernel is launch + prologue + TMEM alloc / free + teardown only
   const int n_units = EXP_IS(8) ? 0 : u_end - u_begin;
+#else
+  const int n_units = u_end - u_begin;
+#endif
   const int gps = args.groups_per_stage;
   const int silu = FUSE ? 0 : args.silu_inter;   // the all-reduce instantiation carries none of the SiLU code
 
@@ -802,7 +806,11 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         if (jb + j < m_valid) cdst[(size_t)(jb + j) * args.N] = from_f32<T>(acc[j] * ch_scale);
     };
     long long p_mark = PROF_ON(args.prof) ? clock64() : 0, p_wacc = 0, p_epi = 0, p_red = 0;
+#ifdef B200_GEMM_ABLATE
     for (int u = u_begin; u < u_begin + n_units;) {
+#else
+    for (int u = u_begin; u < u_end;) {
+#endif
       const int tile = u / KS, ks0 = u - tile * KS;
       const int len = min(KS - ks0, u_end - u);
       const int it0 = u - u_begin, it1 = it0 + len;
