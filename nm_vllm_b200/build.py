@@ -70,7 +70,8 @@ def build_ops(force=False, verbose=False):
                     print("nvcc", os.path.basename(s))
     objs = [os.path.join(OBJ, os.path.basename(s)[:-3] + ".o") for s in srcs]
     if jobs or force or _newer(objs, LIB_OPS):
-        _run([NVCC, "-shared", "-o", LIB_OPS] + objs + ["-lcudart", "-Xlinker", "-rpath=/usr/local/cuda/lib64"])
+        _run([NVCC, "-shared", "-o", LIB_OPS] + objs + ["-lcudart", "-Xlinker", "-rpath=/usr/local/cuda/lib64",
+                                                          "-Xlinker", "-soname=libb200ops.so"])
     return LIB_OPS
 
 

@@ -453,9 +453,8 @@ marlin_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     // ================= TMA producers: warp 0 streams packed weights, warp 1 activations + group scales ================
     // (the whole warp runs the loops so that coordinates / descriptors stay warp-uniform; one elected lane issues)
     // (tile, k-stage) of the first unit by division ONCE, then stepped: runtime integer divisions cost ~50 dependent
-    // instructions each, and three of them per unit made this single warp the slowest stage of the whole pipeline
-    // (ablations that removed the dequant ALU work, the MMAs, the TMEM traffic or the TMA traffic itself left the kernel
-    // time unchanged: profiles/r2_gemm_ablations.txt)
+    // instructions each, and three of them per unit in these single-warp loops cost 6-9 % of the kernel time
+    // (production before / after: profiles/r2_gemm_ablations.txt)
     int ks, nt, mc;
     {
       const int tile0 = u_begin / KS;

@@ -40,9 +40,9 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-// non-blocking poll in a tight loop: mbarrier.try_wait may suspend the thread, and the wake-up after the phase completes
-// was measured at 100-400 clk per hand-off in the Marlin GEMM pipeline; test_wait sees the flip one shared-memory round
-// trip later at the price of issue slots
+// non-blocking poll in a tight loop (build option B200_MBAR_SPIN=1, not the default; its one measurement this round was
+// taken with a mis-loaded variant library and says nothing either way): mbarrier.try_wait may suspend the thread,
+// test_wait sees the flip one shared-memory round trip later at the price of issue slots
 __device__ __forceinline__ void mbar_wait_spin(uint32_t bar, uint32_t parity) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"

@@ -1,6 +1,12 @@
 """Tuning helper: build a variant of libb200ops.so with extra -D flags for the decode GEMM translation units.
 usage: python tools/build_variant.py NAME -DB200_DEC_NSHF_FMA=0 ...   ->  build/variants/NAME/libb200ops.so
-Run with B200_LIB_OPS=build/variants/NAME/libb200ops.so."""
+Run with B200_LIB_OPS=build/variants/NAME/libb200ops.so.
+
+PITFALL (cost a session of wrong conclusions): _b200_C.so has a NEEDED entry for libb200ops.so.  Without a SONAME on the
+variant the loader does not recognise the pre-loaded variant as that library and maps the in-tree copy as well; two fatbins
+then register kernels of the same name and WHICH one a launch runs differs per instantiation (some ablations silently ran
+the production kernel and "changed nothing").  Both link lines now set -soname=libb200ops.so; tools/variant_check.py prints a
+checksum to confirm that a variant really runs (an ablated kernel gives a different one)."""
 import os, subprocess, sys
 from concurrent.futures import ThreadPoolExecutor
 sys.path.insert(0, ".")
@@ -18,5 +24,6 @@ def cc(s):
 with ThreadPoolExecutor(8) as ex:
     vobjs = list(ex.map(cc, var))
 objs = [os.path.join(B.OBJ, os.path.basename(s)[:-3] + ".o") for s in srcs if s not in var] + vobjs
-B._run([B.NVCC, "-shared", "-o", os.path.join(out, "libb200ops.so")] + objs + ["-lcudart", "-Xlinker", "-rpath=/usr/local/cuda/lib64"])
+B._run([B.NVCC, "-shared", "-o", os.path.join(out, "libb200ops.so")] + objs + ["-lcudart", "-Xlinker", "-rpath=/usr/local/cuda/lib64",
+                                                                          "-Xlinker", "-soname=libb200ops.so"])
 print("built", out)
