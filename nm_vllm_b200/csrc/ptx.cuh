@@ -40,9 +40,10 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-// non-blocking poll in a tight loop (build option B200_MBAR_SPIN=1, not the default; its one measurement this round was
-// taken with a mis-loaded variant library and says nothing either way): mbarrier.try_wait may suspend the thread,
-// test_wait sees the flip one shared-memory round trip later at the price of issue slots
+// non-blocking poll in a tight loop (build option B200_MBAR_SPIN=1, not the default): mbarrier.try_wait may suspend the
+// thread, test_wait sees the flip one shared-memory round trip later at the price of issue slots -- measured 4-6 % SLOWER
+// on every Llama-3-8B shape of the Marlin GEMM (profiles/r2_gemm_ablations.txt): the kernel is short of issue slots, not
+// of wake-up latency
 __device__ __forceinline__ void mbar_wait_spin(uint32_t bar, uint32_t parity) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
