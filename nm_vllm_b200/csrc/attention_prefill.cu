@@ -285,15 +285,18 @@ __device__ __forceinline__ void ldsm4_t(uint32_t (&r)[4], uint32_t addr) {
 }
 
 template <typename T, int DPAD>
-__global__ void __launch_bounds__(128) prefill_paged_attn_tiled_kernel(const PrefillArgs a) {
+__global__ void __launch_bounds__(128, 3) prefill_paged_attn_tiled_kernel(const PrefillArgs a) {   // 3 CTAs / SM: <= 168 registers, 3 x 64 KB
   using TL = PrefillTile<DPAD>;
-  __shared__ __align__(128) uint8_t smem[TL::K_BYTES + TL::V_BYTES];
+  extern __shared__ __align__(128) uint8_t smem[];       // two buffers of (K tile, V tile)
+  constexpr uint32_t kBufBytes = TL::K_BYTES + TL::V_BYTES;
   pdl_wait();
   pdl_launch_dependents();
   const int seq = blockIdx.z, head = blockIdx.y;
   const int ctx = a.ctx_lens[seq];
   const int qlen = a.seq_lens[seq] - ctx;
-  const int m0 = blockIdx.x * kPrefillRows;
+  // heaviest query blocks first: block x attends to ctx + 64 (x + 1) keys, so the last blocks of a long prompt run ~32x longer
+  // than the first; launched in index order they would make up the tail of the grid (2.3 waves of 3 CTAs / SM on a 2k prompt)
+  const int m0 = (int)(gridDim.x - 1 - blockIdx.x) * kPrefillRows;
   if (m0 >= qlen) return;                                // CTA-uniform
   const int start = a.start_loc[seq];
   const int kvh = head / (a.num_heads / a.num_kv_heads);
@@ -309,7 +312,7 @@ __global__ void __launch_bounds__(128) prefill_paged_attn_tiled_kernel(const Pre
   const T* VC = reinterpret_cast<const T*>(a.vc);
   const int* bt = a.block_tables + (int64_t)seq * a.bt_stride;
   const float slope = a.alibi ? a.alibi[head] : 0.f;
-  const uint32_t Ks = (uint32_t)__cvta_generic_to_shared(smem), Vs = Ks + TL::K_BYTES;
+  const uint32_t Ks = (uint32_t)__cvta_generic_to_shared(smem), Vs = Ks + TL::K_BYTES;   // buffer 0; buffer 1 at + kBufBytes
 
   uint32_t qa[KSTEPS][4];
 #pragma unroll
@@ -330,7 +333,7 @@ __global__ void __launch_bounds__(128) prefill_paged_attn_tiled_kernel(const Pre
 
   // S = Q.K^T over the staged 64 keys, masks, online softmax, O += P.V.  NEW: keys are the call's own tokens (causal, V row-major);
   // otherwise cached context (V^T)
-  auto compute = [&](const int t0, const bool is_new) {
+  auto compute = [&](const int t0, const bool is_new, const uint32_t Kb, const uint32_t Vb) {
     float s[8][4];
 #pragma unroll
     for (int nt = 0; nt < 8; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
@@ -340,12 +343,25 @@ __global__ void __launch_bounds__(128) prefill_paged_attn_tiled_kernel(const Pre
 #pragma unroll
       for (int np = 0; np < 4; ++np) {
         uint32_t r[4];
-        ldsm4(r, Ks + kv_off(16 * np + 8 * (mid >> 1) + rr, 2 * kk + (mid & 1)));
+        ldsm4(r, Kb + kv_off(16 * np + 8 * (mid >> 1) + rr, 2 * kk + (mid & 1)));
         MmaT<T>::mma(s[2 * np], qa[kk], r[0], r[1]);
         MmaT<T>::mma(s[2 * np + 1], qa[kk], r[2], r[3]);
       }
     }
     float mx[2] = {-INFINITY, -INFINITY};
+    // most tiles need no mask at all: every key valid and (own tokens) strictly below this warp's diagonal, no window, no ALiBi
+    const bool plain = SW == 0 && a.alibi == nullptr &&
+                       (is_new ? (t0 + TL::BN <= qlen && t0 + TL::BN - 1 <= m0 + 16 * warp) : (t0 + TL::BN <= ctx));
+    if (plain) {
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          s[nt][i] *= a.scale;
+          mx[i >> 1] = fmaxf(mx[i >> 1], s[nt][i]);
+        }
+      }
+    } else
 #pragma unroll
     for (int nt = 0; nt < 8; ++nt) {
 #pragma unroll
@@ -399,49 +415,65 @@ __global__ void __launch_bounds__(128) prefill_paged_attn_tiled_kernel(const Pre
 #pragma unroll
       for (int dp = 0; dp < NDT / 2; ++dp) {
         uint32_t r[4];
-        if (is_new) ldsm4_t(r, Vs + kv_off(16 * ks + 8 * (mid & 1) + rr, 2 * dp + (mid >> 1)));
-        else ldsm4(r, Vs + vt_off(8 * (2 * dp + (mid >> 1)) + rr, 2 * ks + (mid & 1)));
+        if (is_new) ldsm4_t(r, Vb + kv_off(16 * ks + 8 * (mid & 1) + rr, 2 * dp + (mid >> 1)));
+        else ldsm4(r, Vb + vt_off(8 * (2 * dp + (mid >> 1)) + rr, 2 * ks + (mid & 1)));
         MmaT<T>::mma(acc[2 * dp], pa, r[0], r[1]);
         MmaT<T>::mma(acc[2 * dp + 1], pa, r[2], r[3]);
       }
     }
   };
 
-  // ---- cached context ---------------------------------------------------------------------------------------------------
-  for (int t0 = 0; t0 < ctx; t0 += TL::BN) {
-    __syncthreads();
-    for (int id = tid; id < TL::BN * CPR; id += 128) {
-      const int t = id / CPR, c = id - t * CPR, tok = t0 + t;
-      const bool ok = tok < ctx && 8 * c < D;
-      const T* src = ok ? KC + (int64_t)bt[tok / BS] * a.kc_bs + (int64_t)kvh * a.kc_hs + ((int64_t)c * BS + tok % BS) * 8 : KC;
-      cp_async16(Ks + kv_off(t, c), src, ok ? 16 : 0);
-    }
-    for (int id = tid; id < DPAD * 8; id += 128) {
-      const int d = id >> 3, j = id & 7, tok0 = t0 + 8 * j;
-      int nv = ctx - tok0;                               // valid keys of this 8-key chunk; the rest is zero-filled so that
-      nv = (d < D) ? (nv > 8 ? 8 : (nv < 0 ? 0 : nv)) : 0;   // stale cache contents never meet a zero probability
-      const T* src = nv > 0 ? VC + (int64_t)bt[tok0 / BS] * a.vc_bs + (int64_t)kvh * a.vc_hs + (int64_t)d * BS + tok0 % BS : VC;
-      cp_async16(Vs + vt_off(d, j), src, nv * 2);
-    }
-    cp_async_wait_all();
-    __syncthreads();
-    if (warp_active) compute(t0, false);
-  }
-  // ---- the call's own tokens (causal) ---------------------------------------------------------------------------------------
+  // ---- one list of 64-key tiles: the cached context first, then the call's own tokens; two buffers, the copy of tile
+  // i + 1 is in flight while tile i is computed ------------------------------------------------------------------------------
   const int n_end = min(qlen, m0 + kPrefillRows);
-  for (int t0 = 0; t0 < n_end; t0 += TL::BN) {
-    __syncthreads();
-    for (int id = tid; id < TL::BN * CPR; id += 128) {
-      const int t = id / CPR, c = id - t * CPR, tok = t0 + t;
-      const bool ok = tok < qlen && 8 * c < D;
-      const int64_t off = ok ? (int64_t)(start + tok) * a.k_s0 + (int64_t)kvh * a.k_s1 + 8 * c : 0;
-      const int64_t voff = ok ? (int64_t)(start + tok) * a.v_s0 + (int64_t)kvh * a.v_s1 + 8 * c : 0;
-      cp_async16(Ks + kv_off(t, c), Kn + off, ok ? 16 : 0);
-      cp_async16(Vs + kv_off(t, c), Vn + voff, ok ? 16 : 0);
+  const int n_ctx_tiles = (ctx + TL::BN - 1) / TL::BN, n_tiles = n_ctx_tiles + (n_end + TL::BN - 1) / TL::BN;
+  auto load_tile = [&](const int ti) {
+    const uint32_t kb = Ks + (uint32_t)(ti & 1) * kBufBytes, vb = Vs + (uint32_t)(ti & 1) * kBufBytes;
+    if (ti < n_ctx_tiles) {
+      const int t0 = ti * TL::BN;
+      for (int id = tid; id < TL::BN * CPR; id += 128) {
+        const int t = id / CPR, c = id - t * CPR, tok = t0 + t;
+        const bool ok = tok < ctx && 8 * c < D;
+        const T* src = ok ? KC + (int64_t)bt[tok / BS] * a.kc_bs + (int64_t)kvh * a.kc_hs + ((int64_t)c * BS + tok % BS) * 8 : KC;
+        cp_async16(kb + kv_off(t, c), src, ok ? 16 : 0);
+      }
+      for (int id = tid; id < DPAD * 8; id += 128) {
+        const int d = id >> 3, j = id & 7, tok0 = t0 + 8 * j;
+        int nv = ctx - tok0;                               // valid keys of this 8-key chunk; the rest is zero-filled so that
+        nv = (d < D) ? (nv > 8 ? 8 : (nv < 0 ? 0 : nv)) : 0;   // stale cache contents never meet a zero probability
+        const T* src = nv > 0 ? VC + (int64_t)bt[tok0 / BS] * a.vc_bs + (int64_t)kvh * a.vc_hs + (int64_t)d * BS + tok0 % BS : VC;
+        cp_async16(vb + vt_off(d, j), src, nv * 2);
+      }
+    } else {
+      const int t0 = (ti - n_ctx_tiles) * TL::BN;
+      for (int id = tid; id < TL::BN * CPR; id += 128) {
+        const int t = id / CPR, c = id - t * CPR, tok = t0 + t;
+        const bool ok = tok < qlen && 8 * c < D;
+        const int64_t off = ok ? (int64_t)(start + tok) * a.k_s0 + (int64_t)kvh * a.k_s1 + 8 * c : 0;
+        const int64_t voff = ok ? (int64_t)(start + tok) * a.v_s0 + (int64_t)kvh * a.v_s1 + 8 * c : 0;
+        cp_async16(kb + kv_off(t, c), Kn + off, ok ? 16 : 0);
+        cp_async16(vb + kv_off(t, c), Vn + voff, ok ? 16 : 0);
+      }
     }
-    cp_async_wait_all();
-    __syncthreads();
-    if (warp_active && t0 <= m0 + 16 * warp + 15) compute(t0, true);   // tiles entirely above the warp's rows are all masked
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  if (n_tiles > 0) load_tile(0);
+  for (int ti = 0; ti < n_tiles; ++ti) {
+    if (ti + 1 < n_tiles) {
+      load_tile(ti + 1);                                   // its buffer was released by the barrier that ended tile ti - 1
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();                                       // tile ti has landed for every thread
+    const uint32_t kb = Ks + (uint32_t)(ti & 1) * kBufBytes, vb = Vs + (uint32_t)(ti & 1) * kBufBytes;
+    if (ti < n_ctx_tiles) {
+      if (warp_active) compute(ti * TL::BN, false, kb, vb);
+    } else {
+      const int t0 = (ti - n_ctx_tiles) * TL::BN;
+      if (warp_active && t0 <= m0 + 16 * warp + 15) compute(t0, true, kb, vb);   // tiles entirely above the warp's rows are all masked
+    }
+    __syncthreads();                                       // everyone is done with buffer ti & 1 before tile ti + 2 overwrites it
   }
 
   if (!warp_active) return;
@@ -471,10 +503,21 @@ static int launch_prefill(const PrefillArgs& a, int batch, int max_input_len, cu
   const bool aligned = ((a.k_s0 | a.k_s1 | a.v_s0 | a.v_s1 | a.kc_bs | a.kc_hs | a.vc_bs | a.vc_hs) % 8 == 0) &&
                        (((uintptr_t)a.k | (uintptr_t)a.v | (uintptr_t)a.kc | (uintptr_t)a.vc) % 16 == 0);
   if (aligned && !no_tiled) {
-    if (D <= 32) e = launch_pdl(prefill_paged_attn_tiled_kernel<T, 32>, grid, dim3(128), 0, st, a);
-    else if (D <= 64) e = launch_pdl(prefill_paged_attn_tiled_kernel<T, 64>, grid, dim3(128), 0, st, a);
-    else if (D <= 96) e = launch_pdl(prefill_paged_attn_tiled_kernel<T, 96>, grid, dim3(128), 0, st, a);
-    else e = launch_pdl(prefill_paged_attn_tiled_kernel<T, 128>, grid, dim3(128), 0, st, a);
+#define PREFILL_GO(DP)                                                                                                   \
+  do {                                                                                                                   \
+    constexpr int smem = 2 * (PrefillTile<DP>::K_BYTES + PrefillTile<DP>::V_BYTES);                                      \
+    static bool attr_done = false;   /* > 48 KB of dynamic shared memory needs the opt-in, once per instantiation */     \
+    if (!attr_done) {                                                                                                    \
+      cudaFuncSetAttribute(prefill_paged_attn_tiled_kernel<T, DP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);   \
+      attr_done = true;                                                                                                  \
+    }                                                                                                                    \
+    e = launch_pdl(prefill_paged_attn_tiled_kernel<T, DP>, grid, dim3(128), smem, st, a);                                \
+  } while (0)
+    if (D <= 32) PREFILL_GO(32);
+    else if (D <= 64) PREFILL_GO(64);
+    else if (D <= 96) PREFILL_GO(96);
+    else PREFILL_GO(128);
+#undef PREFILL_GO
     if (e != cudaSuccess) return set_error(B200_ECUDA, "context_attention_fwd launch: %s", cudaGetErrorString(e));
     return B200_OK;
   }
