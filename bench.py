@@ -136,7 +136,7 @@ _OUR_KERNELS_PER_CALL = {  # CUDA launches of OUR kernels behind one operator ca
     "paged_attention_v1": 1, "paged_attention_v2": 2, "gptq_marlin_gemm": 1, "gptq_marlin_gemm_silu_and_mul": 1, "gptq_marlin_24_gemm": 1,
     "cutlass_scaled_mm": 1, "scaled_fp8_quant": 2, "scaled_int8_quant": 1, "greedy_sample": 1,
     "rope_cache_paged_attention": 1,   # + the v2 merge kernel when exp_sums is given (counted in the wrapper)
-    "rms_norm_quant": 1, "silu_and_mul_quant": 1,
+    "rms_norm_quant": 1, "silu_and_mul_quant": 1,   # (also with kind "fp8_dynamic": the grid-wide maximum is inside the launch)
 }
 
 

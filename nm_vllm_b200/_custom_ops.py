@@ -80,17 +80,22 @@ def context_attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, o: 
                                  alibi_slopes, 0 if sliding_window is None or sliding_window <= 0 else sliding_window)
 
 
-_Q_DTYPE = {"fp8": torch.float8_e4m3fn, "int8": torch.int8, "int8_token": torch.int8}
+_Q_DTYPE = {"fp8": torch.float8_e4m3fn, "fp8_dynamic": torch.float8_e4m3fn, "int8": torch.int8, "int8_token": torch.int8}
+FUSED_DYNAMIC_FP8_MAX_TOKENS = 512   # kind "fp8_dynamic": all token CTAs must be co-resident (csrc/glue_quant.cu kDynMaxTokens)
 
 
 def rms_norm_quant(input: torch.Tensor, weight: torch.Tensor, epsilon: float, kind: str, scale: Optional[torch.Tensor] = None,
                    residual: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
     """rms_norm (residual is None) or fused_add_rms_norm (residual updated in place) fused with the activation quantiser of the
     W8A8 linear that consumes it; returns (quantised activations, scales) like scaled_fp8_quant / scaled_int8_quant.
-    kind "fp8" / "int8": `scale` is the static per-tensor scale; "int8_token": dynamic per-token scales are produced."""
+    kind "fp8" / "int8": `scale` is the static per-tensor scale; "int8_token": dynamic per-token scales are produced;
+    "fp8_dynamic": the dynamic per-TENSOR scale max|x| / 448 of scaled_fp8_quant(x, None) is computed in the same launch
+    (at most FUSED_DYNAMIC_FP8_MAX_TOKENS rows)."""
     out = torch.empty(input.shape, dtype=_Q_DTYPE[kind], device=input.device)
     if kind == "int8_token":
         scale = torch.empty((input.numel() // input.shape[-1], 1), dtype=torch.float32, device=input.device)
+    elif kind == "fp8_dynamic":
+        scale = torch.empty(1, dtype=torch.float32, device=input.device)
     _ops().rms_norm_quant(out, scale, input, residual, weight, epsilon, kind)
     return out, scale
 
@@ -101,6 +106,8 @@ def silu_and_mul_quant(x: torch.Tensor, kind: str, scale: Optional[torch.Tensor]
     out = torch.empty(x.shape[:-1] + (d,), dtype=_Q_DTYPE[kind], device=x.device)
     if kind == "int8_token":
         scale = torch.empty((x.numel() // x.shape[-1], 1), dtype=torch.float32, device=x.device)
+    elif kind == "fp8_dynamic":
+        scale = torch.empty(1, dtype=torch.float32, device=x.device)
     _ops().silu_and_mul_quant(out, scale, x, kind)
     return out, scale
 

@@ -13,7 +13,38 @@
 namespace b200 {
 namespace gq {
 
-enum { kFp8Static = 1, kInt8Static = 2, kInt8Token = 3 };
+enum { kFp8Static = 1, kInt8Static = 2, kInt8Token = 3, kFp8Dynamic = 4 };
+constexpr int64_t kDynMaxTokens = 512;   // kFp8Dynamic: every CTA of the grid must be co-resident (grid-wide maximum in one launch)
+
+// kFp8Dynamic (Fp8LinearMethod activation_scheme "dynamic": ONE per-tensor scale = max|x| / 448, fp8/common.cu:39-72): the
+// grid-wide maximum is taken inside the producing kernel -- every CTA holds its token row, publishes its row maximum with
+// an integer atomicMax, meets the others at a counter, then quantises with the common scale.  No allocation, no pre-zeroed
+// scale tensor: the three words below live for the life of the library (one set per GPU), are left zero by the last CTA of
+// every call, and are shared by every call -- calls that overlap on one GPU would race (decode steps run on one stream).
+// Bit-identical to norm / silu_and_mul -> dynamic_scaled_fp8_quant (same max|x| / 448 and 1 / scale).
+static __device__ unsigned int g_dyn_ws[4];   // [0] max bits of (row max / 448), [1] arrivals, [2] departures
+
+__device__ __forceinline__ float dyn_scale_exchange(float row_amax, float* __restrict__ scale_out, unsigned n_ctas) {
+  __shared__ float s_scale;
+  if (threadIdx.x == 0) {
+    atomicMax(reinterpret_cast<int*>(&g_dyn_ws[0]), __float_as_int(row_amax / 448.0f));
+    __threadfence();
+    atomicAdd(&g_dyn_ws[1], 1u);
+    while (*reinterpret_cast<volatile unsigned int*>(&g_dyn_ws[1]) < n_ctas) {}
+    __threadfence();
+    const float sc = __int_as_float(*reinterpret_cast<volatile int*>(&g_dyn_ws[0]));
+    s_scale = sc;
+    if (blockIdx.x == 0 && blockIdx.y == 0) *scale_out = sc;
+    if (atomicAdd(&g_dyn_ws[2], 1u) == n_ctas - 1) {   // everyone has read the maximum: leave the words zero for the next call
+      g_dyn_ws[0] = 0u;
+      g_dyn_ws[2] = 0u;
+      __threadfence();
+      g_dyn_ws[1] = 0u;
+    }
+  }
+  __syncthreads();
+  return s_scale;
+}
 
 template <typename T> __device__ __forceinline__ T mul_t(T a, T b) { return from_f32<T>(to_f32<T>(a) * to_f32<T>(b)); }
 template <typename T> __device__ __forceinline__ T add_t(T a, T b) { return from_f32<T>(to_f32<T>(a) + to_f32<T>(b)); }
@@ -50,7 +81,7 @@ __device__ __forceinline__ uint2 quant8(const T* z, float qmul) {
 #pragma unroll
   for (int e = 0; e < 8; ++e) {
     const float x = to_f32<T>(z[e]);
-    o[e] = QK == kFp8Static ? q_fp8(x, qmul) : (QK == kInt8Static ? q_i8(x / qmul) : q_i8(x * qmul));
+    o[e] = (QK == kFp8Static || QK == kFp8Dynamic) ? q_fp8(x, qmul) : (QK == kInt8Static ? q_i8(x / qmul) : q_i8(x * qmul));
   }
   return *reinterpret_cast<uint2*>(o);
 }
@@ -96,7 +127,7 @@ rms_norm_quant_kernel(uint8_t* __restrict__ out_q, float* __restrict__ scales, c
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
         z[e] = mul_t<T>(from_f32<T>(to_f32<T>(z[e]) * inv), ww[e]);
-        if (QK == kInt8Token) amax = fmaxf(amax, fabsf(to_f32<T>(z[e])));
+        if (QK == kInt8Token || QK == kFp8Dynamic) amax = fmaxf(amax, fabsf(to_f32<T>(z[e])));
       }
     }
   }
@@ -105,6 +136,9 @@ rms_norm_quant_kernel(uint8_t* __restrict__ out_q, float* __restrict__ scales, c
     amax = block_reduce(amax, red, true);
     if (threadIdx.x == 0) scales[blockIdx.x] = amax / 127.0f;
     qmul = 127.0f / amax;
+  } else if (QK == kFp8Dynamic) {
+    amax = block_reduce(amax, red, true);
+    qmul = 1.0f / dyn_scale_exchange(amax, scales, gridDim.x);
   } else {
     qmul = QK == kFp8Static ? 1.0f / (*scales) : *scales;
   }
@@ -137,7 +171,7 @@ silu_and_mul_quant_kernel(uint8_t* __restrict__ out_q, float* __restrict__ scale
     }
   };
   float qmul;
-  if (QK == kInt8Token) {
+  if (QK == kInt8Token || QK == kFp8Dynamic) {
     float amax = 0.f;
     for (int i = threadIdx.x * 8; i < d; i += 256 * 8) {
       T z[8];
@@ -146,8 +180,12 @@ silu_and_mul_quant_kernel(uint8_t* __restrict__ out_q, float* __restrict__ scale
       for (int e = 0; e < 8; ++e) amax = fmaxf(amax, fabsf(to_f32<T>(z[e])));
     }
     amax = block_reduce(amax, red, true);
-    if (threadIdx.x == 0) scales[tok] = amax / 127.0f;
-    qmul = 127.0f / amax;
+    if (QK == kFp8Dynamic) {
+      qmul = 1.0f / dyn_scale_exchange(amax, scales, gridDim.x);
+    } else {
+      if (threadIdx.x == 0) scales[tok] = amax / 127.0f;
+      qmul = 127.0f / amax;
+    }
   } else {
     qmul = QK == kFp8Static ? 1.0f / (*scales) : *scales;
   }
@@ -173,14 +211,18 @@ static int launch_norm(uint8_t* out_q, float* scales, const T* in, T* res, const
 }  // namespace b200
 
 // qkind: 1 = fp8 e4m3 with the static per-tensor scale *scales; 2 = int8 with the static per-tensor scale *scales; 3 = int8 with
-// dynamic per-token scales written to scales[num_tokens].  residual == NULL: rms_norm; otherwise fused_add_rms_norm (residual
+// dynamic per-token scales written to scales[num_tokens]; 4 = fp8 e4m3 with the DYNAMIC per-tensor scale max|x| / 448 computed
+// in the same launch and written to *scales (num_tokens <= 512, B200_ENOTSUP beyond).  residual == NULL: rms_norm; otherwise fused_add_rms_norm (residual
 // updated in place, `input` left untouched).
 extern "C" int b200_rms_norm_quant(void* out_q, float* scales, const void* input, void* residual, const void* weight,
                                    int64_t num_tokens, int hidden_size, float epsilon, int dtype, int qkind, void* stream) {
   using namespace b200;
   if (num_tokens == 0) return B200_OK;
   B200_CHECK(dtype == B200_F16 || dtype == B200_BF16, "rms_norm_quant: fp16 / bf16 activations only");
-  B200_CHECK(qkind >= 1 && qkind <= 3, "rms_norm_quant: qkind %d", qkind);
+  B200_CHECK(qkind >= 1 && qkind <= 4, "rms_norm_quant: qkind %d", qkind);
+  if (qkind == 4 && num_tokens > gq::kDynMaxTokens)
+    return set_error(B200_ENOTSUP, "rms_norm_quant: the fused dynamic per-tensor fp8 scale needs all %lld token CTAs co-resident (limit %lld): "
+                     "run the norm and dynamic_scaled_fp8_quant separately", (long long)num_tokens, (long long)gq::kDynMaxTokens);
   B200_CHECK(hidden_size % 8 == 0 && hidden_size <= 8192, "rms_norm_quant: hidden_size %d must be a multiple of 8 and <= 8192", hidden_size);
   B200_CHECK(((reinterpret_cast<uintptr_t>(input) | reinterpret_cast<uintptr_t>(residual) | reinterpret_cast<uintptr_t>(weight)) & 15) == 0 &&
              (reinterpret_cast<uintptr_t>(out_q) & 7) == 0, "rms_norm_quant: 16-byte aligned rows required");
@@ -192,10 +234,12 @@ extern "C" int b200_rms_norm_quant(void* out_q, float* scales, const void* input
     if (residual) {                                                                                                            \
       if (qkind == 1) rc = gq::launch_norm<TT, 1, true>(o, scales, in, rs, w, epsilon, hidden_size, num_tokens, st);           \
       else if (qkind == 2) rc = gq::launch_norm<TT, 2, true>(o, scales, in, rs, w, epsilon, hidden_size, num_tokens, st);      \
+      else if (qkind == 4) rc = gq::launch_norm<TT, 4, true>(o, scales, in, rs, w, epsilon, hidden_size, num_tokens, st);      \
       else rc = gq::launch_norm<TT, 3, true>(o, scales, in, rs, w, epsilon, hidden_size, num_tokens, st);                      \
     } else {                                                                                                                   \
       if (qkind == 1) rc = gq::launch_norm<TT, 1, false>(o, scales, in, rs, w, epsilon, hidden_size, num_tokens, st);          \
       else if (qkind == 2) rc = gq::launch_norm<TT, 2, false>(o, scales, in, rs, w, epsilon, hidden_size, num_tokens, st);     \
+      else if (qkind == 4) rc = gq::launch_norm<TT, 4, false>(o, scales, in, rs, w, epsilon, hidden_size, num_tokens, st);     \
       else rc = gq::launch_norm<TT, 3, false>(o, scales, in, rs, w, epsilon, hidden_size, num_tokens, st);                     \
     }                                                                                                                          \
   } while (0)
@@ -211,15 +255,18 @@ extern "C" int b200_silu_and_mul_quant(void* out_q, float* scales, const void* i
   using namespace b200;
   if (num_tokens == 0) return B200_OK;
   B200_CHECK(dtype == B200_F16 || dtype == B200_BF16, "silu_and_mul_quant: fp16 / bf16 activations only");
-  B200_CHECK(qkind >= 1 && qkind <= 3, "silu_and_mul_quant: qkind %d", qkind);
+  B200_CHECK(qkind >= 1 && qkind <= 4, "silu_and_mul_quant: qkind %d", qkind);
+  if (qkind == 4 && num_tokens > gq::kDynMaxTokens)
+    return set_error(B200_ENOTSUP, "silu_and_mul_quant: the fused dynamic per-tensor fp8 scale needs all %lld token CTAs co-resident (limit %lld)",
+                     (long long)num_tokens, (long long)gq::kDynMaxTokens);
   B200_CHECK(d % 8 == 0 && (reinterpret_cast<uintptr_t>(input) & 15) == 0 && (reinterpret_cast<uintptr_t>(out_q) & 7) == 0,
              "silu_and_mul_quant: d %% 8 == 0 and aligned rows required");
   cudaStream_t st = (cudaStream_t)stream;
   cudaError_t e = cudaSuccess;
-  const unsigned chunks = qkind == 3 ? 1u : (unsigned)((d + 2047) / 2048);
+  const unsigned chunks = (qkind == 3 || qkind == 4) ? 1u : (unsigned)((d + 2047) / 2048);
 #define GQ_SILU(TT, QQ) e = launch_pdl(gq::silu_and_mul_quant_kernel<TT, QQ>, dim3((unsigned)num_tokens, chunks), dim3(256), 0, st, (uint8_t*)out_q, scales, (const TT*)input, d)
-  if (dtype == B200_F16) { if (qkind == 1) GQ_SILU(__half, 1); else if (qkind == 2) GQ_SILU(__half, 2); else GQ_SILU(__half, 3); }
-  else { if (qkind == 1) GQ_SILU(__nv_bfloat16, 1); else if (qkind == 2) GQ_SILU(__nv_bfloat16, 2); else GQ_SILU(__nv_bfloat16, 3); }
+  if (dtype == B200_F16) { if (qkind == 1) GQ_SILU(__half, 1); else if (qkind == 2) GQ_SILU(__half, 2); else if (qkind == 4) GQ_SILU(__half, 4); else GQ_SILU(__half, 3); }
+  else { if (qkind == 1) GQ_SILU(__nv_bfloat16, 1); else if (qkind == 2) GQ_SILU(__nv_bfloat16, 2); else if (qkind == 4) GQ_SILU(__nv_bfloat16, 4); else GQ_SILU(__nv_bfloat16, 3); }
 #undef GQ_SILU
   if (e != cudaSuccess) return set_error(B200_ECUDA, "silu_and_mul_quant launch: %s", cudaGetErrorString(e));
   B200_LAUNCH_CHECK("silu_and_mul_quant");

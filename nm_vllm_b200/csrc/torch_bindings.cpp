@@ -98,6 +98,7 @@ static int qkind_enum(const std::string& kind) {
   if (kind == "fp8") return 1;
   if (kind == "int8") return 2;
   if (kind == "int8_token") return 3;
+  if (kind == "fp8_dynamic") return 4;
   TORCH_CHECK(false, "unknown quantisation kind: ", kind);
   return 0;
 }

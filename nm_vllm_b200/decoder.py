@@ -143,7 +143,7 @@ class QuantLinear:
     # ---- W8A8 with the activation quantiser fused into the producing kernel (fp8_static / int8) ----------------------
     @property
     def fused_quant_kind(self):
-        return {"fp8_static": "fp8", "int8": "int8_token"}.get(self.kind)
+        return {"fp8_static": "fp8", "int8": "int8_token", "fp8": "fp8_dynamic"}.get(self.kind)   # fp8_dynamic: opt-in, see SyntheticLlama.fuse_dynamic_fp8
 
     def mm_quantized(self, xq, xs):
         return ops.cutlass_scaled_mm(xq, self.weight, xs, self.weight_scale, self.dtype)
@@ -162,7 +162,12 @@ class SyntheticLlama:
         self.custom_ar = None  # CustomAllreduce once enable_custom_all_reduce() has been called
         self.n_custom_ar_calls = 0  # stand-alone all-reduce kernel launches (bench.py counts them per step)
         self.fuse_gemm_all_reduce = True  # row-parallel W4A16 GEMMs all-reduce in their epilogue when custom_ar is on
-        self.fuse_act_quant = True  # W8A8 with static fp8 / per-token int8 activations: quantiser fused into norm / silu kernels
+        # W8A8: activation quantiser (static fp8, per-token int8, dynamic per-tensor fp8) fused into the norm / silu kernels
+        self.fuse_act_quant = os.environ.get("B200_FUSE_ACT_QUANT", "1") != "0"
+        # dynamic per-tensor fp8 (kind "fp8_dynamic": grid-wide maximum inside the norm / silu launch) is OFF by default:
+        # measured on the 8B fp8 step it is slower than the three short kernels it replaces (5.02 vs 4.91 ms per step, 322 vs
+        # 514 launches) -- the in-kernel grid barrier costs more than two PDL-overlapped launches (profiles/r2_fp8_dynamic_fusion_ab.txt)
+        self.fuse_dynamic_fp8 = os.environ.get("B200_FUSE_DYNAMIC_FP8", "0") == "1"
         self.fuse_attention = True  # rope + cache write + paged attention in one launch when the shape is on the fast path
         self.fuse_silu = os.environ.get("B200_NO_FUSE_SILU", "0") != "1"   # SiluAndMul in the epilogue of the W4A16 gate_up GEMM
         s = shape
@@ -297,6 +302,8 @@ class SyntheticLlama:
         h = self.embed.index_select(0, token_ids)
         residual = None
         fq = self.layers[0]["qkv"].fused_quant_kind if self.fuse_act_quant else None
+        if fq == "fp8_dynamic" and (not self.fuse_dynamic_fp8 or token_ids.shape[0] > ops.FUSED_DYNAMIC_FP8_MAX_TOKENS):
+            fq = None   # off by default (measured slower); prefill-sized batches cannot take it at all (co-residency)
         for li, L in enumerate(self.layers):
             if fq is not None:
                 # norm (+ residual add) and the activation quantiser of qkv_proj in one kernel
