@@ -189,7 +189,11 @@ int b200_silu_and_mul(void* out, const void* input, int64_t num_tokens, int d, i
  * quantised in the same kernel exactly like static_scaled_fp8_quant (csrc/quantization/fp8/common.cu:74-125) or
  * static / dynamic_scaled_int8_quant (compressed_tensors/int8_quant_kernels.cu:30-71) would -- bit-identical to the two-op
  * chain.  qkind 1: fp8 e4m3, static per-tensor scale *scales; 2: int8, static per-tensor scale *scales; 3: int8, dynamic
- * per-token scales WRITTEN to scales[num_tokens].  residual != NULL: fused_add_rms_norm (residual updated in place). */
+ * per-token scales WRITTEN to scales[num_tokens]; 4: fp8 e4m3 with the DYNAMIC per-tensor scale max|x| / 448 of
+ * dynamic_scaled_fp8_quant (fp8/common.cu:39-72) computed inside the same launch and WRITTEN to scales[0] (grid-wide
+ * maximum through a static device word and an in-kernel barrier: num_tokens <= 512 or B200_ENOTSUP; calls that overlap on
+ * one GPU race; measured slower than the separate kernels at decode sizes, so nothing selects it by default).
+ * residual != NULL: fused_add_rms_norm (residual updated in place). */
 int b200_rms_norm_quant(void* out_q, float* scales, const void* input, void* residual, const void* weight,
                         int64_t num_tokens, int hidden_size, float epsilon, int dtype, int qkind, void* stream);
 int b200_silu_and_mul_quant(void* out_q, float* scales, const void* input, int64_t num_tokens, int d, int dtype,
