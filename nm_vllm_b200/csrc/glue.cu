@@ -68,6 +68,14 @@ template <typename T, bool FUSED_ADD, int VPT>
 __global__ void __launch_bounds__(256)
 rms_norm_vec_kernel(T* __restrict__ out, T* __restrict__ input, T* __restrict__ residual, const T* __restrict__ weight,
                     float eps, int hidden) {
+  // the norm weights do not depend on the previous kernel of the stream: fetch them BEFORE the programmatic-dependency wait,
+  // so their L2 latency (and, first time, HBM latency) overlaps the predecessor's tail instead of sitting behind the reduction
+  uint4 wv[VPT];
+#pragma unroll
+  for (int j = 0; j < VPT; ++j) {
+    const int i = (threadIdx.x + j * 256) * 8;
+    if (i < hidden) wv[j] = *reinterpret_cast<const uint4*>(weight + i);
+  }
   pdl_wait();
   pdl_launch_dependents();
   __shared__ float red[33];
@@ -97,8 +105,7 @@ rms_norm_vec_kernel(T* __restrict__ out, T* __restrict__ input, T* __restrict__ 
   for (int j = 0; j < VPT; ++j) {
     const int i = (threadIdx.x + j * 256) * 8;
     if (i < hidden) {
-      const uint4 w = *reinterpret_cast<const uint4*>(weight + i);
-      const T* ww = reinterpret_cast<const T*>(&w);
+      const T* ww = reinterpret_cast<const T*>(&wv[j]);
       T* z = reinterpret_cast<T*>(&v[j]);
 #pragma unroll
       for (int e = 0; e < 8; ++e) z[e] = mul_t<T>(from_f32<T>(to_f32<T>(z[e]) * inv), ww[e]);
