@@ -145,16 +145,36 @@ paged_attn_gqa_kernel(float* __restrict__ exp_sums, float* __restrict__ max_logi
   constexpr int OSTR = D + 4;   // padded row of the merge buffer (conflict-free fragment stores)
   __shared__ float sm_m[kWarps][GMAX], sm_l[kWarps][GMAX];
   __shared__ float sm_o[kWarps][GMAX][OSTR];
-  pdl_wait();
-  pdl_launch_dependents();
   const int kvh = blockIdx.x, seq = blockIdx.y, part = blockIdx.z, num_parts = gridDim.z;
   const int G = num_heads / num_kv_heads;
-  const int seq_len = seq_lens[seq];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int* btab = block_tables + (int64_t)seq * max_blocks_per_seq;
+  // L2 prefetch of this warp's first pages BEFORE the programmatic-dependency wait.  Nothing here depends on the previous
+  // kernel of the step: seq_lens / block_tables are step inputs, the pages hold tokens of earlier steps (the one slot written
+  // this step is written through L2, which the prefetch cannot make stale).  A warp otherwise walks its pages as a chain of
+  // dependent HBM round trips (all 64 loads of a page in flight, then the MMAs); at 16 pages per CTA (ctx 256) that chain,
+  // not bandwidth, is the kernel time.  kPrefetch pages ahead are kept in flight further down the loop.
+  constexpr int kPrefetch = 2;   // measured 1 .. 4: 1 is best stand-alone (85 % at 64 x 256), 2 best inside the decode step; 3-4 lose both ways
+  constexpr int kPageLines = D * BS * (FP8 ? 1 : 2) / 128;   // 128-byte lines of one K (or V) page: 32 / 16
+  const int seq_len_pf = seq_lens[seq];
+  const int start_block_pf = partitioned ? (part * kPartition) / BS : 0;
+  const int end_block_pf = ((partitioned ? min(part * kPartition + kPartition, seq_len_pf) : seq_len_pf) + BS - 1) / BS;
+  auto prefetch_page = [&](int blk) {
+    if (blk < end_block_pf && lane < kPageLines) {
+      const int64_t pb = ((int64_t)btab[blk] * kv_block_stride + (int64_t)kvh * kv_head_stride) * (FP8 ? 1 : 2) + lane * 128;
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char*>(k_cache_v) + pb));
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char*>(v_cache_v) + pb));
+    }
+  };
+#pragma unroll
+  for (int i = 0; i < kPrefetch; ++i) prefetch_page(start_block_pf + warp + i * kWarps);
+  pdl_wait();
+  pdl_launch_dependents();
+  const int seq_len = seq_len_pf;
   const int start_token = partitioned ? part * kPartition : 0;
   if (partitioned && start_token >= seq_len) return;   // attention_kernels.cu:116-119
   const int end_token = partitioned ? min(start_token + kPartition, seq_len) : seq_len;
   const int start_block = start_token / BS, end_block = (end_token + BS - 1) / BS;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane >> 2, qd = lane & 3;
   const int head0 = kvh * G;
 
@@ -225,8 +245,8 @@ paged_attn_gqa_kernel(float* __restrict__ exp_sums, float* __restrict__ max_logi
 #pragma unroll
   for (int i = 0; i < 8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
 
-  const int* btab = block_tables + (int64_t)seq * max_blocks_per_seq;
   for (int blk = start_block + warp; blk < end_block; blk += kWarps) {
+    prefetch_page(blk + kPrefetch * kWarps);
     const int64_t base = (int64_t)btab[blk] * kv_block_stride + (int64_t)kvh * kv_head_stride;
     const int tok0 = blk * BS;
     // MMA row r of S^T <-> token: auto: r; fp8: rows 0-7 -> 2r - r%2, rows 8-15 -> that + 2 (so that the transposed P

@@ -1,0 +1,5 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_attention.py tests/test_gpu_fused_attention.py tests/test_gpu_decode_e2e.py tests/test_gpu_linear_methods.py -m gpu -x -q 2>&1 | tail -2
+timeout 300 python tools/attn_perf.py > gpurun_out/attn_perf_bf16.txt 2>&1; tail -6 gpurun_out/attn_perf_bf16.txt
+timeout 300 python tools/attn_perf.py 64x256x32x8,64x2048x32x8,8x8192x32x8,64x8192x8x1,1x32768x32x8,64x32768x8x1 fp8 > gpurun_out/attn_perf_fp8.txt 2>&1; tail -6 gpurun_out/attn_perf_fp8.txt
