@@ -114,6 +114,7 @@ scaled_mm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     // ================= TMA producer: one weight box [128 n x 128 k] + one activation box [MT m x 128 k] per stage =======
     const uint64_t pol_w = policy_evict_first();
     const uint64_t pol_a = policy_evict_last();
+#ifdef B200_SMM_DIV_COORDS   // A/B build only: the producer loop as it was (runtime divisions per unit)
     auto coords = [&](int it, int& nt, int& mc, int& ks) {
       const int u = u_begin + it;
       const int tile = u / KS;
@@ -149,6 +150,51 @@ scaled_mm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       issue_w(it);
       issue_a(it);
     }
+#else
+    // (tile, k-block) cursor: divided ONCE, then stepped -- runtime integer divisions per unit in this single-warp loop cost
+    // 6-9 % of the Marlin kernel's time before they were removed there (profiles/r2_gemm_ablations.txt); same pattern here
+    struct Cursor { int ks, nt, mc; };
+    auto cursor_at = [&](int u) {
+      Cursor c;
+      const int tile = u / KS;
+      c.ks = u - tile * KS;
+      c.nt = tile / args.m_chunks;
+      c.mc = tile - c.nt * args.m_chunks;
+      return c;
+    };
+    auto advance = [&](Cursor& c) {
+      if (++c.ks == KS) {
+        c.ks = 0;
+        if (++c.mc == args.m_chunks) { c.mc = 0; ++c.nt; }
+      }
+    };
+    auto issue_w = [&](int it, const Cursor& c) {
+      const int s = it % NS;
+      if (elect_one()) {
+        mbar_arrive_expect_tx(full_bar(s), C::STAGE_BYTES);
+        tma_2d_g2s_hint(w_base + s * C::W_BYTES, &tmap_w, c.ks * kBlockK, c.nt * kTileN, full_bar(s),
+                        args.m_chunks > 1 ? pol_a : pol_w);
+      }
+      __syncwarp();
+    };
+    auto issue_a = [&](int it, const Cursor& c) {
+      const int s = it % NS;
+      if (elect_one()) tma_2d_g2s_hint(a_base + s * C::A_BYTES, &tmap_a, c.ks * kBlockK, c.mc * MT, full_bar(s), pol_a);
+      __syncwarp();
+    };
+    // weights do not depend on the previous kernel of the stream: first ring pass before the PDL wait
+    const int first = n_units < NS ? n_units : NS;
+    Cursor cw = cursor_at(u_begin), ca = cw;
+    for (int it = 0; it < first; ++it) { issue_w(it, cw); advance(cw); }
+    pdl_wait();
+    for (int it = 0; it < first; ++it) { issue_a(it, ca); advance(ca); }
+    for (int it = NS; it < n_units; ++it) {
+      mbar_wait(empty_bar(it % NS), ((it / NS) & 1) ^ 1);
+      issue_w(it, cw);
+      issue_a(it, cw);
+      advance(cw);
+    }
+#endif
   } else if (warp == 1) {
     // ================= MMA issuer =================
     constexpr uint32_t idesc = IS_FP8 ? make_idesc(1 /*F32*/, 0 /*E4M3*/, 0, kTileN, MT)

@@ -16,7 +16,7 @@ out = os.path.join(B.ROOT, "build", "variants", name)
 os.makedirs(out, exist_ok=True)
 B.build_ops()
 srcs = B.cuda_sources()
-var = [s for s in srcs if os.path.basename(s).startswith(("marlin_decode_inst", "marlin_gemm_inst")) or os.path.basename(s) == "marlin_gemm.cu"]
+var = [s for s in srcs if os.path.basename(s).startswith(("marlin_decode_inst", "marlin_gemm_inst")) or os.path.basename(s) in ("marlin_gemm.cu", "scaled_mm.cu")]
 def cc(s):
     o = os.path.join(out, os.path.basename(s)[:-3] + ".o")
     B._run([B.NVCC] + B.NVCC_FLAGS + flags + ["-c", s, "-o", o], log=o + ".log")
